@@ -1,0 +1,1282 @@
+// opal_oracle.cpp -- CPU ORACLE for the opal PIC hot path.  TEST INFRASTRUCTURE ONLY.
+//
+// A statement-by-statement C++ restatement of the reference's arithmetic for the per-timestep
+// loop (src/main.rs:238-267 of tgblackburn/opal v1.5.1).  Only tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference legs may load this library; the product
+// (libopal_b200.so) never does.  It exports the C ABI of include/opal_b200.h with the prefix
+// `opal_ref_`.
+//
+// Build: g++ -O2 -std=c++17 -fopenmp -ffp-contract=off -fno-fast-math (see oracle/Makefile):
+// rustc/LLVM never contracts a*b+c, so FMA contraction is disabled here as well.
+//
+// Pinning: the reference cannot be compiled in this environment (no cargo/rustc, no MPI, no
+// CFITSIO, no network for its 98 crates).  The oracle is pinned against the reference's own 13
+// known-answer tests for this path (tests/test_oracle_kat.py): yee.rs:903-1079 (laser_bc,
+// conducting_bc, periodic_bc), electron.rs:401-436, qed/photon_emission.rs:299-336,
+// qed/pwmci.rs:235-281, vec3.rs:152-169.  Third-party RNG distributions (rand_distr 0.2.2
+// ziggurat Exp1/StandardNormal) are NOT restated bit-for-bit: "parity unpinned" for every random
+// draw; QED-on comparisons are statistical.
+//
+// Legal-instance choices where the reference is non-deterministic: the cell sort is a stable
+// sort (mod.rs:288 is an unstable parallel sort: only key order is defined); deposit partial
+// sums are added in chunk order (yee.rs:621-628) with nthreads chunks.
+
+#define OPAL_PREFIX opal_ref_
+#include "../include/opal_b200.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#include <parallel/algorithm>
+#endif
+
+namespace {
+
+// ---- src/constants.rs:4-28 (rounded literals are part of the parity contract) ------------
+constexpr double SPEED_OF_LIGHT = 2.997925e8;
+constexpr double SPEED_OF_LIGHT_SQD = 89875517873681764.0;
+constexpr double VACUUM_PERMITTIVITY = 8.854188e-12;
+constexpr double VACUUM_PERMEABILITY = 1.256637e-6;
+constexpr double ELECTRON_CHARGE = -1.602177e-19;
+constexpr double ELEMENTARY_CHARGE = -ELECTRON_CHARGE;
+constexpr double ELECTRON_MASS = 9.109383e-31;
+constexpr double PROTON_MASS = 1.672622e-27;
+constexpr double ELECTRON_MASS_MEV = 0.510999;
+constexpr double CRITICAL_FIELD = 1.323285e18;
+constexpr double ALPHA_FINE = 7.29735257e-3;
+constexpr double COMPTON_TIME = 1.28808867e-21;
+constexpr double PI = 3.14159265358979323846264338327950288;   // std::f64::consts::PI
+constexpr double FRAC_PI_3 = 1.04719755119659774615421446109316763; // consts::FRAC_PI_3
+constexpr double INF = std::numeric_limits<double>::infinity();
+
+int g_threads = 1;
+
+// ---- particle/vec3.rs -----------------------------------------------------------------
+struct Vec3 { double x, y, z; };
+inline Vec3 operator+(Vec3 a, Vec3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }   // vec3.rs:39
+inline Vec3 operator-(Vec3 a, Vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }   // vec3.rs:46
+inline double operator*(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; } // vec3.rs:54
+inline Vec3 operator*(Vec3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }       // vec3.rs:62
+inline Vec3 operator*(double s, Vec3 a) { return {s * a.x, s * a.y, s * a.z}; }       // vec3.rs:70
+inline Vec3 operator/(Vec3 a, double s) { return {a.x / s, a.y / s, a.z / s}; }       // vec3.rs:86
+inline Vec3 cross(Vec3 a, Vec3 b) {                                                     // vec3.rs:102
+    return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+inline double norm_sqr(Vec3 a) { return a * a; }
+inline Vec3 normalize(Vec3 a) { double mag = std::sqrt(norm_sqr(a)); return a / mag; } // vec3.rs:114
+inline Vec3 orthogonal(Vec3 a) {                                                        // vec3.rs:120
+    Vec3 perp = (std::fabs(a.x) > std::fabs(a.z)) ? Vec3{-a.y, a.x, 0.0} : Vec3{0.0, -a.z, a.y};
+    return normalize(perp);
+}
+inline Vec3 rotate_around(Vec3 v, Vec3 axis, double theta) {                            // vec3.rs:129
+    double s = std::sin(theta), c = std::cos(theta);
+    return {
+        (c + axis.x * axis.x * (1.0 - c)) * v.x + (axis.x * axis.y * (1.0 - c) - axis.z * s) * v.y
+            + (axis.x * axis.z * (1.0 - c) + axis.y * s) * v.z,
+        (axis.y * axis.x * (1.0 - c) + axis.z * s) * v.x + (c + axis.y * axis.y * (1.0 - c)) * v.y
+            + (axis.y * axis.z * (1.0 - c) - axis.x * s) * v.z,
+        (axis.z * axis.x * (1.0 - c) - axis.y * s) * v.x + (axis.z * axis.y * (1.0 - c) + axis.x * s) * v.y
+            + (c + axis.z * axis.z * (1.0 - c)) * v.z};
+}
+
+// ---- rand_xoshiro 0.4.0 Xoshiro256StarStar + rand 0.7 f64 sampling ---------------------
+// (third-party crate, absent from /root/reference; published algorithm restated.  Exp1 is drawn
+// by inversion, not rand_distr's ziggurat: statistically identical, bitwise "unpinned".)
+struct Xoshiro {
+    uint64_t s[4];
+    static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
+    void seed_from_u64(uint64_t state) {   // SplitMix64 fill (rand_xoshiro's override)
+        for (int i = 0; i < 4; i++) {
+            state += 0x9e3779b97f4a7c15ULL;
+            uint64_t z = state;
+            z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+            z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+            s[i] = z ^ (z >> 31);
+        }
+    }
+    uint64_t next() {
+        uint64_t result = rotl(s[1] * 5, 7) * 9;
+        uint64_t t = s[1] << 17;
+        s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3];
+        s[2] ^= t; s[3] = rotl(s[3], 45);
+        return result;
+    }
+    void jump_with(const uint64_t J[4]) {
+        uint64_t t[4] = {0, 0, 0, 0};
+        for (int i = 0; i < 4; i++)
+            for (int b = 0; b < 64; b++) {
+                if (J[i] & (1ULL << b)) { t[0] ^= s[0]; t[1] ^= s[1]; t[2] ^= s[2]; t[3] ^= s[3]; }
+                next();
+            }
+        for (int i = 0; i < 4; i++) s[i] = t[i];
+    }
+    void jump() { static const uint64_t J[4] = {0x180ec6d33cfd0abaULL, 0xd5a61266f0c9392cULL, 0xa9582618e03fc9aaULL, 0x39abdc4529b1661cULL}; jump_with(J); }
+    void long_jump() { static const uint64_t J[4] = {0x76e15d3efefdcbbfULL, 0xc5004e441c522fb3ULL, 0x77710069854ee241ULL, 0x39109bb02acbe635ULL}; jump_with(J); }
+    double gen() { return (double)(next() >> 11) * (1.0 / 9007199254740992.0); }   // [0,1)
+    double exp1() { return -std::log1p(-gen()); }
+};
+
+// ---- grid/yee.rs:86-205 ------------------------------------------------------------------
+struct Cell { double x, rho, j[3], E[3], B[3]; };
+static_assert(sizeof(Cell) == 88, "Cell is 11 f64");
+
+inline double weight(double xi) {                       // yee.rs:140-149
+    double xhat = std::fabs(xi);
+    if (xhat > 1.5) return 0.0;
+    else if (xhat < 0.5) return 0.75 - xhat * xhat;
+    else return 1.125 - 1.5 * xhat + 0.5 * (xhat * xhat);
+}
+
+inline double flux(double x_i, double x_f) {            // yee.rs:185-204
+    if (std::fabs(x_i) < 1.0) {
+        if (std::fabs(x_f) >= 1.0) {
+            double t = 1.0 - std::fabs(x_i);
+            double v = 0.5 * (t * t);
+            return std::copysign(v, -x_i);
+        } else if (x_i * x_f >= 0.0) {
+            double tf = 1.0 - std::fabs(x_f), ti = 1.0 - std::fabs(x_i);
+            double v = 0.5 * (tf * tf) - 0.5 * (ti * ti);
+            return std::copysign(v, x_i - x_f);
+        } else {
+            double v = std::fabs(x_i) * (1.0 - 0.5 * std::fabs(x_i)) + std::fabs(x_f) * (1.0 - 0.5 * std::fabs(x_f));
+            return std::copysign(v, x_i);
+        }
+    } else if (std::fabs(x_f) < 1.0) {
+        double t = 1.0 - std::fabs(x_f);
+        double v = 0.5 * (t * t);
+        return std::copysign(v, x_f);
+    } else {
+        return 0.0;
+    }
+}
+
+// ---- qed/pwmci.rs -----------------------------------------------------------------------
+struct Fit { double x[2], f[2], m[2]; };
+typedef const double (*Table)[2];
+
+inline Fit fit_construct(size_t i, Table table, size_t len) {   // pwmci.rs:14-68
+    double secant[3];
+    auto sec = [&](size_t a, size_t b) { return (table[a][1] - table[b][1]) / (table[a][0] - table[b][0]); };
+    if (i == 1) { secant[0] = sec(i, i - 1); secant[1] = sec(i, i - 1); secant[2] = sec(i + 1, i); }
+    else if (i == len - 1) { secant[0] = sec(i - 1, i - 2); secant[1] = sec(i, i - 1); secant[2] = sec(i, i - 1); }
+    else { secant[0] = sec(i - 1, i - 2); secant[1] = sec(i, i - 1); secant[2] = sec(i + 1, i); }
+    double tangent[2];
+    tangent[0] = (secant[0] * secant[1] > 0.0) ? 0.5 * (secant[0] + secant[1]) : 0.0;
+    tangent[1] = (secant[1] * secant[2] > 0.0) ? 0.5 * (secant[1] + secant[2]) : 0.0;
+    if (secant[1] != 0.0) { double alpha = tangent[0] / secant[1]; if (alpha > 3.0) tangent[0] = 3.0 * secant[1]; }
+    if (secant[2] != 0.0) { double beta = tangent[1] / secant[2]; if (beta > 3.0) tangent[1] = 3.0 * secant[2]; }
+    return Fit{{table[i - 1][0], table[i][0]}, {table[i - 1][1], table[i][1]}, {tangent[0], tangent[1]}};
+}
+inline double fit_eval(const Fit& p, double x) {                // pwmci.rs:70-77
+    double t = (x - p.x[0]) / (p.x[1] - p.x[0]);
+    double h00 = (1.0 + 2.0 * t) * ((1.0 - t) * (1.0 - t));
+    double h10 = t * ((1.0 - t) * (1.0 - t));
+    double h01 = (t * t) * (3.0 - 2.0 * t);
+    double h11 = (t * t) * (t - 1.0);
+    return p.f[0] * h00 + p.f[1] * h01 + (p.x[1] - p.x[0]) * (p.m[0] * h10 + p.m[1] * h11);
+}
+inline bool is_between(double x, double mn, double mx) {        // pwmci.rs:86-94
+    if (mn < mx) return x > mn && x < mx;
+    else if (mx < mn) return x > mx && x < mn;
+    else return true;
+}
+// pwmci.rs:96-111; returns false for None.  (i == 0 would index table[-1] in the reference and
+// panic; callers never reach it, here it reports None.)
+inline bool pwmci_evaluate(double x, Table table, size_t len, double* out) {
+    size_t i = 0;
+    while (i < len && x > table[i][0]) i++;
+    if (i >= len - 1 && x > table[len - 1][0]) return false;
+    if (i == 0) return false;
+    Fit p = fit_construct(i, table, len);
+    *out = fit_eval(p, x);
+    return true;
+}
+// pwmci.rs:113-228
+inline bool pwmci_invert(double f, Table table, size_t len, double* out, int* nevals) {
+    size_t i = 0;
+    while (i < len && f > table[i][1]) i++;
+    if (i >= len - 1 && f > table[len - 1][1]) return false;
+    if (i == 0) return false;
+    Fit fit = fit_construct(i, table, len);
+    struct Root { double x, f; } root[4] = {{0, 0}, {0, 0}, {0, 0}, {0, 0}};
+    root[0].x = table[i - 1][0]; root[0].f = table[i - 1][1] - f;
+    root[1].x = table[i][0];     root[1].f = table[i][1] - f;
+    if (std::fabs(root[1].f) < std::fabs(root[0].f)) std::swap(root[0], root[1]);
+    root[2] = root[1];
+    bool prev_bisect = false;
+    int counter = 0;
+    for (int it = 0; it < 32; it++) {
+        counter++;
+        double s;
+        if (root[0].f != root[2].f && root[1].f != root[2].f) {
+            double r = root[0].f / root[2].f;
+            double s_ = root[0].f / root[1].f;
+            double t = root[1].f / root[2].f;
+            double p = s_ * (t * (r - t) * (root[2].x - root[0].x) - (1.0 - r) * (root[0].x - root[1].x));
+            double q = (t - 1.0) * (r - 1.0) * (s_ - 1.0);
+            s = root[0].x + p / q;
+        } else {
+            s = root[0].x - (root[0].f * (root[0].x - root[1].x) / (root[0].f - root[1].f));
+        }
+        if (!is_between(s, 0.25 * (3.0 * root[1].x + root[0].x), root[0].x)
+            || (prev_bisect && std::fabs(s - root[0].x) >= 0.5 * std::fabs(root[0].x - root[2].x))
+            || (!prev_bisect && std::fabs(s - root[0].x) >= 0.5 * std::fabs(root[2].x - root[3].x))) {
+            prev_bisect = true;
+            s = 0.5 * (root[0].x + root[1].x);
+        } else {
+            prev_bisect = false;
+        }
+        root[3] = root[2];
+        root[2] = root[0];
+        root[0].x = s;
+        root[0].f = fit_eval(fit, s) - f;
+        if (root[1].f * root[0].f >= 0.0) { root[1] = root[0]; root[0] = root[2]; }
+        if (std::fabs(root[1].f) < std::fabs(root[0].f)) std::swap(root[0], root[1]);
+        double error = std::fabs(root[1].x - root[0].x) / std::fabs(root[0].x);
+        if (error < 1.0e-6 || root[0].f == 0.0) break;
+    }
+    *out = root[0].x;
+    if (nevals) *nevals = counter;
+    return true;
+}
+
+// ---- qed/photon_emission.rs + tables -------------------------------------------------------
+#define OPAL_QED_TABLE_DATA
+static const double QED_TABLES[73][64] = {
+#include "../opal_b200/csrc/qed_tables.inc"
+};
+#undef OPAL_QED_TABLE_DATA
+struct CDF { double coeff, power; double table[31][2]; };
+static_assert(sizeof(CDF) == 64 * 8, "CDF is 64 f64");
+inline const CDF& quantum_cdf(size_t i) { return *reinterpret_cast<const CDF*>(QED_TABLES[i]); }
+inline const CDF& y_infinite_cdf() { return *reinterpret_cast<const CDF*>(QED_TABLES[41]); }
+inline const CDF& y_cdf(size_t i) { return *reinterpret_cast<const CDF*>(QED_TABLES[42 + i]); }
+constexpr size_t N_QUANTUM_CDF = 41, N_Y_CDF = 31;
+constexpr double LN_CHI_MIN = -4.60517018599, LN_CHI_STEP = 0.230258509299;      // tables.rs:3-4
+constexpr double LN_DELTA_MIN = -2.30258509299, LN_DELTA_STEP = 0.230258509299;  // tables.rs:6-7
+constexpr double DELTA_LN_CHI = 0.230258509299;                                  // photon_emission.rs:9
+
+static const double LN_H_CHI_TABLE[41][2] = {   // photon_emission.rs:14-56
+    {-4.60517019e+0, 1.64660829e+0}, {-4.37491168e+0, 1.64437994e+0}, {-4.14465317e+0, 1.64162210e+0},
+    {-3.91439466e+0, 1.63822181e+0}, {-3.68413615e+0, 1.63404803e+0}, {-3.45387764e+0, 1.62895132e+0},
+    {-3.22361913e+0, 1.62276454e+0}, {-2.99336062e+0, 1.61530492e+0}, {-2.76310211e+0, 1.60637755e+0},
+    {-2.53284360e+0, 1.59578044e+0}, {-2.30258509e+0, 1.58331053e+0}, {-2.07232658e+0, 1.56877061e+0},
+    {-1.84206807e+0, 1.55197597e+0}, {-1.61180957e+0, 1.53276058e+0}, {-1.38155106e+0, 1.51098175e+0},
+    {-1.15129255e+0, 1.48652339e+0}, {-9.21034037e-1, 1.45929745e+0}, {-6.90775528e-1, 1.42924408e+0},
+    {-4.60517019e-1, 1.39633080e+0}, {-2.30258509e-1, 1.36055104e+0}, {0.00000000e0, 1.32192247e+0},
+    {2.30258509e-1, 1.28048533e+0}, {4.60517019e-1, 1.23630061e+0}, {6.90775528e-1, 1.18944834e+0},
+    {9.21034037e-1, 1.14002554e+0}, {1.15129255e+0, 1.08814410e+0}, {1.38155106e+0, 1.03392829e+0},
+    {1.61180957e+0, 9.77512163e-1}, {1.84206807e+0, 9.19036694e-1}, {2.07232658e+0, 8.58647059e-1},
+    {2.30258509e+0, 7.96489918e-1}, {2.53284360e+0, 7.32710951e-1}, {2.76310211e+0, 6.67452686e-1},
+    {2.99336062e+0, 6.00852676e-1}, {3.22361913e+0, 5.33042051e-1}, {3.45387764e+0, 4.64144437e-1},
+    {3.68413615e+0, 3.94275229e-1}, {3.91439466e+0, 3.23541171e-1}, {4.14465317e+0, 2.52040210e-1},
+    {4.37491168e+0, 1.79861566e-1}, {4.60517019e+0, 1.07085976e-1}};
+
+static const double CLASSICAL_SPECTRUM_TABLE[41][2] = {   // photon_emission.rs:207-249
+    {-3.91202301e+0, -6.60517238e+0}, {-3.73932912e+0, -6.32380043e+0}, {-3.56663524e+0, -6.04325741e+0},
+    {-3.39394136e+0, -5.76365479e+0}, {-3.22124748e+0, -5.48512019e+0}, {-3.04855360e+0, -5.20779983e+0},
+    {-2.87585971e+0, -4.93186151e+0}, {-2.70316583e+0, -4.65749813e+0}, {-2.53047195e+0, -4.38493162e+0},
+    {-2.35777807e+0, -4.11441770e+0}, {-2.18508419e+0, -3.84625132e+0}, {-2.01239030e+0, -3.58077293e+0},
+    {-1.83969642e+0, -3.31837570e+0}, {-1.66700254e+0, -3.05951374e+0}, {-1.49430866e+0, -2.80471134e+0},
+    {-1.32161478e+0, -2.55457314e+0}, {-1.14892089e+0, -2.30979520e+0}, {-9.76227012e-1, -2.07117645e+0},
+    {-8.03533130e-1, -1.83963003e+0}, {-6.30839248e-1, -1.61619332e+0}, {-4.58145366e-1, -1.40203511e+0},
+    {-2.85451484e-1, -1.19845722e+0}, {-1.12757602e-1, -1.00688674e+0}, {5.99362800e-2, -8.28853548e-1},
+    {2.32630162e-1, -6.65945768e-1}, {4.05324044e-1, -5.19734006e-1}, {5.78017926e-1, -3.91654410e-1},
+    {7.50711808e-1, -2.82842583e-1}, {9.23405690e-1, -1.93918722e-1}, {1.09609957e+0, -1.24743702e-1},
+    {1.26879345e+0, -7.41989867e-2}, {1.44148734e+0, -4.00839889e-2}, {1.61418122e+0, -1.92451749e-2},
+    {1.78687510e+0, -8.00296501e-3}, {1.95956898e+0, -2.79652691e-3}, {2.13226286e+0, -7.92727241e-4},
+    {2.30495675e+0, -1.74957252e-4}, {2.47765063e+0, -2.86508630e-5}, {2.65034451e+0, -3.28906586e-6},
+    {2.82303839e+0, -2.47459791e-7}, {2.99573227e+0, -1.12649296e-8}};
+
+inline double fract(double v) { return v - std::trunc(v); }   // f64::fract
+
+bool g_chi_range_error = false;
+
+double qed_rate(double chi, double gamma) {            // photon_emission.rs:59-79
+    double h;
+    if (chi < 0.01) {
+        h = 5.0 * FRAC_PI_3 * (1.0 - 8.0 * chi / (5.0 * std::sqrt(3.0)));
+    } else if (chi >= 100.0) {
+        double cbrt_chi = std::cbrt(chi);
+        h = -1019.4661473121777 + 1786.716527650374 * cbrt_chi * cbrt_chi;
+        h = 1750.6263395722715 + cbrt_chi * cbrt_chi * h;
+        h = -2260.1819695887225 + cbrt_chi * h;
+        h = 0.00296527643253334 * h / (chi * chi);
+    } else {
+        double index = (std::log(chi) - LN_H_CHI_TABLE[0][0]) / DELTA_LN_CHI;
+        double w = fract(index);
+        size_t i = (size_t)std::floor(index);
+        if (i >= 40) i = 39;   // reference asserts index < 40 (photon_emission.rs:73)
+        double ln_h = (1.0 - w) * LN_H_CHI_TABLE[i][1] + w * LN_H_CHI_TABLE[i + 1][1];
+        h = std::exp(ln_h);
+    }
+    return std::sqrt(3.0) * ALPHA_FINE * chi * h / (2.0 * PI * gamma * COMPTON_TIME);
+}
+double qed_classical_rate(double chi, double gamma) {  // photon_emission.rs:82-85
+    double h = 5.0 * FRAC_PI_3;
+    return std::sqrt(3.0) * ALPHA_FINE * chi * h / (2.0 * PI * gamma * COMPTON_TIME);
+}
+
+double from_linear_cdf_table(double global_zero, double local_zero, double rand, const CDF& cdf) {   // :87-121
+    double r_zero;
+    if (local_zero < cdf.table[0][0]) {
+        r_zero = cdf.coeff * std::pow(local_zero - global_zero, cdf.power);
+    } else {
+        double tmp;
+        if (!pwmci_evaluate(local_zero, cdf.table, 31, &tmp)) return local_zero;
+        r_zero = tmp;
+    }
+    double r = r_zero + (1.0 - r_zero) * rand;
+    double y;
+    double inv;
+    if (r <= cdf.table[0][1]) {
+        double tmp = (std::log(r) - std::log(cdf.coeff)) / cdf.power;
+        y = std::exp(tmp) + global_zero;
+    } else if (pwmci_invert(r, cdf.table, 31, &inv, nullptr)) {
+        y = inv;
+    } else {
+        y = local_zero;
+    }
+    return y;
+}
+
+void qed_classical_sample(double chi, double gamma, double rand1, double rand2, double rand3, double out[3]) {  // :264-292
+    double delta = std::acos((-9.0 + 50.0 * rand2 - 25.0 * (rand2 * rand2)) / 16.0);
+    double zb = (2.0 + 4.0 * std::cos(delta / 3.0)) / (5.0 * (1.0 - rand2));
+    double z = zb * zb * zb;   // powi(3)
+    double ln_rand = std::log(rand1);
+    double x;
+    if (ln_rand < CLASSICAL_SPECTRUM_TABLE[0][1]) {
+        x = 1.020377255 * std::pow(rand1, 0.6);
+    } else {
+        double ln_x;
+        if (!pwmci_invert(ln_rand, CLASSICAL_SPECTRUM_TABLE, 41, &ln_x, nullptr)) ln_x = CLASSICAL_SPECTRUM_TABLE[40][0];
+        x = std::exp(ln_x);
+    }
+    double u = 3.0 * chi * x / (2.0 * z);
+    double omega_mc2 = u * gamma;
+    double cos_theta = (gamma - std::pow(z, 2.0 / 3.0) / (2.0 * gamma)) / std::sqrt(gamma * gamma - 1.0);
+    // f64::min/max ignore NaN: a NaN cos_theta becomes 1.0
+    double ct = std::isnan(cos_theta) ? 1.0 : std::min(cos_theta, 1.0);
+    ct = std::max(ct, -1.0);
+    out[0] = omega_mc2; out[1] = std::acos(ct); out[2] = 2.0 * PI * rand3;
+}
+
+void qed_sample(double chi, double gamma, double rand1, double rand2, double rand3, double out[3]) {   // :129-203
+    double index_f = (std::log(chi) - LN_CHI_MIN) / LN_CHI_STEP;
+    double w = fract(index_f);
+    // `as usize` saturates: negative -> 0
+    double fl = std::floor(index_f);
+    size_t index = fl <= 0.0 ? 0 : (size_t)fl;
+    if (std::log(chi) <= LN_CHI_MIN) {
+        double c[3];
+        qed_classical_sample(chi, gamma, rand1, rand2, rand3, c);
+        out[0] = c[0] * gamma / (gamma + c[0]); out[1] = c[1]; out[2] = c[2];
+        return;
+    } else if (index >= N_QUANTUM_CDF - 1) {
+        g_chi_range_error = true;   // unimplemented!() photon_emission.rs:144
+        out[0] = out[1] = out[2] = std::numeric_limits<double>::quiet_NaN();
+        return;
+    }
+    auto ln_u_from = [&](const CDF& t) {
+        double inv;
+        if (std::log(rand1) <= t.table[0][1]) return (std::log(rand1) - std::log(t.coeff)) / t.power;
+        else if (pwmci_invert(std::log(rand1), t.table, 31, &inv, nullptr)) return inv;
+        else return t.table[30][0];
+    };
+    double ln_u_lower = ln_u_from(quantum_cdf(index));
+    double ln_u_upper = ln_u_from(quantum_cdf(index + 1));
+    double u = std::exp((1.0 - w) * ln_u_lower + w * ln_u_upper);
+    double beta = 2.0 * u / (3.0 * chi);
+    double delta = (1.0 + (1.0 + u) * (1.0 + u)) * std::pow(beta, -2.0 / 3.0) / (1.0 + u);
+    double index2_f = (std::log(delta) - LN_DELTA_MIN) / LN_DELTA_STEP;
+    double w2 = fract(index2_f);
+    double fl2 = std::floor(index2_f);
+    size_t index2 = fl2 <= 0.0 ? 0 : (size_t)fl2;
+    double y;
+    if (index2 >= N_Y_CDF - 1) {
+        y = from_linear_cdf_table(0.0, beta, rand2, y_infinite_cdf());
+    } else {
+        double y_lower = from_linear_cdf_table(std::pow(delta, -1.5), beta, rand2, y_cdf(index2));
+        double y_upper = from_linear_cdf_table(std::pow(delta, -1.5), beta, rand2, y_cdf(index2 + 1));
+        y = (1.0 - w2) * y_lower + w2 * y_upper;
+    }
+    double z = std::fmax(y / beta, 1.0);
+    double cos_theta = (gamma - std::pow(z, 2.0 / 3.0) / (2.0 * gamma)) / std::sqrt(gamma * gamma - 1.0);
+    double ct = std::isnan(cos_theta) ? 1.0 : std::min(cos_theta, 1.0);
+    ct = std::max(ct, -1.0);
+    out[0] = gamma * u / (1.0 + u); out[1] = std::acos(ct); out[2] = 2.0 * PI * rand3;
+}
+
+// ---- particle structs: reference layouts (electron.rs:14-27, ion.rs:14-26, photon.rs:16-32) ---
+struct Electron {
+    int64_t cell; double prev_x, x, y, z, weight, gamma; Vec3 u; double chi, tau, work; bool flag;
+};
+static_assert(sizeof(Electron) == 112, "Electron is 112 B");
+struct Ion {
+    int64_t cell; double prev_x, x, weight, Z_star, Z, A, gamma_m1; Vec3 u; double work; bool flag;
+};
+static_assert(sizeof(Ion) == 104, "Ion is 104 B");
+struct Photon {
+    int64_t cell; double prev_x, x, y, z, weight; Vec3 k; double pol[2][2]; Vec3 basis[2];
+    double chi, tau[2], tau_abs, tau_st, birth_time; bool flag;
+};
+static_assert(sizeof(Photon) == 208, "Photon is 208 B");
+
+inline Electron electron_create(int64_t cell, double x, Vec3 u, double weight, double dx, double dt) {  // electron.rs:85-103
+    double gamma = std::sqrt(1.0 + u * u);
+    double prev_x = x - SPEED_OF_LIGHT * u.x * dt / (gamma * dx);
+    return Electron{cell, prev_x, x, 0.0, 0.0, weight, gamma, u, 0.0, INF, 0.0, false};
+}
+inline Ion ion_create(int64_t cell, double x, Vec3 u, double weight, double dx, double dt) {  // ion.rs:81-101
+    double gamma_m1 = norm_sqr(u) / (1.0 + std::sqrt(1.0 + norm_sqr(u)));
+    Vec3 v = SPEED_OF_LIGHT * u / (1.0 + gamma_m1);
+    double prev_x = x - v.x * dt / dx;
+    return Ion{cell, prev_x, x, weight, 1.0, 1.0, 1.0, gamma_m1, u, 0.0, false};
+}
+inline Photon photon_create(int64_t cell, double x, Vec3 k, double weight, double dx, double dt) {  // photon.rs:95-116
+    double k0 = std::sqrt(norm_sqr(k));
+    double prev_x = x - SPEED_OF_LIGHT * k.x * dt / (k0 * dx);
+    Photon p;
+    std::memset(&p, 0, sizeof(p));
+    p.cell = cell; p.prev_x = prev_x; p.x = x; p.y = 0.0; p.z = 0.0; p.weight = weight; p.k = k;
+    p.basis[0] = k; p.basis[1] = k; p.chi = 0.0; p.tau[0] = p.tau[1] = INF; p.tau_abs = INF; p.tau_st = INF;
+    p.birth_time = -INF; p.flag = false;
+    return p;
+}
+
+template <class P> inline void cell_update(P& p) {   // electron.rs:319-329 (same in ion.rs, photon.rs)
+    double fl = std::floor(p.x);
+    if (fl < 0.0) p.cell = p.cell - 1;
+    else if (fl > 0.0) p.cell = p.cell + 1;
+    p.prev_x -= fl;
+    p.x -= fl;
+}
+
+struct PushCtx { uint32_t flags; bool cfl_violation; };
+
+// electron.rs:268-330
+inline void push(Electron& e, const double E_[3], const double B_[3], double dx, double dt, PushCtx& pc) {
+    Vec3 E{E_[0], E_[1], E_[2]}, B{B_[0], B_[1], B_[2]};
+    Vec3 v = SPEED_OF_LIGHT * e.u / e.gamma;
+    double alpha = ELECTRON_CHARGE * dt / (2.0 * ELECTRON_MASS * SPEED_OF_LIGHT);
+    Vec3 u_half = e.u + alpha * (E + cross(v, B));
+    e.work += ELECTRON_CHARGE * SPEED_OF_LIGHT * (u_half * E) * dt / std::sqrt(1.0 + u_half * u_half);
+    double gamma_half = std::sqrt(1.0 + u_half * u_half);
+    double eu = E * u_half;
+    e.chi = std::sqrt(norm_sqr(gamma_half * E + SPEED_OF_LIGHT * cross(u_half, B)) - eu * eu) / CRITICAL_FIELD;
+    if (pc.flags & OPAL_FLAG_NO_RADIATION_REACTION) e.tau = e.tau - qed_classical_rate(e.chi, gamma_half) * dt;
+    else e.tau = e.tau - qed_rate(e.chi, gamma_half) * dt;
+    Vec3 u_prime = u_half + alpha * E;
+    double gamma_prime_sqd = 1.0 + u_prime * u_prime;
+    Vec3 tau = alpha * SPEED_OF_LIGHT * B;
+    double u_star = u_prime * tau;
+    double sigma = gamma_prime_sqd - tau * tau;
+    e.gamma = std::sqrt(0.5 * sigma + std::sqrt(0.25 * (sigma * sigma) + tau * tau + u_star * u_star));
+    Vec3 t = tau / e.gamma;
+    double s = 1.0 / (1.0 + t * t);
+    e.u = s * (u_prime + (u_prime * t) * t + cross(u_prime, t));
+    e.prev_x = e.x;
+    double dxi = SPEED_OF_LIGHT * e.u.x * dt / (dx * e.gamma);
+    if (!(dxi < 1.0)) pc.cfl_violation = true;
+    e.x = e.x + dxi;
+    e.y = e.y + v.y * dt;
+    e.z = e.z + v.z * dt;
+    cell_update(e);
+}
+
+// ion.rs:168-214
+inline void push(Ion& p, const double E_[3], const double B_[3], double dx, double dt, PushCtx& pc) {
+    Vec3 E{E_[0], E_[1], E_[2]};
+    Vec3 cB = SPEED_OF_LIGHT * Vec3{B_[0], B_[1], B_[2]};
+    double q = p.Z_star * ELEMENTARY_CHARGE;
+    double M = p.A * PROTON_MASS;
+    double alpha = q * dt / (2.0 * M * SPEED_OF_LIGHT);
+    Vec3 u_minus = p.u + alpha * E;
+    double gamma = 1.0 + norm_sqr(u_minus) / (1.0 + std::sqrt(1.0 + norm_sqr(u_minus)));
+    double t = alpha / gamma;
+    Vec3 u_prime = u_minus + t * cross(u_minus, cB);
+    double t_prime = 2.0 * t / (1.0 + (t * t) * norm_sqr(cB));
+    Vec3 u_plus = u_minus + t_prime * cross(u_prime, cB);
+    p.u = u_plus + alpha * E;
+    p.gamma_m1 = norm_sqr(p.u) / (1.0 + std::sqrt(1.0 + norm_sqr(p.u)));
+    p.prev_x = p.x;
+    double dxi = SPEED_OF_LIGHT * p.u.x * dt / (dx * (1.0 + p.gamma_m1));
+    if (!(dxi < 1.0)) pc.cfl_violation = true;
+    p.x = p.x + dxi;
+    cell_update(p);
+}
+
+// photon.rs:150-183
+inline void push(Photon& p, const double E_[3], const double B_[3], double dx, double dt, PushCtx& pc) {
+    Vec3 E{E_[0], E_[1], E_[2]}, B{B_[0], B_[1], B_[2]};
+    double k0 = std::sqrt(norm_sqr(p.k));
+    Vec3 v = SPEED_OF_LIGHT * p.k / k0;
+    double ek = E * p.k;
+    p.chi = std::sqrt(norm_sqr(k0 * E + SPEED_OF_LIGHT * cross(p.k, B)) - ek * ek) / CRITICAL_FIELD;
+    p.prev_x = p.x;
+    double dxi = v.x * dt / dx;
+    if (!(dxi < 1.0)) pc.cfl_violation = true;
+    p.x = p.x + dxi;
+    p.y = p.y + v.y * dt;
+    p.z = p.z + v.z * dt;
+    cell_update(p);
+}
+
+inline double charge_of(const Electron&) { return ELECTRON_CHARGE; }
+inline double charge_of(const Ion& p) { return p.Z_star * ELEMENTARY_CHARGE; }
+inline double charge_of(const Photon&) { return 0.0; }
+inline Vec3 velocity_of(const Electron& e) { return SPEED_OF_LIGHT * e.u / e.gamma; }          // electron.rs:148
+inline Vec3 velocity_of(const Ion& p) { return SPEED_OF_LIGHT * p.u / (1.0 + p.gamma_m1); }     // ion.rs:123
+inline Vec3 velocity_of(const Photon& p) { double k0 = std::sqrt(norm_sqr(p.k)); return SPEED_OF_LIGHT * p.k / k0; }
+inline double kinetic_energy_of(const Electron& e) {   // electron.rs:122-126
+    double to_joules = 1.0e6 * ELECTRON_MASS_MEV * ELEMENTARY_CHARGE;
+    return e.weight * norm_sqr(e.u) * to_joules / (e.gamma + 1.0);
+}
+inline double kinetic_energy_of(const Ion& p) {        // ion.rs:128-134
+    double energy = p.gamma_m1 * (p.A * PROTON_MASS / ELECTRON_MASS) * ELECTRON_MASS_MEV;
+    return p.weight * energy * 1.0e6 * ELEMENTARY_CHARGE;
+}
+inline double kinetic_energy_of(const Photon& p) {     // photon.rs:220-226
+    double energy = std::sqrt(norm_sqr(p.k)) * ELECTRON_MASS_MEV;
+    return p.weight * energy * 1.0e6 * ELEMENTARY_CHARGE;
+}
+
+// ---- wire format --------------------------------------------------------------------------
+inline opal_migrant to_wire(const Electron& e) {
+    opal_migrant m; std::memset(&m, 0, sizeof(m));
+    m.cell = e.cell; m.x = e.x; m.prev_x = e.prev_x; m.u[0] = e.u.x; m.u[1] = e.u.y; m.u[2] = e.u.z;
+    m.weight = e.weight; m.gamma = e.gamma; m.chi = e.chi; m.tau = e.tau; m.work = e.work; m.y = e.y; m.z = e.z;
+    return m;
+}
+inline void from_wire(const opal_migrant& m, Electron& e) {
+    e = Electron{m.cell, m.prev_x, m.x, m.y, m.z, m.weight, m.gamma, Vec3{m.u[0], m.u[1], m.u[2]}, m.chi, m.tau, m.work, false};
+}
+inline opal_migrant to_wire(const Ion& p) {
+    opal_migrant m; std::memset(&m, 0, sizeof(m));
+    m.cell = p.cell; m.x = p.x; m.prev_x = p.prev_x; m.u[0] = p.u.x; m.u[1] = p.u.y; m.u[2] = p.u.z;
+    m.weight = p.weight; m.gamma = 1.0 + p.gamma_m1; m.work = p.work; m.pad[0] = p.gamma_m1;
+    return m;
+}
+struct IonSpec { double Z_star = 1.0, A = 1.0; };
+IonSpec g_dummy;
+inline void from_wire(const opal_migrant& m, Ion& p, const IonSpec& s) {
+    p = Ion{m.cell, m.prev_x, m.x, m.weight, s.Z_star, s.Z_star, s.A, m.pad[0], Vec3{m.u[0], m.u[1], m.u[2]}, m.work, false};
+}
+inline opal_migrant to_wire(const Photon& p) {
+    opal_migrant m; std::memset(&m, 0, sizeof(m));
+    m.cell = p.cell; m.x = p.x; m.prev_x = p.prev_x; m.u[0] = p.k.x; m.u[1] = p.k.y; m.u[2] = p.k.z;
+    m.weight = p.weight; m.gamma = std::sqrt(norm_sqr(p.k)); m.chi = p.chi; m.y = p.y; m.z = p.z; m.birth_time = p.birth_time;
+    m.tau = p.tau[0];
+    return m;
+}
+inline void from_wire(const opal_migrant& m, Photon& p) {
+    p = photon_create(m.cell, m.x, Vec3{m.u[0], m.u[1], m.u[2]}, m.weight, 1.0, 0.0);
+    p.prev_x = m.prev_x; p.chi = m.chi; p.y = m.y; p.z = m.z; p.birth_time = m.birth_time;
+    p.tau[0] = p.tau[1] = p.tau_abs = p.tau_st = m.tau;
+}
+
+// ---- Population<T> (particle/mod.rs:141-376) ----------------------------------------------
+template <class T> struct Population {
+    std::vector<T> store;
+    // pending migration state (between advance and the splice of mod.rs:372-373)
+    bool pending = false;
+    size_t num = 0, gone_left = 0, gone_right = 0;
+    std::vector<T> recv_left, recv_right;
+    int64_t last_left = 0, last_right = 0;
+};
+
+}  // namespace
+
+// ---- the context ----------------------------------------------------------------------------
+struct opal_ctx {
+    int rank, nranks;
+    int left_bdy, right_bdy;              // resolved for this slab (yee.rs:278-292)
+    int64_t left_size, right_size, size;  // zone sizes and interior cells
+    double dx, dt;
+    uint32_t flags;
+    std::vector<Cell> cell;
+    double halo_recv[2][OPAL_HALO_CELLS * OPAL_CELL_DOUBLES];
+    bool halo_given[2] = {false, false};
+    Population<Electron> electrons;
+    Population<Ion> ions;
+    Population<Photon> photons;
+    IonSpec ion_spec;
+    Xoshiro rng;
+    int status = OPAL_OK;
+    std::string err;
+
+    bool has_left() const { return left_bdy == OPAL_BDY_INTERNAL; }    // yee.rs:329-343
+    bool has_right() const { return right_bdy == OPAL_BDY_INTERNAL; }
+    bool self_neighbour() const { return nranks == 1; }
+};
+
+namespace {
+
+// yee.rs:499-529
+inline bool fields_at(const opal_ctx* g, int64_t c, double xi, double E[3], double B[3]) {
+    int64_t j = c + g->left_size;
+    if (!(j >= g->left_size) || !(j < (int64_t)g->cell.size() - g->right_size)) return false;
+    const Cell* cell = g->cell.data();
+    E[0] = cell[j - 1].E[0] * weight(0.5 + xi) + cell[j].E[0] * weight(0.5 - xi) + cell[j + 1].E[0] * weight(1.5 - xi);
+    E[1] = cell[j - 1].E[1] * weight(1.0 + xi) + cell[j].E[1] * weight(xi) + cell[j + 1].E[1] * weight(1.0 - xi)
+         + cell[j + 2].E[1] * weight(2.0 - xi);
+    E[2] = cell[j - 1].E[2] * weight(1.0 + xi) + cell[j].E[2] * weight(xi) + cell[j + 1].E[2] * weight(1.0 - xi)
+         + cell[j + 2].E[2] * weight(2.0 - xi);
+    B[0] = cell[j].B[0];
+    B[1] = cell[j - 1].B[1] * weight(0.5 + xi) + cell[j].B[1] * weight(0.5 - xi) + cell[j + 1].B[1] * weight(1.5 - xi);
+    B[2] = cell[j - 1].B[2] * weight(0.5 + xi) + cell[j].B[2] * weight(0.5 - xi) + cell[j + 1].B[2] * weight(1.5 - xi);
+    return true;
+}
+
+template <class T> void apply_recv(opal_ctx*, Population<T>& pop, int64_t max) {
+    // mod.rs:366-373
+    for (auto& pt : pop.recv_right) pt.cell += max;
+    auto& s = pop.store;
+    // splice(num-gone_right..num, recv_right) then splice(0..gone_left, recv_left)
+    s.erase(s.begin() + (pop.num - pop.gone_right), s.begin() + pop.num);
+    s.insert(s.begin() + (pop.num - pop.gone_right), pop.recv_right.begin(), pop.recv_right.end());
+    s.erase(s.begin(), s.begin() + pop.gone_left);
+    s.insert(s.begin(), pop.recv_left.begin(), pop.recv_left.end());
+    pop.recv_left.clear(); pop.recv_right.clear();
+    pop.pending = false;
+}
+
+template <class T> void finalize(opal_ctx* g, Population<T>& pop) {
+    if (pop.pending) apply_recv(g, pop, g->size);
+}
+
+// particle/mod.rs:247-376
+template <class T> void advance(opal_ctx* g, Population<T>& pop) {
+    finalize(g, pop);
+    const double dx = g->dx, dt = g->dt;
+    const int64_t max = g->size;
+    const size_t num = pop.store.size();
+    size_t gone_left = 0, gone_right = 0;
+    bool bad_index = false, bad_cfl = false;
+    T* pts = pop.store.data();
+#pragma omp parallel for schedule(static) num_threads(g_threads) reduction(+ : gone_left, gone_right) reduction(|| : bad_index, bad_cfl)
+    for (size_t i = 0; i < num; i++) {
+        T& pt = pts[i];
+        double E[3], B[3];
+        PushCtx pc{g->flags, false};
+        if (!fields_at(g, pt.cell, pt.x, E, B)) { bad_index = true; continue; }
+        push(pt, E, B, dx, dt, pc);
+        pt.flag = false;
+        if (pc.cfl_violation) bad_cfl = true;
+        if (pt.cell < 0) gone_left++;
+        else if (pt.cell >= max) gone_right++;
+    }
+    if (bad_index && g->status == OPAL_OK) { g->status = OPAL_EASSERT_INDEX; g->err = "fields_at: cell index out of range (yee.rs:501-502)"; }
+    if (bad_cfl && g->status == OPAL_OK) { g->status = OPAL_EASSERT_CFL; g->err = "push: dxi >= 1 (electron.rs:313)"; }
+
+    // mod.rs:288 (any sort with the same key order is a legal instance)
+    auto by_cell = [](const T& a, const T& b) { return a.cell < b.cell; };
+#ifdef _OPENMP
+    if (g_threads > 1) {
+        omp_set_num_threads(g_threads);
+        __gnu_parallel::sort(pop.store.begin(), pop.store.end(), by_cell);
+    } else
+#endif
+        std::stable_sort(pop.store.begin(), pop.store.end(), by_cell);
+
+    for (size_t i = num - gone_right; i < num; i++) pop.store[i].cell -= max;   // mod.rs:291-293
+
+    pop.num = num; pop.gone_left = gone_left; pop.gone_right = gone_right;
+    pop.last_left = (int64_t)gone_left; pop.last_right = (int64_t)gone_right;
+    pop.recv_left.clear(); pop.recv_right.clear();
+    pop.pending = true;
+
+    if (g->self_neighbour()) {
+        // mod.rs:313-315, 338-340: np == 1 periodic short-circuit
+        if (g->has_right()) pop.recv_right.assign(pop.store.begin(), pop.store.begin() + gone_left);
+        if (g->has_left()) pop.recv_left.assign(pop.store.begin() + (num - gone_right), pop.store.begin() + num);
+        apply_recv(g, pop, max);
+    }
+    // remote neighbours: leavers wait at the head/tail of `store` for migrants_take(); the splice
+    // happens at the next use of the population (finalize).
+}
+
+// yee.rs:551-641
+template <class T> void deposit(opal_ctx* g, Population<T>& pop) {
+    finalize(g, pop);
+    const double dx = g->dx, dt = g->dt;
+    const size_t size = g->cell.size();
+    const int64_t left = g->left_size;
+    const size_t n = pop.store.size();
+    if (n == 0) return;
+    const size_t nthreads = (size_t)g_threads;
+    const size_t chunk_len = n > nthreads ? n / nthreads : n;
+    const size_t nchunks = (n + chunk_len - 1) / chunk_len;
+    std::vector<std::vector<double>> j(nchunks);
+    bool bad = false;
+    const T* pts = pop.store.data();
+#pragma omp parallel for schedule(static, 1) num_threads(g_threads) reduction(|| : bad)
+    for (size_t k = 0; k < nchunks; k++) {
+        std::vector<double>& jj = j[k];
+        jj.assign(size * 4, 0.0);
+        const size_t lo = k * chunk_len, hi = std::min(n, lo + chunk_len);
+        for (size_t i = lo; i < hi; i++) {
+            const T& pt = pts[i];
+            const int64_t c = pt.cell; const double x = pt.x, prev_x = pt.prev_x;
+            const double macrocharge = pt.weight * charge_of(pt);
+            const Vec3 velocity = velocity_of(pt);
+            const int64_t index = c + left;
+            if (!(index >= 2) || !(index < (int64_t)size - 2)) { bad = true; continue; }
+            double* J = jj.data() + 4 * index;
+            J[0] += macrocharge * flux(0.5 - prev_x, 0.5 - x) / dt;
+            J[-4] += macrocharge * flux(-0.5 - prev_x, -0.5 - x) / dt;
+            J[-8] += macrocharge * flux(-1.5 - prev_x, -1.5 - x) / dt;
+            J[4] += macrocharge * flux(1.5 - prev_x, 1.5 - x) / dt;
+            J[8] += macrocharge * flux(2.5 - prev_x, 2.5 - x) / dt;
+
+            J[-4 + 1] += macrocharge * velocity.y * weight(1.0 + x) / dx;
+            J[1] += macrocharge * velocity.y * weight(x) / dx;
+            J[4 + 1] += macrocharge * velocity.y * weight(1.0 - x) / dx;
+            J[8 + 1] += macrocharge * velocity.y * weight(2.0 + x) / dx;   // quirk Q1 (yee.rs:597)
+
+            J[-4 + 2] += macrocharge * velocity.z * weight(1.0 + x) / dx;
+            J[2] += macrocharge * velocity.z * weight(x) / dx;
+            J[4 + 2] += macrocharge * velocity.z * weight(1.0 - x) / dx;
+            J[8 + 2] += macrocharge * velocity.z * weight(2.0 + x) / dx;
+
+            J[-4 + 3] += macrocharge * weight(1.0 + x) / dx;
+            J[3] += macrocharge * weight(x) / dx;
+            J[4 + 3] += macrocharge * weight(1.0 - x) / dx;
+            J[-8 + 3] += macrocharge * weight(2.0 - x) / dx;               // quirk Q2 (yee.rs:609)
+        }
+    }
+    if (bad && g->status == OPAL_OK) { g->status = OPAL_EASSERT_INDEX; g->err = "deposit: index out of range (yee.rs:578-579)"; }
+    // serial reduction in chunk order (yee.rs:616-640)
+    for (size_t i = 0; i < size; i++) {
+        double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+        for (size_t k = 0; k < nchunks; k++) {
+            t0 += j[k][4 * i]; t1 += j[k][4 * i + 1]; t2 += j[k][4 * i + 2]; t3 += j[k][4 * i + 3];
+        }
+        Cell& c = g->cell[i];
+        c.j[0] += t0; c.j[1] += t1; c.j[2] += t2; c.rho += t3;
+    }
+}
+
+inline void overlay_ghost(Cell& a, const Cell& o) {   // yee.rs:97-104
+    a.rho += o.rho; a.j[0] += o.j[0]; a.j[1] += o.j[1]; a.j[2] += o.j[2];
+    std::memcpy(a.E, o.E, sizeof(a.E)); std::memcpy(a.B, o.B, sizeof(a.B));
+}
+inline void overlay(Cell& a, const Cell& o) {         // yee.rs:108-113
+    a.rho += o.rho; a.j[0] += o.j[0]; a.j[1] += o.j[1]; a.j[2] += o.j[2];
+}
+
+// yee.rs:351-496
+void synchronize(opal_ctx* g, double laser_y, double laser_z) {
+    const size_t len = g->cell.size();
+    const int G = OPAL_GHOST_SIZE;
+    Cell send_left[2 * OPAL_GHOST_SIZE], send_right[2 * OPAL_GHOST_SIZE];
+    std::memcpy(send_left, g->cell.data(), sizeof(send_left));
+    std::memcpy(send_right, g->cell.data() + len - 2 * G, sizeof(send_right));
+    Cell recv_left[2 * OPAL_GHOST_SIZE], recv_right[2 * OPAL_GHOST_SIZE];
+    bool have_left = false, have_right = false;
+    if (g->has_right()) {
+        if (g->self_neighbour()) { std::memcpy(recv_right, send_left, sizeof(send_left)); have_right = true; }
+        else if (g->halo_given[OPAL_RIGHT]) { std::memcpy(recv_right, g->halo_recv[OPAL_RIGHT], sizeof(recv_right)); have_right = true; }
+    }
+    if (g->has_left()) {
+        if (g->self_neighbour()) { std::memcpy(recv_left, send_right, sizeof(send_right)); have_left = true; }
+        else if (g->halo_given[OPAL_LEFT]) { std::memcpy(recv_left, g->halo_recv[OPAL_LEFT], sizeof(recv_left)); have_left = true; }
+    }
+    if ((g->has_left() && !have_left) || (g->has_right() && !have_right)) {
+        if (g->status == OPAL_OK) { g->status = OPAL_EINVAL; g->err = "synchronize: neighbour halo missing (yee.rs:413-419)"; }
+        return;
+    }
+    g->halo_given[0] = g->halo_given[1] = false;
+    Cell* cell = g->cell.data();
+    if (g->has_left()) {
+        for (int i = 0; i < G; i++) overlay_ghost(cell[i], recv_left[i]);
+        for (int i = 0; i < G; i++) overlay(cell[G + i], recv_left[G + i]);
+    }
+    if (g->has_right()) {
+        for (int i = 0; i < G; i++) overlay(cell[len - 2 * G + i], recv_right[i]);
+        for (int i = 0; i < G; i++) overlay_ghost(cell[len - G + i], recv_right[G + i]);
+    }
+    if (g->left_bdy == OPAL_BDY_LASER) {
+        size_t start = (size_t)(g->left_size - 2);
+        double r = SPEED_OF_LIGHT * g->dt / g->dx;
+        cell[start].E[1] += 2.0 * r * laser_y;
+        cell[start].E[2] += 2.0 * r * laser_z;
+    }
+    if (g->right_bdy == OPAL_BDY_ABSORBING) {
+        double xmin = cell[g->size + g->left_size].x, xmax = cell[g->size + g->left_size + g->right_size - 1].x;
+        double sigma_max = 10.0 / (double)g->right_size;
+        for (size_t i = len - (size_t)g->right_size + 1; i < len; i++) {
+            Cell& c = cell[i];
+            double sigma = sigma_max * (c.x - xmin) / (xmax - xmin);
+            for (int k = 0; k < 3; k++) c.E[k] = (1.0 - sigma) * c.E[k];
+            for (int k = 0; k < 3; k++) c.B[k] = (1.0 - sigma) * c.B[k];
+        }
+        for (size_t i = len - 2; i < len; i++)
+            for (int k = 0; k < 3; k++) { cell[i].E[k] = 0.0; cell[i].B[k] = 0.0; }
+    } else if (g->right_bdy == OPAL_BDY_CONDUCTING) {
+        size_t start = len - (size_t)g->right_size;
+        cell[start].E[0] = 0.0; cell[start].B[1] = 0.0; cell[start].B[2] = 0.0;
+        for (size_t i = 1; i < (size_t)g->right_size; i++) {
+            cell[start + i].E[0] = -cell[start - i].E[0];
+            cell[start + i].E[1] = cell[start + 1 - i].E[1];
+            cell[start + i].E[2] = cell[start + 1 - i].E[2];
+            cell[start + i].B[0] = cell[start + 1 - i].B[0];
+            cell[start + i].B[1] = -cell[start - i].B[1];
+            cell[start + i].B[2] = -cell[start - i].B[2];
+        }
+    }
+}
+
+void advance_B(opal_ctx* g, double dt) {   // yee.rs:839-848
+    Cell* cell = g->cell.data();
+    const size_t end = g->cell.size() - 1;
+    for (size_t i = 0; i < end; i++) {
+        cell[i].B[1] += dt * (cell[i + 1].E[2] - cell[i].E[2]) / g->dx;
+        cell[i].B[2] += dt * (cell[i].E[1] - cell[i + 1].E[1]) / g->dx;
+    }
+}
+void advance_E(opal_ctx* g, double dt) {   // yee.rs:852-867
+    Cell* cell = g->cell.data();
+    double kappa = 2.0 * SPEED_OF_LIGHT * dt / (SPEED_OF_LIGHT * dt + g->dx);
+    double sigma = 1.0 - kappa;
+    cell[0].E[0] = 0.0;
+    cell[0].E[1] = sigma * cell[0].E[1] - SPEED_OF_LIGHT * kappa * cell[0].B[2];
+    cell[0].E[2] = sigma * cell[0].E[2] + SPEED_OF_LIGHT * kappa * cell[0].B[1];
+    const size_t end = g->cell.size();
+    for (size_t i = 1; i < end; i++) {
+        cell[i].E[0] += -dt * cell[i].j[0] / VACUUM_PERMITTIVITY;
+        cell[i].E[1] += dt * SPEED_OF_LIGHT_SQD * (cell[i - 1].B[2] - cell[i].B[2]) / g->dx - dt * cell[i].j[1] / VACUUM_PERMITTIVITY;
+        cell[i].E[2] += dt * SPEED_OF_LIGHT_SQD * (cell[i].B[1] - cell[i - 1].B[1]) / g->dx - dt * cell[i].j[2] / VACUUM_PERMITTIVITY;
+    }
+}
+
+// electron.rs:208-251
+bool radiate(opal_ctx* g, Electron& e, Xoshiro& rng, double t, Photon* out, double* formation_length) {
+    if (!(e.tau < 0.0)) return false;
+    e.tau = rng.exp1();
+    double s3[3];
+    double r1 = rng.gen(), r2 = rng.gen(), r3 = rng.gen();
+    if (g->flags & OPAL_FLAG_NO_RADIATION_REACTION) qed_classical_sample(e.chi, e.gamma, r1, r2, r3, s3);
+    else qed_sample(e.chi, e.gamma, r1, r2, r3, s3);
+    double omega_mc2 = s3[0], theta = s3[1], cphi = s3[2];
+    Vec3 parallel = normalize(e.u);
+    Vec3 perp = orthogonal(parallel);
+    perp = rotate_around(perp, parallel, cphi);
+    Vec3 u = (g->flags & OPAL_FLAG_NO_BEAMING) ? omega_mc2 * parallel
+                                               : omega_mc2 * (std::cos(theta) * parallel + std::sin(theta) * perp);
+    *formation_length = 2.0 * (e.gamma * e.gamma) * theta * SPEED_OF_LIGHT * COMPTON_TIME / e.chi;
+    if (!(g->flags & OPAL_FLAG_NO_RADIATION_REACTION)) {
+        e.u = e.u - u;
+        double new_gamma = std::sqrt(1.0 + e.u * e.u);
+        e.chi = e.chi * new_gamma / e.gamma;
+        e.gamma = new_gamma;
+    }
+    Photon ph = photon_create(e.cell, e.x, u, e.weight, 0.0, 0.0);   // prev_x = x - 0/0 = NaN
+    ph.tau[0] = rng.exp1(); ph.tau[1] = rng.exp1(); ph.tau_abs = rng.exp1(); ph.tau_st = rng.exp1();
+    ph.birth_time = t;
+    *out = ph;
+    return true;
+}
+
+// particle/interactions.rs:45-107 -- one chunk per thread in the reference; here the legal
+// single-chunk instance (chunk 0 clones the rng with zero jumps; the master then long_jumps).
+void emit_radiation(opal_ctx* g, double t, const double* min_energy, const double* max_angle, const double* max_fl) {
+    finalize(g, g->electrons); finalize(g, g->photons);
+    Xoshiro rng = g->rng;
+    std::vector<Photon> emitted;
+    for (Electron& e : g->electrons.store) {
+        Photon ph; double fl;
+        if (!radiate(g, e, rng, t, &ph, &fl)) continue;
+        bool energy_ok = true, angle_ok = true, fl_ok = true;
+        if (min_energy) energy_ok = std::sqrt(norm_sqr(ph.k)) * ELECTRON_MASS_MEV >= *min_energy;
+        if (max_angle) {
+            Vec3 p = ph.k * ELECTRON_MASS_MEV;
+            double magnitude = std::sqrt(p.x * p.x + p.y * p.y + p.z * p.z);
+            double angle = std::acos(-p.x / magnitude);
+            angle_ok = angle <= *max_angle;
+        }
+        if (max_fl) fl_ok = fl < *max_fl;
+        if (energy_ok && angle_ok && fl_ok) emitted.push_back(ph);
+    }
+    if (g_chi_range_error) { g_chi_range_error = false; if (g->status == OPAL_OK) { g->status = OPAL_ECHI_RANGE; g->err = "sample: chi beyond table (photon_emission.rs:144)"; } }
+    g->rng.long_jump();
+    g->photons.store.insert(g->photons.store.end(), emitted.begin(), emitted.end());
+}
+
+template <class T> double kinetic(opal_ctx* g, Population<T>& pop) {
+    finalize(g, pop);
+    double s = 0.0;
+    for (const T& p : pop.store) s += kinetic_energy_of(p);
+    return s;
+}
+
+#define CHECK_CTX(c) do { if (!(c)) return OPAL_EINVAL; if ((c)->status != OPAL_OK) return (opal_status)(c)->status; } while (0)
+
+template <class T> opal_status take(opal_ctx* g, Population<T>& pop, int side, int64_t cap, int64_t* n, opal_migrant* out) {
+    if (!pop.pending) { *n = 0; return OPAL_OK; }
+    size_t lo, hi;
+    if (side == OPAL_LEFT) { lo = 0; hi = pop.gone_left; if (!g->has_left()) hi = lo; }
+    else { lo = pop.num - pop.gone_right; hi = pop.num; if (!g->has_right()) hi = lo; }
+    *n = (int64_t)(hi - lo);
+    if (*n > cap) return OPAL_ECAPACITY;
+    for (size_t i = lo; i < hi; i++) out[i - lo] = to_wire(pop.store[i]);
+    return OPAL_OK;
+}
+
+}  // namespace
+
+// =============================== C ABI ======================================================
+extern "C" {
+
+opal_status opal_ref_set_threads(int n) {
+    g_threads = n < 1 ? 1 : n;
+    return OPAL_OK;
+}
+int opal_ref_max_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+opal_status opal_ref_create(opal_ctx** out, int device, int64_t nx, double xmin, double dx, double dt, int left, int right,
+                            int rank, int nranks, uint64_t seed, uint32_t flags) {
+    (void)device;
+    if (!out || nx < 1 || nranks < 1 || rank < 0 || rank >= nranks) return OPAL_EINVAL;
+    opal_ctx* g = new opal_ctx();
+    g->rank = rank; g->nranks = nranks; g->dx = dx; g->dt = dt; g->flags = flags; g->size = nx;
+    // yee.rs:278-292
+    if (rank == 0 && left == OPAL_BDY_LASER) { g->left_bdy = OPAL_BDY_LASER; g->left_size = OPAL_LASER_BDY_SIZE; }
+    else { g->left_bdy = OPAL_BDY_INTERNAL; g->left_size = OPAL_GHOST_SIZE; }
+    if (rank == nranks - 1 && right == OPAL_BDY_ABSORBING) { g->right_bdy = OPAL_BDY_ABSORBING; g->right_size = OPAL_ABSORBING_BDY_SIZE; }
+    else if (rank == nranks - 1 && right == OPAL_BDY_CONDUCTING) { g->right_bdy = OPAL_BDY_CONDUCTING; g->right_size = OPAL_CONDUCTING_BDY_SIZE; }
+    else { g->right_bdy = OPAL_BDY_INTERNAL; g->right_size = OPAL_GHOST_SIZE; }
+    size_t len = (size_t)(nx + g->left_size + g->right_size);
+    g->cell.resize(len);
+    for (size_t c = 0; c < len; c++) {
+        Cell& ce = g->cell[c];
+        std::memset(&ce, 0, sizeof(ce));
+        ce.x = xmin + ((double)c - (double)g->left_size) * dx;   // yee.rs:296 (offset folded into xmin)
+    }
+    g->rng.seed_from_u64(seed);   // main.rs:53 seeds with the rank id
+    *out = g;
+    return OPAL_OK;
+}
+opal_status opal_ref_destroy(opal_ctx* g) { delete g; return OPAL_OK; }
+const char* opal_ref_last_error(opal_ctx* g) { return g ? g->err.c_str() : "null context"; }
+opal_status opal_ref_grid_shape(opal_ctx* g, int64_t* total, int64_t* l, int64_t* r) {
+    if (!g) return OPAL_EINVAL;
+    if (total) *total = (int64_t)g->cell.size();
+    if (l) *l = g->left_size;
+    if (r) *r = g->right_size;
+    return OPAL_OK;
+}
+
+opal_status opal_ref_particles_upload(opal_ctx* g, int species, int64_t n, const int64_t* cell, const double* x,
+                                      const double* ux, const double* uy, const double* uz, const double* w, const double* tau) {
+    CHECK_CTX(g);
+    if (n < 0 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
+    auto by_cell = [](const auto& a, const auto& b) { return a.cell < b.cell; };
+    if (species == OPAL_ELECTRON) {
+        auto& s = g->electrons; s.pending = false; s.store.resize((size_t)n);
+        for (int64_t i = 0; i < n; i++) {
+            s.store[i] = electron_create(cell[i], x[i], Vec3{ux[i], uy[i], uz[i]}, w[i], g->dx, g->dt);
+            if (tau) s.store[i].tau = tau[i];
+        }
+        std::stable_sort(s.store.begin(), s.store.end(), by_cell);
+    } else if (species == OPAL_ION) {
+        auto& s = g->ions; s.pending = false; s.store.resize((size_t)n);
+        for (int64_t i = 0; i < n; i++) {
+            s.store[i] = ion_create(cell[i], x[i], Vec3{ux[i], uy[i], uz[i]}, w[i], g->dx, g->dt);
+            s.store[i].Z_star = g->ion_spec.Z_star; s.store[i].Z = g->ion_spec.Z_star; s.store[i].A = g->ion_spec.A;
+        }
+        std::stable_sort(s.store.begin(), s.store.end(), by_cell);
+    } else if (species == OPAL_PHOTON) {
+        auto& s = g->photons; s.pending = false; s.store.resize((size_t)n);
+        for (int64_t i = 0; i < n; i++) {
+            s.store[i] = photon_create(cell[i], x[i], Vec3{ux[i], uy[i], uz[i]}, w[i], g->dx, g->dt);
+            if (tau) s.store[i].tau[0] = s.store[i].tau[1] = s.store[i].tau_abs = s.store[i].tau_st = tau[i];
+        }
+        std::stable_sort(s.store.begin(), s.store.end(), by_cell);
+    } else return OPAL_EINVAL;
+    return OPAL_OK;
+}
+opal_status opal_ref_set_ion(opal_ctx* g, double z_star, double a) {
+    CHECK_CTX(g);
+    g->ion_spec.Z_star = z_star; g->ion_spec.A = a;
+    for (auto& p : g->ions.store) { p.Z_star = z_star; p.Z = z_star; p.A = a; }   // main.rs:145-147
+    return OPAL_OK;
+}
+opal_status opal_ref_particles_count(opal_ctx* g, int species, int64_t* n) {
+    CHECK_CTX(g);
+    if (species == OPAL_ELECTRON) { finalize(g, g->electrons); *n = (int64_t)g->electrons.store.size(); }
+    else if (species == OPAL_ION) { finalize(g, g->ions); *n = (int64_t)g->ions.store.size(); }
+    else if (species == OPAL_PHOTON) { finalize(g, g->photons); *n = (int64_t)g->photons.store.size(); }
+    else return OPAL_EINVAL;
+    return OPAL_OK;
+}
+opal_status opal_ref_particles_download(opal_ctx* g, int species, int64_t cap, int64_t* cell, double* x, double* prev_x,
+                                        double* ux, double* uy, double* uz, double* w, double* gamma, double* chi,
+                                        double* tau, double* work, double* y, double* z, double* birth) {
+    CHECK_CTX(g);
+#define PUT(p, v) do { if (p) p[i] = (v); } while (0)
+    if (species == OPAL_ELECTRON) {
+        finalize(g, g->electrons);
+        auto& s = g->electrons.store; if ((int64_t)s.size() > cap) return OPAL_ECAPACITY;
+        for (size_t i = 0; i < s.size(); i++) {
+            const Electron& e = s[i];
+            PUT(cell, e.cell); PUT(x, e.x); PUT(prev_x, e.prev_x); PUT(ux, e.u.x); PUT(uy, e.u.y); PUT(uz, e.u.z);
+            PUT(w, e.weight); PUT(gamma, e.gamma); PUT(chi, e.chi); PUT(tau, e.tau); PUT(work, e.work);
+            PUT(y, e.y); PUT(z, e.z); PUT(birth, 0.0);
+        }
+    } else if (species == OPAL_ION) {
+        finalize(g, g->ions);
+        auto& s = g->ions.store; if ((int64_t)s.size() > cap) return OPAL_ECAPACITY;
+        for (size_t i = 0; i < s.size(); i++) {
+            const Ion& e = s[i];
+            PUT(cell, e.cell); PUT(x, e.x); PUT(prev_x, e.prev_x); PUT(ux, e.u.x); PUT(uy, e.u.y); PUT(uz, e.u.z);
+            PUT(w, e.weight); PUT(gamma, 1.0 + e.gamma_m1); PUT(chi, 0.0); PUT(tau, INF); PUT(work, e.work);
+            PUT(y, 0.0); PUT(z, 0.0); PUT(birth, 0.0);
+        }
+    } else if (species == OPAL_PHOTON) {
+        finalize(g, g->photons);
+        auto& s = g->photons.store; if ((int64_t)s.size() > cap) return OPAL_ECAPACITY;
+        for (size_t i = 0; i < s.size(); i++) {
+            const Photon& e = s[i];
+            PUT(cell, e.cell); PUT(x, e.x); PUT(prev_x, e.prev_x); PUT(ux, e.k.x); PUT(uy, e.k.y); PUT(uz, e.k.z);
+            PUT(w, e.weight); PUT(gamma, std::sqrt(norm_sqr(e.k))); PUT(chi, e.chi); PUT(tau, e.tau[0]); PUT(work, 0.0);
+            PUT(y, e.y); PUT(z, e.z); PUT(birth, e.birth_time);
+        }
+    } else return OPAL_EINVAL;
+#undef PUT
+    return OPAL_OK;
+}
+opal_status opal_ref_fields_upload(opal_ctx* g, const double* cells11) {
+    CHECK_CTX(g);
+    std::memcpy(g->cell.data(), cells11, g->cell.size() * sizeof(Cell));
+    return OPAL_OK;
+}
+opal_status opal_ref_fields_download(opal_ctx* g, double* cells11) {
+    CHECK_CTX(g);
+    std::memcpy(cells11, g->cell.data(), g->cell.size() * sizeof(Cell));
+    return OPAL_OK;
+}
+
+opal_status opal_ref_advance(opal_ctx* g, int species) {
+    CHECK_CTX(g);
+    if (species == OPAL_ELECTRON) advance(g, g->electrons);
+    else if (species == OPAL_ION) advance(g, g->ions);
+    else if (species == OPAL_PHOTON) { if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons); }
+    else return OPAL_EINVAL;
+    return (opal_status)g->status;
+}
+opal_status opal_ref_last_leavers(opal_ctx* g, int species, int64_t* l, int64_t* r) {
+    if (!g) return OPAL_EINVAL;
+    if (species == OPAL_ELECTRON) { *l = g->electrons.last_left; *r = g->electrons.last_right; }
+    else if (species == OPAL_ION) { *l = g->ions.last_left; *r = g->ions.last_right; }
+    else if (species == OPAL_PHOTON) { *l = g->photons.last_left; *r = g->photons.last_right; }
+    else return OPAL_EINVAL;
+    return OPAL_OK;
+}
+opal_status opal_ref_migrants_take(opal_ctx* g, int species, int side, int64_t cap, int64_t* n, opal_migrant* out) {
+    CHECK_CTX(g);
+    if (species == OPAL_ELECTRON) return take(g, g->electrons, side, cap, n, out);
+    if (species == OPAL_ION) return take(g, g->ions, side, cap, n, out);
+    if (species == OPAL_PHOTON) return take(g, g->photons, side, cap, n, out);
+    return OPAL_EINVAL;
+}
+opal_status opal_ref_migrants_give(opal_ctx* g, int species, int side, int64_t n, const opal_migrant* in) {
+    CHECK_CTX(g);
+    if (species == OPAL_ELECTRON) {
+        auto& pop = g->electrons; if (!pop.pending) return OPAL_EINVAL;
+        auto& v = side == OPAL_LEFT ? pop.recv_left : pop.recv_right;
+        for (int64_t i = 0; i < n; i++) { Electron e; from_wire(in[i], e); v.push_back(e); }
+    } else if (species == OPAL_ION) {
+        auto& pop = g->ions; if (!pop.pending) return OPAL_EINVAL;
+        auto& v = side == OPAL_LEFT ? pop.recv_left : pop.recv_right;
+        for (int64_t i = 0; i < n; i++) { Ion e; from_wire(in[i], e, g->ion_spec); v.push_back(e); }
+    } else if (species == OPAL_PHOTON) {
+        auto& pop = g->photons; if (!pop.pending) return OPAL_EINVAL;
+        auto& v = side == OPAL_LEFT ? pop.recv_left : pop.recv_right;
+        for (int64_t i = 0; i < n; i++) { Photon e; from_wire(in[i], e); v.push_back(e); }
+    } else return OPAL_EINVAL;
+    return OPAL_OK;
+}
+
+opal_status opal_ref_emit_radiation(opal_ctx* g, double t, const double* min_energy_mev, const double* max_angle, const double* max_fl) {
+    CHECK_CTX(g);
+    emit_radiation(g, t, min_energy_mev, max_angle, max_fl);
+    return (opal_status)g->status;
+}
+opal_status opal_ref_clear(opal_ctx* g) {   // yee.rs:543-549
+    CHECK_CTX(g);
+    for (Cell& c : g->cell) { c.rho = 0.0; c.j[0] = c.j[1] = c.j[2] = 0.0; }
+    return OPAL_OK;
+}
+opal_status opal_ref_deposit(opal_ctx* g, int species) {
+    CHECK_CTX(g);
+    if (species == OPAL_ELECTRON) deposit(g, g->electrons);
+    else if (species == OPAL_ION) deposit(g, g->ions);
+    else if (species == OPAL_PHOTON) deposit(g, g->photons);
+    else return OPAL_EINVAL;
+    return (opal_status)g->status;
+}
+opal_status opal_ref_halo_take(opal_ctx* g, int side, double* out) {
+    CHECK_CTX(g);
+    const size_t len = g->cell.size();
+    const Cell* src = side == OPAL_LEFT ? g->cell.data() : g->cell.data() + len - OPAL_HALO_CELLS;
+    std::memcpy(out, src, OPAL_HALO_CELLS * sizeof(Cell));
+    return OPAL_OK;
+}
+opal_status opal_ref_halo_give(opal_ctx* g, int side, const double* in) {
+    CHECK_CTX(g);
+    if (side != OPAL_LEFT && side != OPAL_RIGHT) return OPAL_EINVAL;
+    std::memcpy(g->halo_recv[side], in, OPAL_HALO_CELLS * sizeof(Cell));
+    g->halo_given[side] = true;
+    return OPAL_OK;
+}
+opal_status opal_ref_synchronize(opal_ctx* g, double t, double laser_y, double laser_z) {
+    CHECK_CTX(g);
+    (void)t;
+    synchronize(g, laser_y, laser_z);
+    return (opal_status)g->status;
+}
+opal_status opal_ref_laser_x(opal_ctx* g, double* x) {
+    if (!g) return OPAL_EINVAL;
+    *x = g->cell[(size_t)(g->left_size - 2)].x;
+    return OPAL_OK;
+}
+opal_status opal_ref_field_advance(opal_ctx* g) {   // yee.rs:345-349
+    CHECK_CTX(g);
+    advance_B(g, 0.5 * g->dt);
+    advance_E(g, g->dt);
+    advance_B(g, 0.5 * g->dt);
+    return OPAL_OK;
+}
+
+opal_status opal_ref_run_steps(opal_ctx* g, int64_t nsteps, double t0, const double* laser_y, const double* laser_z,
+                               int current_deposition, int photon_emission, const double* f3) {
+    CHECK_CTX(g);
+    if (!g->self_neighbour() && (g->has_left() || g->has_right())) return OPAL_EINVAL;   // needs host-staged exchange
+    double t = t0;
+    for (int64_t s = 0; s < nsteps; s++) {   // main.rs:238-267
+        advance(g, g->electrons);
+        advance(g, g->ions);
+        if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons);
+        if (photon_emission) {
+            const double* a = (f3 && !std::isnan(f3[0])) ? &f3[0] : nullptr;
+            const double* b = (f3 && !std::isnan(f3[1])) ? &f3[1] : nullptr;
+            const double* c = (f3 && !std::isnan(f3[2])) ? &f3[2] : nullptr;
+            emit_radiation(g, t, a, b, c);
+        }
+        if (current_deposition) {
+            opal_ref_clear(g);
+            deposit(g, g->electrons);
+            deposit(g, g->ions);
+        }
+        synchronize(g, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0);
+        advance_B(g, 0.5 * g->dt); advance_E(g, g->dt); advance_B(g, 0.5 * g->dt);
+        t += g->dt;
+        if (g->status != OPAL_OK) break;
+    }
+    return (opal_status)g->status;
+}
+
+opal_status opal_ref_energy(opal_ctx* g, double* em, double* ke_e, double* ke_i, double* ke_ph) {
+    CHECK_CTX(g);
+    if (em) {   // yee.rs:787-799
+        double e2 = 0.0, b2 = 0.0;
+        for (size_t i = (size_t)g->left_size; i < g->cell.size() - (size_t)g->right_size; i++) {
+            const Cell& c = g->cell[i];
+            e2 = e2 + c.E[0] * c.E[0] + c.E[1] * c.E[1] + c.E[2] * c.E[2];
+            b2 = b2 + c.B[0] * c.B[0] + c.B[1] * c.B[1] + c.B[2] * c.B[2];
+        }
+        *em = 0.5 * (VACUUM_PERMITTIVITY * e2 + b2 / VACUUM_PERMEABILITY) * g->dx;
+    }
+    if (ke_e) *ke_e = kinetic(g, g->electrons);
+    if (ke_i) *ke_i = kinetic(g, g->ions);
+    if (ke_ph) *ke_ph = kinetic(g, g->photons);
+    return OPAL_OK;
+}
+
+opal_status opal_ref_comm_unique_id(void*) { return OPAL_ENCCL; }
+opal_status opal_ref_comm_init(opal_ctx*, const void*) { return OPAL_ENCCL; }
+opal_status opal_ref_stream(opal_ctx*, void** s) { if (s) *s = nullptr; return OPAL_OK; }
+opal_status opal_ref_launch_count(opal_ctx*, int64_t* n) { if (n) *n = 0; return OPAL_OK; }
+opal_status opal_ref_particles_generate(opal_ctx*, int, int64_t, double, const double*, const double*, int, int64_t, uint64_t) {
+    return OPAL_EINVAL;   // the oracle is fed the arrays the GPU generator produced (download -> upload)
+}
+
+opal_status opal_ref_qed_rate(int64_t n, const double* chi, const double* gamma, double* out) {
+    for (int64_t i = 0; i < n; i++) out[i] = qed_rate(chi[i], gamma[i]);
+    return OPAL_OK;
+}
+opal_status opal_ref_qed_sample(int64_t n, const double* chi, const double* gamma, const double* r1, const double* r2,
+                                const double* r3, int classical, double* out3) {
+    for (int64_t i = 0; i < n; i++) {
+        if (classical) qed_classical_sample(chi[i], gamma[i], r1[i], r2[i], r3[i], out3 + 3 * i);
+        else qed_sample(chi[i], gamma[i], r1[i], r2[i], r3[i], out3 + 3 * i);
+    }
+    bool bad = g_chi_range_error; g_chi_range_error = false;
+    return bad ? OPAL_ECHI_RANGE : OPAL_OK;
+}
+opal_status opal_ref_fields_at(opal_ctx* g, int64_t n, const int64_t* cell, const double* xi, double* out6) {
+    CHECK_CTX(g);
+    for (int64_t i = 0; i < n; i++)
+        if (!fields_at(g, cell[i], xi[i], out6 + 6 * i, out6 + 6 * i + 3)) return OPAL_EASSERT_INDEX;
+    return OPAL_OK;
+}
+
+// ---- oracle-only helpers for the known-answer tests ------------------------------------------
+double opal_ref_weight(double xi) { return weight(xi); }
+double opal_ref_flux(double xi, double xf) { return flux(xi, xf); }
+int opal_ref_pwmci_invert(double f, const double* table2, int64_t len, double* x, int* nevals) {
+    return pwmci_invert(f, reinterpret_cast<Table>(table2), (size_t)len, x, nevals) ? 1 : 0;
+}
+int opal_ref_pwmci_evaluate(double x, const double* table2, int64_t len, double* f) {
+    return pwmci_evaluate(x, reinterpret_cast<Table>(table2), (size_t)len, f) ? 1 : 0;
+}
+void opal_ref_vec3_orthogonal(const double a[3], double out[3]) {
+    Vec3 r = orthogonal(Vec3{a[0], a[1], a[2]}); out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+void opal_ref_vec3_rotate_around(const double v[3], const double axis[3], double theta, double out[3]) {
+    Vec3 r = rotate_around(Vec3{v[0], v[1], v[2]}, Vec3{axis[0], axis[1], axis[2]}, theta); out[0] = r.x; out[1] = r.y; out[2] = r.z;
+}
+// Electron::create + n x Electron::push in uniform fields (electron.rs:401-436).
+// out = {gamma, ux, uy, uz, x, cell, work, chi, tau}
+void opal_ref_electron_push_uniform(const double u0[3], const double E[3], const double B[3], double dx, double dt, int64_t n, double* out9) {
+    Electron e = electron_create(0, 0.0, Vec3{u0[0], u0[1], u0[2]}, 1.0, dx, dt);
+    PushCtx pc{0, false};
+    for (int64_t i = 0; i < n; i++) push(e, E, B, dx, dt, pc);
+    out9[0] = e.gamma; out9[1] = e.u.x; out9[2] = e.u.y; out9[3] = e.u.z; out9[4] = e.x; out9[5] = (double)e.cell;
+    out9[6] = e.work; out9[7] = e.chi; out9[8] = e.tau;
+}
+void opal_ref_ion_push_uniform(const double u0[3], double z_star, double a, const double E[3], const double B[3], double dx, double dt, int64_t n, double* out6) {
+    Ion p = ion_create(0, 0.0, Vec3{u0[0], u0[1], u0[2]}, 1.0, dx, dt);
+    p.Z_star = z_star; p.Z = z_star; p.A = a;
+    PushCtx pc{0, false};
+    for (int64_t i = 0; i < n; i++) push(p, E, B, dx, dt, pc);
+    out6[0] = 1.0 + p.gamma_m1; out6[1] = p.u.x; out6[2] = p.u.y; out6[3] = p.u.z; out6[4] = p.x; out6[5] = (double)p.cell;
+}
+uint64_t opal_ref_table_checksum(void) {
+    uint64_t h = 0xcbf29ce484222325ULL;
+    const unsigned char* p = reinterpret_cast<const unsigned char*>(QED_TABLES);
+    for (size_t i = 0; i < sizeof(QED_TABLES); i++) h = (h ^ p[i]) * 0x100000001b3ULL;
+    return h;
+}
+uint64_t opal_ref_table_checksum_expected(void) { return OPAL_QED_TABLE_FNV1A; }
+// xoshiro256** stream for tests (seed_from_u64 -> n x gen::<f64>())
+void opal_ref_rng_stream(uint64_t seed, int64_t n, double* out) {
+    Xoshiro r; r.seed_from_u64(seed);
+    for (int64_t i = 0; i < n; i++) out[i] = r.gen();
+}
+
+}  // extern "C"
