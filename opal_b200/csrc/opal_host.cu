@@ -1,0 +1,1011 @@
+// opal_host.cu -- context, memory layout and the C ABI of include/opal_b200.h.
+//
+// One opal_ctx = one x-slab (one reference MPI rank) on one GPU.  Everything between
+// main.rs:240 and main.rs:266 stays on the device; the host contributes the two laser scalars
+// per step and reads back a 44-byte status block.  There is no CPU compute path in this file.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "opal_types.h"
+
+#define OPAL_QED_TABLE_DATA
+static const double H_QED_TABLES[73 * 64] = {
+#include "qed_tables.inc"
+};
+#undef OPAL_QED_TABLE_DATA
+
+using namespace opal;
+
+namespace {
+
+constexpr double C_LIGHT = 2.997925e8;   // constants.rs:4
+
+// ---- NCCL, resolved at run time (torch's bundled libnccl.so.2 is already in the process) -----
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+struct NcclApi {
+    void* h = nullptr;
+    int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    bool load() {
+        if (h) return true;
+        const char* names[] = {"libnccl.so.2", "libnccl.so"};
+        for (const char* n : names) { h = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+        if (!h) return false;
+#define SYM(f) *(void**)(&f) = dlsym(h, "nccl" #f); if (!f) return false
+        SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(Send); SYM(Recv); SYM(GroupStart); SYM(GroupEnd);
+#undef SYM
+        return true;
+    }
+} g_nccl;
+constexpr int NCCL_CHAR = 0;   // ncclInt8 / ncclChar
+
+struct Buckets {
+    bool allocated = false;
+    bool full = false;
+    long long slots = 0;
+    std::vector<long long> h_start;   // ncell + 1
+    long long* d_start = nullptr;
+    int* d_count = nullptr;
+    double* d_f[NF_FULL] = {nullptr};
+    long long n_hint = 0;             // particle count at the last layout (sizing of the mover buffer)
+};
+
+struct Photons {
+    int cap = 0;
+    int* d_n = nullptr;
+    int* d_cell = nullptr;
+    double* d_f[NF_PHOTON] = {nullptr};
+};
+
+}  // namespace
+
+struct opal_ctx {
+    int device = 0, rank = 0, nranks = 1;
+    uint32_t flags = 0;
+    uint64_t seed = 0;
+    bool full = true;
+    cudaStream_t stream = nullptr;
+    KernelTable k;
+    GridDev g;              // current E/B buffers
+    double* eb_alt[6] = {nullptr};   // the other half of the E/B ping-pong
+    double* grid_block = nullptr;    // one allocation for all grid arrays
+    Buckets bk[2];          // electrons, ions
+    double z_star = 1.0, mass_number = 1.0;
+    Photons ph[2];          // ping-pong
+    int ph_cur = 0;
+    // exchange / mover buffers
+    opal_migrant* d_movers = nullptr; int mover_seg_cap = 0;
+    opal_migrant* d_overflow = nullptr;
+    opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
+    opal_migrant* d_in[2] = {nullptr, nullptr};
+    int out_cap = 0;
+    int64_t pending_in[3][2] = {{0, 0}, {0, 0}, {0, 0}};   // host-staged migrants given, per species/side (for bookkeeping)
+    double* d_halo_send = nullptr;   // [2][8][11]
+    double* d_halo_recv = nullptr;   // [2][8][11]
+    bool halo_given[2] = {false, false};
+    StatusDev* d_status = nullptr;   // followed by OPAL_MOVER_SEGMENTS ints
+    StatusDev* h_status = nullptr;   // pinned
+    double* d_energy = nullptr;      // 4 doubles
+    double* h_energy = nullptr;      // pinned
+    int* d_tmp_int = nullptr;
+    double* d_qed_tables = nullptr;
+    int64_t last_gone[3][2] = {{0, 0}, {0, 0}, {0, 0}};
+    uint64_t emit_calls = 0;
+    int64_t launches = 0;
+    ncclComm_t comm = nullptr;
+    int status = OPAL_OK;
+    std::string err;
+    double slack = 1.25; int pad = 64;
+
+    bool has_left() const { return g.left_bdy == OPAL_BDY_INTERNAL; }
+    bool has_right() const { return g.right_bdy == OPAL_BDY_INTERNAL; }
+    bool self_nbr() const { return nranks == 1; }
+    int left_rank() const { return (rank - 1 + nranks) % nranks; }    // yee.rs:309
+    int right_rank() const { return (rank + 1) % nranks; }            // yee.rs:310
+};
+
+namespace {
+
+bool fail(opal_ctx* c, int st, const std::string& msg) {
+    if (c && c->status == OPAL_OK) { c->status = st; c->err = msg; }
+    return false;
+}
+#define CU(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(c, OPAL_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); return (opal_status)c->status; } } while (0)
+#define CUB(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { fail(c, OPAL_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); return false; } } while (0)
+#define CHECK_CTX(c) do { if (!(c)) return OPAL_EINVAL; if ((c)->status != OPAL_OK) return (opal_status)(c)->status; cudaSetDevice((c)->device); } while (0)
+
+double env_double(const char* name, double dflt) { const char* v = getenv(name); return v ? atof(v) : dflt; }
+long long env_ll(const char* name, long long dflt) { const char* v = getenv(name); return v ? atoll(v) : dflt; }
+
+BucketDev bdev(opal_ctx* c, int sp) {
+    BucketDev b;
+    Buckets& B = c->bk[sp];
+    b.ncell = c->g.nx; b.start = B.d_start; b.count = B.d_count;
+    for (int k = 0; k < NF_FULL; k++) b.f[k] = B.d_f[k];
+    b.z_star = c->z_star; b.mass_number = c->mass_number;
+    return b;
+}
+PhotonDev pdev(opal_ctx* c, int which) {
+    PhotonDev p;
+    Photons& P = c->ph[which];
+    p.cap = P.cap; p.n = P.d_n; p.cell = P.d_cell;
+    for (int k = 0; k < NF_PHOTON; k++) p.f[k] = P.d_f[k];
+    return p;
+}
+StepParams sparams(opal_ctx* c, int species) {
+    StepParams sp;
+    sp.flags = c->flags; sp.species = species;
+    sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
+    sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
+    sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap;
+    return sp;
+}
+
+void free_buckets(Buckets& B) {
+    if (B.d_start) cudaFree(B.d_start);
+    if (B.d_count) cudaFree(B.d_count);
+    for (int k = 0; k < NF_FULL; k++) if (B.d_f[k]) { cudaFree(B.d_f[k]); B.d_f[k] = nullptr; }
+    B.d_start = nullptr; B.d_count = nullptr; B.allocated = false; B.slots = 0;
+}
+
+// capacity policy: demand * slack + pad, rounded up to a multiple of 32 slots
+long long bucket_cap(opal_ctx* c, long long demand) {
+    long long cap = (long long)std::ceil((double)demand * c->slack) + c->pad;
+    return (cap + 31) / 32 * 32;
+}
+
+bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand, bool full) {
+    const int ncell = c->g.nx;
+    B.h_start.assign(ncell + 1, 0);
+    for (int i = 0; i < ncell; i++) B.h_start[i + 1] = B.h_start[i] + bucket_cap(c, demand[i]);
+    B.slots = B.h_start[ncell];
+    B.full = full;
+    CUB(cudaMalloc(&B.d_start, (size_t)(ncell + 1) * sizeof(long long)));
+    CUB(cudaMalloc(&B.d_count, (size_t)ncell * sizeof(int)));
+    CUB(cudaMemcpyAsync(B.d_start, B.h_start.data(), (size_t)(ncell + 1) * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+    CUB(cudaMemsetAsync(B.d_count, 0, (size_t)ncell * sizeof(int), c->stream));
+    const int nf = full ? NF_FULL : NF_LEAN;
+    for (int k = 0; k < nf; k++) CUB(cudaMalloc(&B.d_f[k], (size_t)std::max<long long>(B.slots, 1) * sizeof(double)));
+    CUB(cudaStreamSynchronize(c->stream));
+    B.allocated = true;
+    return true;
+}
+
+bool ensure_movers(opal_ctx* c, long long n_particles) {
+    const double frac = env_double("OPAL_MOVER_FRACTION", n_particles <= 4000000 ? 1.0 : 0.05);
+    long long seg_cap = (long long)std::ceil(2.0 * frac * (double)n_particles / OPAL_MOVER_SEGMENTS);
+    if (seg_cap < 1024) seg_cap = 1024;
+    if (seg_cap <= c->mover_seg_cap) return true;
+    if (c->d_movers) cudaFree(c->d_movers);
+    if (c->d_overflow) cudaFree(c->d_overflow);
+    c->d_movers = nullptr; c->d_overflow = nullptr;
+    CUB(cudaMalloc(&c->d_movers, (size_t)seg_cap * OPAL_MOVER_SEGMENTS * sizeof(opal_migrant)));
+    CUB(cudaMalloc(&c->d_overflow, (size_t)seg_cap * sizeof(opal_migrant)));
+    c->mover_seg_cap = (int)seg_cap;
+    return true;
+}
+
+bool ensure_photons(opal_ctx* c, long long need) {
+    if (need <= c->ph[0].cap) return true;
+    long long cap = std::max<long long>(need * 2, 1 << 16);
+    for (int w = 0; w < 2; w++) {
+        Photons old = c->ph[w];
+        Photons& P = c->ph[w];
+        P = Photons();
+        P.cap = (int)cap;
+        CUB(cudaMalloc(&P.d_n, sizeof(int)));
+        CUB(cudaMemsetAsync(P.d_n, 0, sizeof(int), c->stream));
+        CUB(cudaMalloc(&P.d_cell, (size_t)cap * sizeof(int)));
+        for (int k = 0; k < NF_PHOTON; k++) CUB(cudaMalloc(&P.d_f[k], (size_t)cap * sizeof(double)));
+        if (old.cap > 0) {
+            if (w == c->ph_cur) {
+                CUB(cudaMemcpyAsync(P.d_n, old.d_n, sizeof(int), cudaMemcpyDeviceToDevice, c->stream));
+                CUB(cudaMemcpyAsync(P.d_cell, old.d_cell, (size_t)old.cap * sizeof(int), cudaMemcpyDeviceToDevice, c->stream));
+                for (int k = 0; k < NF_PHOTON; k++)
+                    CUB(cudaMemcpyAsync(P.d_f[k], old.d_f[k], (size_t)old.cap * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+            }
+            CUB(cudaStreamSynchronize(c->stream));
+            cudaFree(old.d_n); cudaFree(old.d_cell);
+            for (int k = 0; k < NF_PHOTON; k++) cudaFree(old.d_f[k]);
+        }
+    }
+    return true;
+}
+
+bool photon_count(opal_ctx* c, int* n) {
+    *n = 0;
+    if (c->ph[0].cap == 0) return true;
+    CUB(cudaMemcpyAsync(n, c->ph[c->ph_cur].d_n, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    return true;
+}
+
+bool reset_status(opal_ctx* c, bool keep_err) {
+    // zero the counters (and the per-segment mover counters); the sticky error word survives
+    if (keep_err) {
+        CUB(cudaMemsetAsync(c->d_status, 0, offsetof(StatusDev, err), c->stream));
+        CUB(cudaMemsetAsync((char*)c->d_status + offsetof(StatusDev, n_new_photons), 0,
+                            sizeof(StatusDev) - offsetof(StatusDev, n_new_photons) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
+    } else {
+        CUB(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
+    }
+    return true;
+}
+
+// copy the status block to the host, translate sticky device-side assertion bits
+bool fetch_status(opal_ctx* c) {
+    CUB(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev), cudaMemcpyDeviceToHost, c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    const unsigned e = c->h_status->err;
+    if (e & ERR_CFL) return fail(c, OPAL_EASSERT_CFL, "push: assert!(dxi < 1.0) failed (electron.rs:313 / ion.rs:199 / photon.rs:164)");
+    if (e & ERR_INDEX) return fail(c, OPAL_EASSERT_INDEX, "cell index out of range (yee.rs:501-502)");
+    if (e & ERR_CHI) return fail(c, OPAL_ECHI_RANGE, "sample: chi beyond the tabulated range (photon_emission.rs:144)");
+    if (e & ERR_CAPACITY) return fail(c, OPAL_ECAPACITY, "mover/exchange/photon buffer overflow (raise OPAL_MOVER_FRACTION / OPAL_EXCHANGE_CAP)");
+    return true;
+}
+
+// Re-lay the buckets of species `sp` out for the demand recorded in count[] (which includes the
+// movers parked in d_overflow), then scatter the parked movers.
+bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
+    Buckets& B = c->bk[sp];
+    const int ncell = c->g.nx;
+    std::vector<int> cnt(ncell);
+    CUB(cudaMemcpyAsync(cnt.data(), B.d_count, (size_t)ncell * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    std::vector<long long> demand(ncell);
+    long long total = 0;
+    for (int i = 0; i < ncell; i++) { demand[i] = cnt[i]; total += cnt[i]; }
+    Buckets old = B;
+    B = Buckets();
+    if (!alloc_buckets(c, B, demand, old.full)) return false;
+    B.n_hint = total;
+    BucketDev src; src.ncell = ncell; src.start = old.d_start; src.count = old.d_count;
+    for (int k = 0; k < NF_FULL; k++) src.f[k] = old.d_f[k];
+    src.z_star = c->z_star; src.mass_number = c->mass_number;
+    c->k.copy_buckets(c->stream, src, bdev(c, sp), old.full); c->launches++;
+    // parked movers: their cells are final
+    const int n_parked = c->h_status->n_overflow;
+    CUB(cudaMemcpyAsync(c->d_tmp_int, &c->d_status->n_overflow, sizeof(int), cudaMemcpyDeviceToDevice, c->stream));
+    CUB(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
+    StepParams sp_ = sparams(c, sp);
+    sp_.route_left = sp_.route_right = 0;
+    c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, old.full, deposit_parked, c->d_overflow, c->d_tmp_int, c->mover_seg_cap, 0, nullptr,
+                 nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
+    (void)n_parked;
+    CUB(cudaStreamSynchronize(c->stream));
+    free_buckets(old);
+    return fetch_status(c);
+}
+
+bool handle_overflow(opal_ctx* c, int sp, bool deposit_parked) {
+    int guard = 0;
+    while (c->h_status->n_overflow > 0) {
+        if (c->h_status->n_overflow > c->mover_seg_cap) return fail(c, OPAL_ECAPACITY, "too many parked movers");
+        if (!regrid(c, sp, deposit_parked)) return false;
+        if (++guard > 4) return fail(c, OPAL_ECAPACITY, "re-layout did not converge");
+    }
+    return true;
+}
+
+// write the record counts into the header records of both outboxes
+__global__ void k_outbox_headers(opal_migrant* out_l, opal_migrant* out_r, const StatusDev* st) {
+    if (threadIdx.x == 0) { out_l[0].cell = st->n_out[0]; out_r[0].cell = st->n_out[1]; }
+}
+__global__ void k_header_to_int(const opal_migrant* in, int* n) { if (threadIdx.x == 0) *n = (int)in[0].cell; }
+
+// NCCL ring exchange of both outboxes (fixed size: header + out_cap records) -- replaces the
+// even/odd blocking p2p of mod.rs:308-354 with one grouped, deadlock-free exchange.
+bool nccl_exchange(opal_ctx* c, void* send_l, void* send_r, void* recv_l, void* recv_r, size_t bytes) {
+    if (!c->comm) return fail(c, OPAL_ENCCL, "remote neighbour but no communicator (call opal_comm_init) -- or use the host-staged take/give calls");
+    int rc = 0;
+    rc |= g_nccl.GroupStart();
+    // order matters when both neighbours are the same rank (nranks == 2): my send-to-right pairs
+    // with the peer's recv-from-left
+    if (c->has_right()) rc |= g_nccl.Send(send_r, bytes, NCCL_CHAR, c->right_rank(), c->comm, c->stream);
+    if (c->has_left()) rc |= g_nccl.Send(send_l, bytes, NCCL_CHAR, c->left_rank(), c->comm, c->stream);
+    if (c->has_left()) rc |= g_nccl.Recv(recv_l, bytes, NCCL_CHAR, c->left_rank(), c->comm, c->stream);
+    if (c->has_right()) rc |= g_nccl.Recv(recv_r, bytes, NCCL_CHAR, c->right_rank(), c->comm, c->stream);
+    rc |= g_nccl.GroupEnd();
+    if (rc) return fail(c, OPAL_ENCCL, "ncclSend/ncclRecv failed");
+    return true;
+}
+
+bool remote(opal_ctx* c) { return !c->self_nbr() && (c->has_left() || c->has_right()); }
+
+// insert what the neighbours sent (d_in[side], header + records) into species `sp`
+bool insert_inbox(opal_ctx* c, int sp, int side, bool dep) {
+    k_header_to_int<<<1, 32, 0, c->stream>>>(c->d_in[side], c->d_tmp_int + 1 + side); c->launches++;
+    const long long shift = side == OPAL_RIGHT ? c->g.nx : 0;   // mod.rs:366-368
+    if (sp == OPAL_PHOTON) {
+        c->k.photon_insert(c->stream, pdev(c, c->ph_cur), c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->out_cap, shift, c->d_status);
+    } else {
+        StepParams sp_ = sparams(c, sp);
+        sp_.route_left = sp_.route_right = 0;
+        c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, c->bk[sp].full, dep, c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->out_cap, shift,
+                     nullptr, nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status);
+    }
+    c->launches++;
+    return true;
+}
+
+// gather + push + re-bucket + migrate one charged species (mod.rs:247-376); dep: fused deposit
+bool advance_charged(opal_ctx* c, int sp, bool dep, bool check) {
+    Buckets& B = c->bk[sp];
+    if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
+    if (!reset_status(c, true)) return false;
+    StepParams p = sparams(c, sp);
+    c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_status); c->launches++;
+    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                 reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
+    if (remote(c)) {
+        k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status); c->launches++;
+        if (c->comm) {
+            const size_t bytes = (size_t)(c->out_cap + 1) * sizeof(opal_migrant);
+            if (!nccl_exchange(c, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], bytes)) return false;
+            if (c->has_left()) insert_inbox(c, sp, OPAL_LEFT, dep);
+            if (c->has_right()) insert_inbox(c, sp, OPAL_RIGHT, dep);
+        }
+    }
+    if (check) {
+        if (!fetch_status(c)) return false;
+        c->last_gone[sp][0] = c->h_status->gone[0]; c->last_gone[sp][1] = c->h_status->gone[1];
+        if (!handle_overflow(c, sp, dep)) return false;
+    }
+    return true;
+}
+
+bool advance_photons(opal_ctx* c, bool check) {
+    if (c->flags & OPAL_FLAG_IMMOBILE_PHOTONS) return true;
+    if (c->ph[0].cap == 0) { c->last_gone[2][0] = c->last_gone[2][1] = 0; return true; }
+    if (!reset_status(c, true)) return false;
+    const int src = c->ph_cur, dst = 1 - src;
+    CUB(cudaMemsetAsync(c->ph[dst].d_n, 0, sizeof(int), c->stream));
+    c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status);
+    c->launches++;
+    c->ph_cur = dst;
+    if (remote(c)) {
+        k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status); c->launches++;
+        if (c->comm) {
+            const size_t bytes = (size_t)(c->out_cap + 1) * sizeof(opal_migrant);
+            if (!nccl_exchange(c, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], bytes)) return false;
+            if (c->has_left()) insert_inbox(c, OPAL_PHOTON, OPAL_LEFT, false);
+            if (c->has_right()) insert_inbox(c, OPAL_PHOTON, OPAL_RIGHT, false);
+        }
+    }
+    if (check) {
+        if (!fetch_status(c)) return false;
+        c->last_gone[2][0] = c->h_status->gone[0]; c->last_gone[2][1] = c->h_status->gone[1];
+    }
+    return true;
+}
+
+bool do_emit(opal_ctx* c, double t, double min_e, double max_a, double max_fl) {
+    Buckets& E = c->bk[OPAL_ELECTRON];
+    if (!E.allocated) return true;
+    if (!E.full) return fail(c, OPAL_EINVAL, "emit_radiation needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)");
+    int nph = 0;
+    if (!photon_count(c, &nph)) return false;
+    // at most one photon per electron per call (electron.rs:208-251): make room up front
+    if (!ensure_photons(c, (long long)nph + E.n_hint + c->out_cap)) return false;
+    c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, t, min_e, max_a, max_fl,
+              c->seed, c->emit_calls++, c->d_status);
+    c->launches++;
+    return fetch_status(c);
+}
+
+bool do_sync(opal_ctx* c, double ly, double lz) {
+    const double* halo = nullptr;
+    if (remote(c)) {
+        if (c->comm) {
+            c->k.halo_pack(c->stream, c->g, c->d_halo_send); c->launches++;
+            const size_t bytes = OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double);
+            if (!nccl_exchange(c, c->d_halo_send, c->d_halo_send + OPAL_HALO_CELLS * OPAL_CELL_DOUBLES, c->d_halo_recv,
+                               c->d_halo_recv + OPAL_HALO_CELLS * OPAL_CELL_DOUBLES, bytes)) return false;
+        } else {
+            if ((c->has_left() && !c->halo_given[0]) || (c->has_right() && !c->halo_given[1]))
+                return fail(c, OPAL_EINVAL, "synchronize: neighbour halo missing (halo_give) (yee.rs:413-419)");
+        }
+        halo = c->d_halo_recv;
+        c->halo_given[0] = c->halo_given[1] = false;
+    }
+    c->k.sync_bc(c->stream, c->g, halo, ly, lz, nullptr); c->launches++;
+    return true;
+}
+
+void do_field(opal_ctx* c) {
+    GridDev nxt = c->g;
+    nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
+    c->k.field(c->stream, c->g, nxt, false); c->launches++;
+    c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
+    c->g = nxt;
+}
+
+}  // namespace
+
+// =============================== C ABI ======================================================
+extern "C" {
+
+opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, double dx, double dt, int left, int right,
+                        int rank, int nranks, uint64_t seed, uint32_t flags) {
+    if (!out || nx < 1 || nx > (1ll << 30) || nranks < 1 || rank < 0 || rank >= nranks) return OPAL_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return OPAL_ECUDA;   // no CPU fallback
+    if (device < 0 || device >= ndev) return OPAL_EINVAL;
+    opal_ctx* c = new opal_ctx();
+    *out = c;
+    c->device = device; c->rank = rank; c->nranks = nranks; c->flags = flags; c->seed = seed;
+    c->full = !(flags & OPAL_FLAG_LEAN_STATE);
+    c->k = (flags & OPAL_FLAG_STRICT_FP) ? strict::table() : fast::table();
+    c->slack = env_double("OPAL_BUCKET_SLACK", 1.25);
+    c->pad = (int)env_ll("OPAL_BUCKET_PAD", 64);
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    GridDev& g = c->g;
+    g.nx = (int)nx; g.xmin = xmin; g.dx = dx; g.dt = dt; g.self_nbr = nranks == 1;
+    // yee.rs:278-292
+    if (rank == 0 && left == OPAL_BDY_LASER) { g.left_bdy = OPAL_BDY_LASER; g.left = OPAL_LASER_BDY_SIZE; }
+    else { g.left_bdy = OPAL_BDY_INTERNAL; g.left = OPAL_GHOST_SIZE; }
+    if (rank == nranks - 1 && right == OPAL_BDY_ABSORBING) { g.right_bdy = OPAL_BDY_ABSORBING; g.right = OPAL_ABSORBING_BDY_SIZE; }
+    else if (rank == nranks - 1 && right == OPAL_BDY_CONDUCTING) { g.right_bdy = OPAL_BDY_CONDUCTING; g.right = OPAL_CONDUCTING_BDY_SIZE; }
+    else { g.right_bdy = OPAL_BDY_INTERNAL; g.right = OPAL_GHOST_SIZE; }
+    g.len = g.nx + g.left + g.right;
+    const size_t n = (size_t)g.len;
+    CU(cudaMalloc(&c->grid_block, 16 * n * sizeof(double)));
+    CU(cudaMemsetAsync(c->grid_block, 0, 16 * n * sizeof(double), c->stream));
+    double* p = c->grid_block;
+    g.rho = p; g.jx = p + n; g.jy = p + 2 * n; g.jz = p + 3 * n;
+    g.ex = p + 4 * n; g.ey = p + 5 * n; g.ez = p + 6 * n; g.bx = p + 7 * n; g.by = p + 8 * n; g.bz = p + 9 * n;
+    for (int k = 0; k < 6; k++) c->eb_alt[k] = p + (10 + k) * n;
+    CU(cudaMalloc(&c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int)));
+    CU(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
+    CU(cudaMallocHost(&c->h_status, sizeof(StatusDev)));
+    memset(c->h_status, 0, sizeof(StatusDev));
+    CU(cudaMalloc(&c->d_energy, 4 * sizeof(double)));
+    CU(cudaMallocHost(&c->h_energy, 4 * sizeof(double)));
+    CU(cudaMalloc(&c->d_tmp_int, 8 * sizeof(int)));
+    c->out_cap = (int)env_ll("OPAL_EXCHANGE_CAP", 4096);
+    for (int s = 0; s < 2; s++) {
+        CU(cudaMalloc(&c->d_out[s], (size_t)(c->out_cap + 1) * sizeof(opal_migrant)));
+        CU(cudaMalloc(&c->d_in[s], (size_t)(c->out_cap + 1) * sizeof(opal_migrant)));
+        CU(cudaMemsetAsync(c->d_in[s], 0, sizeof(opal_migrant), c->stream));
+    }
+    CU(cudaMalloc(&c->d_halo_send, 2 * OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double)));
+    CU(cudaMalloc(&c->d_halo_recv, 2 * OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double)));
+    CU(cudaMalloc(&c->d_qed_tables, sizeof(H_QED_TABLES)));
+    CU(cudaMemcpyAsync(c->d_qed_tables, H_QED_TABLES, sizeof(H_QED_TABLES), cudaMemcpyHostToDevice, c->stream));
+    if (!ensure_movers(c, 1024)) return (opal_status)c->status;
+    CU(cudaStreamSynchronize(c->stream));
+    return OPAL_OK;
+}
+
+opal_status opal_destroy(opal_ctx* c) {
+    if (!c) return OPAL_EINVAL;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (int s = 0; s < 2; s++) free_buckets(c->bk[s]);
+    for (int w = 0; w < 2; w++) {
+        if (c->ph[w].d_n) cudaFree(c->ph[w].d_n);
+        if (c->ph[w].d_cell) cudaFree(c->ph[w].d_cell);
+        for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
+    }
+    void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables};
+    for (void* p : frees) if (p) cudaFree(p);
+    if (c->h_status) cudaFreeHost(c->h_status);
+    if (c->h_energy) cudaFreeHost(c->h_energy);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return OPAL_OK;
+}
+
+const char* opal_last_error(opal_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+opal_status opal_grid_shape(opal_ctx* c, int64_t* total, int64_t* l, int64_t* r) {
+    if (!c) return OPAL_EINVAL;
+    if (total) *total = c->g.len;
+    if (l) *l = c->g.left;
+    if (r) *r = c->g.right;
+    return OPAL_OK;
+}
+
+opal_status opal_set_ion(opal_ctx* c, double z_star, double a) {
+    CHECK_CTX(c);
+    c->z_star = z_star; c->mass_number = a;
+    return OPAL_OK;
+}
+
+opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int64_t* cell, const double* x, const double* ux,
+                                  const double* uy, const double* uz, const double* w, const double* tau) {
+    CHECK_CTX(c);
+    if (n < 0 || n > (1ll << 31) - 64 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
+    const double dx = c->g.dx, dt = c->g.dt;
+    const double inf = std::numeric_limits<double>::infinity();
+    if (species == OPAL_PHOTON) {
+        if (!ensure_photons(c, std::max<int64_t>(n, 1))) return (opal_status)c->status;
+        Photons& P = c->ph[c->ph_cur];
+        std::vector<int> hc((size_t)n);
+        std::vector<double> hf[NF_PHOTON];
+        for (auto& v : hf) v.assign((size_t)n, 0.0);
+        for (int64_t i = 0; i < n; i++) {
+            if (cell[i] < 0 || cell[i] >= c->g.nx) return (opal_status)(fail(c, OPAL_EINVAL, "upload: cell out of range"), c->status);
+            hc[i] = (int)cell[i];
+            const double k0 = std::sqrt(ux[i] * ux[i] + uy[i] * uy[i] + uz[i] * uz[i]);   // photon.rs:95-116
+            hf[P_X][i] = x[i]; hf[P_PREVX][i] = x[i] - C_LIGHT * ux[i] * dt / (k0 * dx);
+            hf[P_KX][i] = ux[i]; hf[P_KY][i] = uy[i]; hf[P_KZ][i] = uz[i]; hf[P_W][i] = w[i];
+            hf[P_TAU][i] = tau ? tau[i] : inf; hf[P_BIRTH][i] = -inf;
+        }
+        const int nn = (int)n;
+        CU(cudaMemcpyAsync(P.d_n, &nn, sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        if (n > 0) {
+            CU(cudaMemcpyAsync(P.d_cell, hc.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+            for (int k = 0; k < NF_PHOTON; k++) CU(cudaMemcpyAsync(P.d_f[k], hf[k].data(), (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        }
+        CU(cudaStreamSynchronize(c->stream));
+        return OPAL_OK;
+    }
+    if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
+    Buckets& B = c->bk[species];
+    free_buckets(B);
+    B = Buckets();
+    if (n == 0) return OPAL_OK;
+    const int ncell = c->g.nx;
+    std::vector<long long> demand(ncell, 0);
+    for (int64_t i = 0; i < n; i++) {
+        if (cell[i] < 0 || cell[i] >= ncell) return (opal_status)(fail(c, OPAL_EINVAL, "upload: cell out of range"), c->status);
+        demand[cell[i]]++;
+    }
+    if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
+    B.n_hint = n;
+    if (!ensure_movers(c, n)) return (opal_status)c->status;
+    // host-side bucketing into the slot layout (stable: keeps the caller's order inside a cell)
+    const int nf = c->full ? NF_FULL : NF_LEAN;
+    std::vector<std::vector<double>> hf(nf, std::vector<double>((size_t)B.slots, 0.0));
+    std::vector<int> fill(ncell, 0);
+    for (int64_t i = 0; i < n; i++) {
+        const long long s = B.h_start[cell[i]] + fill[cell[i]]++;
+        hf[F_X][s] = x[i]; hf[F_UX][s] = ux[i]; hf[F_UY][s] = uy[i]; hf[F_UZ][s] = uz[i]; hf[F_W][s] = w[i];
+        if (c->full) {
+            const double u2 = ux[i] * ux[i] + uy[i] * uy[i] + uz[i] * uz[i];
+            if (species == OPAL_ELECTRON) {           // electron.rs:85-103
+                const double gamma = std::sqrt(1.0 + u2);
+                hf[F_GAMMA][s] = gamma;
+                hf[F_PREVX][s] = x[i] - C_LIGHT * ux[i] * dt / (gamma * dx);
+                hf[F_TAU][s] = tau ? tau[i] : inf;
+            } else {                                  // ion.rs:81-101
+                const double gm1 = u2 / (1.0 + std::sqrt(1.0 + u2));
+                const double vx = C_LIGHT * ux[i] / (1.0 + gm1);
+                hf[F_GAMMA][s] = gm1;
+                hf[F_PREVX][s] = x[i] - vx * dt / dx;
+                hf[F_TAU][s] = inf;
+            }
+        }
+    }
+    CU(cudaMemcpyAsync(B.d_count, fill.data(), (size_t)ncell * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    for (int k = 0; k < nf; k++) CU(cudaMemcpyAsync(B.d_f[k], hf[k].data(), (size_t)B.slots * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return OPAL_OK;
+}
+
+opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, double weight, const double u_th[3], const double drift[3],
+                                    int two_stream, int64_t global_cell_offset, uint64_t seed) {
+    CHECK_CTX(c);
+    if ((species != OPAL_ELECTRON && species != OPAL_ION) || npc < 1 || !u_th || !drift) return OPAL_EINVAL;
+    Buckets& B = c->bk[species];
+    free_buckets(B);
+    B = Buckets();
+    std::vector<long long> demand(c->g.nx, npc);
+    if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
+    B.n_hint = npc * (long long)c->g.nx;
+    if (!ensure_movers(c, B.n_hint)) return (opal_status)c->status;
+    c->k.generate(c->stream, bdev(c, species), species, npc, weight, u_th, drift, two_stream, global_cell_offset, seed, c->full, c->g.dx, c->g.dt);
+    c->launches++;
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    return OPAL_OK;
+}
+
+opal_status opal_particles_count(opal_ctx* c, int species, int64_t* n) {
+    CHECK_CTX(c);
+    if (!n) return OPAL_EINVAL;
+    *n = 0;
+    if (species == OPAL_PHOTON) {
+        int v = 0;
+        if (!photon_count(c, &v)) return (opal_status)c->status;
+        *n = v;
+        return OPAL_OK;
+    }
+    if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
+    Buckets& B = c->bk[species];
+    if (!B.allocated) return OPAL_OK;
+    std::vector<int> cnt(c->g.nx);
+    CU(cudaMemcpyAsync(cnt.data(), B.d_count, cnt.size() * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    long long t = 0;
+    for (int v : cnt) t += v;
+    *n = t;
+    return OPAL_OK;
+}
+
+opal_status opal_particles_download(opal_ctx* c, int species, int64_t cap, int64_t* cell, double* x, double* prev_x, double* ux,
+                                    double* uy, double* uz, double* w, double* gamma, double* chi, double* tau, double* work,
+                                    double* y, double* z, double* birth) {
+    CHECK_CTX(c);
+    const double inf = std::numeric_limits<double>::infinity();
+    if (species == OPAL_PHOTON) {
+        int n = 0;
+        if (!photon_count(c, &n)) return (opal_status)c->status;
+        if (n > cap) return OPAL_ECAPACITY;
+        if (n == 0) return OPAL_OK;
+        Photons& P = c->ph[c->ph_cur];
+        std::vector<int> hc(n);
+        std::vector<double> hf[NF_PHOTON];
+        CU(cudaMemcpyAsync(hc.data(), P.d_cell, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        for (int k = 0; k < NF_PHOTON; k++) { hf[k].resize(n); CU(cudaMemcpyAsync(hf[k].data(), P.d_f[k], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream)); }
+        CU(cudaStreamSynchronize(c->stream));
+        // Population::advance leaves the store sorted by cell (mod.rs:288)
+        std::vector<int> order(n);
+        for (int i = 0; i < n; i++) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return hc[a] < hc[b]; });
+        for (int o = 0; o < n; o++) {
+            const int i = order[o];
+            if (cell) cell[o] = hc[i];
+            if (x) x[o] = hf[P_X][i];
+            if (prev_x) prev_x[o] = hf[P_PREVX][i];
+            if (ux) ux[o] = hf[P_KX][i];
+            if (uy) uy[o] = hf[P_KY][i];
+            if (uz) uz[o] = hf[P_KZ][i];
+            if (w) w[o] = hf[P_W][i];
+            if (gamma) gamma[o] = std::sqrt(hf[P_KX][i] * hf[P_KX][i] + hf[P_KY][i] * hf[P_KY][i] + hf[P_KZ][i] * hf[P_KZ][i]);
+            if (chi) chi[o] = hf[P_CHI][i];
+            if (tau) tau[o] = hf[P_TAU][i];
+            if (work) work[o] = 0.0;
+            if (y) y[o] = hf[P_Y][i];
+            if (z) z[o] = hf[P_Z][i];
+            if (birth) birth[o] = hf[P_BIRTH][i];
+        }
+        return OPAL_OK;
+    }
+    if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
+    Buckets& B = c->bk[species];
+    if (!B.allocated) return OPAL_OK;
+    const int ncell = c->g.nx;
+    std::vector<int> cnt(ncell);
+    CU(cudaMemcpyAsync(cnt.data(), B.d_count, (size_t)ncell * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    std::vector<long long> off(ncell);
+    long long n = 0;
+    for (int i = 0; i < ncell; i++) { off[i] = n; n += cnt[i]; }
+    if (n > cap) return OPAL_ECAPACITY;
+    if (n == 0) return OPAL_OK;
+    long long* d_off = nullptr; long long* d_cell = nullptr;
+    CU(cudaMalloc(&d_off, (size_t)ncell * sizeof(long long)));
+    CU(cudaMemcpyAsync(d_off, off.data(), (size_t)ncell * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+    if (cell) CU(cudaMalloc(&d_cell, (size_t)n * sizeof(long long)));
+    double* host_dst[NF_FULL] = {x, ux, uy, uz, w, prev_x, gamma, chi, tau, work, y, z};
+    double* d_out[NF_FULL] = {nullptr};
+    const int nf = B.full ? NF_FULL : NF_LEAN;
+    for (int k = 0; k < nf; k++) if (host_dst[k]) CU(cudaMalloc(&d_out[k], (size_t)n * sizeof(double)));
+    c->k.gather_out(c->stream, bdev(c, species), B.full, species, d_off, d_cell, d_out); c->launches++;
+    if (cell) CU(cudaMemcpyAsync(cell, d_cell, (size_t)n * sizeof(long long), cudaMemcpyDeviceToHost, c->stream));
+    for (int k = 0; k < nf; k++) if (host_dst[k]) CU(cudaMemcpyAsync(host_dst[k], d_out[k], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(d_off); if (d_cell) cudaFree(d_cell);
+    for (int k = 0; k < nf; k++) if (d_out[k]) cudaFree(d_out[k]);
+    if (B.full) {
+        if (species == OPAL_ION) {
+            if (gamma) for (long long i = 0; i < n; i++) gamma[i] = 1.0 + gamma[i];
+            if (chi) for (long long i = 0; i < n; i++) chi[i] = 0.0;
+            if (tau) for (long long i = 0; i < n; i++) tau[i] = inf;
+        }
+    } else {
+        // lean layout: derived quantities are recomputed, unobservable ones reported as zero
+        for (long long i = 0; i < n; i++) {
+            if (gamma) {
+                if (!ux || !uy || !uz) return (opal_status)(fail(c, OPAL_EINVAL, "lean download of gamma needs ux, uy, uz"), c->status);
+                gamma[i] = std::sqrt(1.0 + (ux[i] * ux[i] + uy[i] * uy[i] + uz[i] * uz[i]));
+            }
+            if (prev_x) prev_x[i] = std::numeric_limits<double>::quiet_NaN();
+            if (chi) chi[i] = 0.0;
+            if (tau) tau[i] = inf;
+            if (work) work[i] = 0.0;
+            if (y) y[i] = 0.0;
+            if (z) z[i] = 0.0;
+        }
+    }
+    if (birth) for (long long i = 0; i < n; i++) birth[i] = 0.0;
+    return OPAL_OK;
+}
+
+opal_status opal_fields_upload(opal_ctx* c, const double* cells11) {
+    CHECK_CTX(c);
+    const int len = c->g.len;
+    std::vector<double> soa((size_t)10 * len);
+    for (int i = 0; i < len; i++)
+        for (int k = 0; k < 10; k++) soa[(size_t)k * len + i] = cells11[(size_t)i * 11 + 1 + k];
+    double* dst[10] = {c->g.rho, c->g.jx, c->g.jy, c->g.jz, c->g.ex, c->g.ey, c->g.ez, c->g.bx, c->g.by, c->g.bz};
+    for (int k = 0; k < 10; k++) CU(cudaMemcpyAsync(dst[k], soa.data() + (size_t)k * len, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return OPAL_OK;
+}
+
+opal_status opal_fields_download(opal_ctx* c, double* cells11) {
+    CHECK_CTX(c);
+    const int len = c->g.len;
+    std::vector<double> soa((size_t)10 * len);
+    double* src[10] = {c->g.rho, c->g.jx, c->g.jy, c->g.jz, c->g.ex, c->g.ey, c->g.ez, c->g.bx, c->g.by, c->g.bz};
+    for (int k = 0; k < 10; k++) CU(cudaMemcpyAsync(soa.data() + (size_t)k * len, src[k], (size_t)len * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < len; i++) {
+        cells11[(size_t)i * 11] = c->g.xmin + ((double)i - (double)c->g.left) * c->g.dx;   // yee.rs:296
+        for (int k = 0; k < 10; k++) cells11[(size_t)i * 11 + 1 + k] = soa[(size_t)k * len + i];
+    }
+    return OPAL_OK;
+}
+
+opal_status opal_advance(opal_ctx* c, int species) {
+    CHECK_CTX(c);
+    if (species == OPAL_PHOTON) { advance_photons(c, true); return (opal_status)c->status; }
+    if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
+    if (!c->full) return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context: only opal_run_steps is available"), c->status);
+    advance_charged(c, species, false, true);
+    return (opal_status)c->status;
+}
+
+opal_status opal_last_leavers(opal_ctx* c, int species, int64_t* l, int64_t* r) {
+    if (!c || species < 0 || species > 2) return OPAL_EINVAL;
+    if (l) *l = c->last_gone[species][0];
+    if (r) *r = c->last_gone[species][1];
+    return OPAL_OK;
+}
+
+opal_status opal_migrants_take(opal_ctx* c, int species, int side, int64_t cap, int64_t* n, opal_migrant* out) {
+    CHECK_CTX(c);
+    if (side != OPAL_LEFT && side != OPAL_RIGHT) return OPAL_EINVAL;
+    (void)species;   // the outbox holds the leavers of the most recent advance()
+    *n = 0;
+    if (!remote(c)) return OPAL_OK;
+    if ((side == OPAL_LEFT && !c->has_left()) || (side == OPAL_RIGHT && !c->has_right())) return OPAL_OK;
+    opal_migrant hdr;
+    CU(cudaMemcpyAsync(&hdr, c->d_out[side], sizeof(hdr), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *n = hdr.cell;
+    if (*n > cap) return OPAL_ECAPACITY;
+    if (*n > 0) {
+        CU(cudaMemcpyAsync(out, c->d_out[side] + 1, (size_t)*n * sizeof(opal_migrant), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    return OPAL_OK;
+}
+
+opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, const opal_migrant* in) {
+    CHECK_CTX(c);
+    if (side != OPAL_LEFT && side != OPAL_RIGHT || n < 0 || species < 0 || species > 2) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    if (n > c->out_cap) return OPAL_ECAPACITY;
+    opal_migrant hdr;
+    memset(&hdr, 0, sizeof(hdr));
+    hdr.cell = n;
+    CU(cudaMemcpyAsync(c->d_in[side], &hdr, sizeof(hdr), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->d_in[side] + 1, in, (size_t)n * sizeof(opal_migrant), cudaMemcpyHostToDevice, c->stream));
+    if (species == OPAL_PHOTON) { if (!ensure_photons(c, c->ph[0].cap / 2 + n)) return (opal_status)c->status; }
+    else if (!c->bk[species].allocated) {
+        std::vector<long long> demand(c->g.nx, 0);
+        if (!alloc_buckets(c, c->bk[species], demand, c->full)) return (opal_status)c->status;
+    }
+    CU(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
+    insert_inbox(c, species, side, false);
+    if (!fetch_status(c)) return (opal_status)c->status;
+    if (species != OPAL_PHOTON) handle_overflow(c, species, false);
+    return (opal_status)c->status;
+}
+
+opal_status opal_emit_radiation(opal_ctx* c, double t, const double* min_energy_mev, const double* max_angle, const double* max_fl) {
+    CHECK_CTX(c);
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    do_emit(c, t, min_energy_mev ? *min_energy_mev : nan, max_angle ? *max_angle : nan, max_fl ? *max_fl : nan);
+    return (opal_status)c->status;
+}
+
+opal_status opal_clear(opal_ctx* c) {
+    CHECK_CTX(c);
+    c->k.clear(c->stream, c->g); c->launches++;
+    return OPAL_OK;
+}
+
+opal_status opal_deposit(opal_ctx* c, int species) {
+    CHECK_CTX(c);
+    if (species == OPAL_PHOTON) return OPAL_OK;   // charge 0 (photon.rs:197-199)
+    if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
+    if (!c->full) return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context: only opal_run_steps is available"), c->status);
+    if (!c->bk[species].allocated) return OPAL_OK;
+    c->k.deposit(c->stream, c->g, bdev(c, species), sparams(c, species), c->d_status); c->launches++;
+    return OPAL_OK;
+}
+
+opal_status opal_halo_take(opal_ctx* c, int side, double* out) {
+    CHECK_CTX(c);
+    if (side != OPAL_LEFT && side != OPAL_RIGHT) return OPAL_EINVAL;
+    c->k.halo_pack(c->stream, c->g, c->d_halo_send); c->launches++;
+    CU(cudaMemcpyAsync(out, c->d_halo_send + side * OPAL_HALO_CELLS * OPAL_CELL_DOUBLES, OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double),
+                       cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return OPAL_OK;
+}
+
+opal_status opal_halo_give(opal_ctx* c, int side, const double* in) {
+    CHECK_CTX(c);
+    if (side != OPAL_LEFT && side != OPAL_RIGHT) return OPAL_EINVAL;
+    CU(cudaMemcpyAsync(c->d_halo_recv + side * OPAL_HALO_CELLS * OPAL_CELL_DOUBLES, in, OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double),
+                       cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->halo_given[side] = true;
+    return OPAL_OK;
+}
+
+opal_status opal_synchronize(opal_ctx* c, double t, double laser_y, double laser_z) {
+    CHECK_CTX(c);
+    (void)t;
+    do_sync(c, laser_y, laser_z);
+    return (opal_status)c->status;
+}
+
+opal_status opal_laser_x(opal_ctx* c, double* x) {
+    if (!c || !x) return OPAL_EINVAL;
+    *x = c->g.xmin + ((double)(c->g.left - 2) - (double)c->g.left) * c->g.dx;
+    return OPAL_OK;
+}
+
+opal_status opal_field_advance(opal_ctx* c) {
+    CHECK_CTX(c);
+    do_field(c);
+    return OPAL_OK;
+}
+
+opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double* laser_y, const double* laser_z,
+                           int current_deposition, int photon_emission, const double* f3) {
+    CHECK_CTX(c);
+    if (remote(c) && !c->comm) return (opal_status)(fail(c, OPAL_ENCCL, "run_steps with remote neighbours needs opal_comm_init"), c->status);
+    if (!c->full && (photon_emission || !current_deposition))
+        return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context supports only the fused push+deposit step (deposition on, emission off)"), c->status);
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    const bool fused = current_deposition && !photon_emission;
+    double t = t0;
+    for (int64_t s = 0; s < nsteps; s++) {   // main.rs:238-267
+        if (current_deposition) { c->k.clear(c->stream, c->g); c->launches++; }
+        if (!advance_charged(c, OPAL_ELECTRON, fused, true)) break;
+        if (!advance_charged(c, OPAL_ION, fused, true)) break;
+        if (!advance_photons(c, c->ph[0].cap > 0)) break;
+        if (photon_emission) { if (!do_emit(c, t, f3 ? f3[0] : nan, f3 ? f3[1] : nan, f3 ? f3[2] : nan)) break; }
+        if (current_deposition && !fused) {
+            if (c->bk[0].allocated) { c->k.deposit(c->stream, c->g, bdev(c, 0), sparams(c, 0), c->d_status); c->launches++; }
+            if (c->bk[1].allocated) { c->k.deposit(c->stream, c->g, bdev(c, 1), sparams(c, 1), c->d_status); c->launches++; }
+        }
+        if (!do_sync(c, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0)) break;
+        do_field(c);
+        t += c->g.dt;
+    }
+    if (c->status == OPAL_OK) {
+        cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        if (e != cudaSuccess) fail(c, OPAL_ECUDA, std::string("run_steps: ") + cudaGetErrorString(e));
+    }
+    return (opal_status)c->status;
+}
+
+opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, double* ke_ph) {
+    CHECK_CTX(c);
+    BucketDev be, bi;
+    PhotonDev pp;
+    const bool he = c->bk[0].allocated, hi = c->bk[1].allocated, hp = c->ph[0].cap > 0;
+    if (he) be = bdev(c, 0);
+    if (hi) bi = bdev(c, 1);
+    if (hp) pp = pdev(c, c->ph_cur);
+    c->k.energy(c->stream, c->g, he ? &be : nullptr, hi ? &bi : nullptr, hp ? &pp : nullptr, c->full, c->d_energy);
+    c->launches += 1 + (he ? 1 : 0) + (hi ? 1 : 0) + (hp ? 1 : 0);
+    CU(cudaMemcpyAsync(c->h_energy, c->d_energy, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (em) *em = c->h_energy[0];
+    if (ke_e) *ke_e = c->h_energy[1];
+    if (ke_i) *ke_i = c->h_energy[2];
+    if (ke_ph) *ke_ph = c->h_energy[3];
+    return OPAL_OK;
+}
+
+opal_status opal_comm_unique_id(void* id128) {
+    if (!id128) return OPAL_EINVAL;
+    if (!g_nccl.load()) return OPAL_ENCCL;
+    ncclUniqueId id;
+    if (g_nccl.GetUniqueId(&id)) return OPAL_ENCCL;
+    memcpy(id128, &id, 128);
+    return OPAL_OK;
+}
+
+opal_status opal_comm_init(opal_ctx* c, const void* id128) {
+    CHECK_CTX(c);
+    if (!id128) return OPAL_EINVAL;
+    if (!g_nccl.load()) return (opal_status)(fail(c, OPAL_ENCCL, "libnccl.so.2 not found"), c->status);
+    ncclUniqueId id;
+    memcpy(&id, id128, 128);
+    if (g_nccl.CommInitRank(&c->comm, c->nranks, id, c->rank)) return (opal_status)(fail(c, OPAL_ENCCL, "ncclCommInitRank failed"), c->status);
+    return OPAL_OK;
+}
+
+opal_status opal_stream(opal_ctx* c, void** s) {
+    if (!c || !s) return OPAL_EINVAL;
+    *s = (void*)c->stream;
+    return OPAL_OK;
+}
+
+opal_status opal_launch_count(opal_ctx* c, int64_t* n) {
+    if (!c || !n) return OPAL_EINVAL;
+    *n = c->launches;
+    return OPAL_OK;
+}
+
+// ---- pure functions (no context): run on the current device's default stream -----------------
+opal_status opal_qed_rate(int64_t n, const double* chi, const double* gamma, double* out) {
+    if (n < 0 || (n > 0 && (!chi || !gamma || !out))) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    double *d_chi = nullptr, *d_g = nullptr, *d_o = nullptr;
+    const size_t b = (size_t)n * sizeof(double);
+    if (cudaMalloc(&d_chi, b) != cudaSuccess || cudaMalloc(&d_g, b) != cudaSuccess || cudaMalloc(&d_o, b) != cudaSuccess) return OPAL_ECUDA;
+    cudaMemcpy(d_chi, chi, b, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_g, gamma, b, cudaMemcpyHostToDevice);
+    fast::table().qed_rate(0, (int)n, d_chi, d_g, d_o);
+    cudaError_t e = cudaMemcpy(out, d_o, b, cudaMemcpyDeviceToHost);
+    cudaFree(d_chi); cudaFree(d_g); cudaFree(d_o);
+    return e == cudaSuccess ? OPAL_OK : OPAL_ECUDA;
+}
+
+opal_status opal_qed_sample(int64_t n, const double* chi, const double* gamma, const double* r1, const double* r2, const double* r3,
+                            int classical, double* out3) {
+    if (n < 0 || (n > 0 && (!chi || !gamma || !r1 || !r2 || !r3 || !out3))) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    const size_t b = (size_t)n * sizeof(double);
+    double* d[5]; double* d_o = nullptr; double* d_t = nullptr; StatusDev* d_st = nullptr;
+    const double* h[5] = {chi, gamma, r1, r2, r3};
+    for (int k = 0; k < 5; k++) { if (cudaMalloc(&d[k], b) != cudaSuccess) return OPAL_ECUDA; cudaMemcpy(d[k], h[k], b, cudaMemcpyHostToDevice); }
+    if (cudaMalloc(&d_o, 3 * b) != cudaSuccess || cudaMalloc(&d_t, sizeof(H_QED_TABLES)) != cudaSuccess || cudaMalloc(&d_st, sizeof(StatusDev)) != cudaSuccess) return OPAL_ECUDA;
+    cudaMemcpy(d_t, H_QED_TABLES, sizeof(H_QED_TABLES), cudaMemcpyHostToDevice);
+    cudaMemset(d_st, 0, sizeof(StatusDev));
+    fast::table().qed_sample(0, (int)n, d_t, d[0], d[1], d[2], d[3], d[4], classical, d_o, d_st);
+    cudaError_t e = cudaMemcpy(out3, d_o, 3 * b, cudaMemcpyDeviceToHost);
+    StatusDev st;
+    cudaMemcpy(&st, d_st, sizeof(st), cudaMemcpyDeviceToHost);
+    for (int k = 0; k < 5; k++) cudaFree(d[k]);
+    cudaFree(d_o); cudaFree(d_t); cudaFree(d_st);
+    if (e != cudaSuccess) return OPAL_ECUDA;
+    return (st.err & ERR_CHI) ? OPAL_ECHI_RANGE : OPAL_OK;
+}
+
+opal_status opal_fields_at(opal_ctx* c, int64_t n, const int64_t* cell, const double* xi, double* out6) {
+    CHECK_CTX(c);
+    if (n <= 0) return OPAL_OK;
+    long long* d_c = nullptr; double *d_x = nullptr, *d_o = nullptr;
+    CU(cudaMalloc(&d_c, (size_t)n * sizeof(long long)));
+    CU(cudaMalloc(&d_x, (size_t)n * sizeof(double)));
+    CU(cudaMalloc(&d_o, (size_t)n * 6 * sizeof(double)));
+    CU(cudaMemcpyAsync(d_c, cell, (size_t)n * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_x, xi, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    c->k.fields_at(c->stream, c->g, (int)n, d_c, d_x, d_o, c->d_status); c->launches++;
+    CU(cudaMemcpyAsync(out6, d_o, (size_t)n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    fetch_status(c);
+    cudaFree(d_c); cudaFree(d_x); cudaFree(d_o);
+    return (opal_status)c->status;
+}
+
+}  // extern "C"

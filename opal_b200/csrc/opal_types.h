@@ -1,0 +1,102 @@
+// opal_types.h -- plain structs shared by the host library and the kernels.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../../include/opal_b200.h"
+
+namespace opal {
+
+// The mover buffer is split into this many independently counted segments (cell c appends to
+// segment c mod N) so the per-chunk slot reservations do not serialise on one L2 atomic address.
+#define OPAL_MOVER_SEGMENTS 1024
+
+// particle field indices of a BucketStore (charged species).  The first NF_LEAN are always
+// allocated; the rest only for full-state contexts.
+enum { F_X = 0, F_UX, F_UY, F_UZ, F_W, NF_LEAN, F_PREVX = NF_LEAN, F_GAMMA, F_CHI, F_TAU, F_WORK, F_Y, F_Z, NF_FULL };
+// flat photon store
+enum { P_X = 0, P_PREVX, P_KX, P_KY, P_KZ, P_W, P_CHI, P_TAU, P_Y, P_Z, P_BIRTH, NF_PHOTON };
+
+// device-side view of the Yee grid: SoA over `len` cells (ghost/boundary zones included).
+struct GridDev {
+    int len, left, right, nx;       // total cells, zone sizes, interior cells
+    int left_bdy, right_bdy;        // resolved opal_boundary of this slab
+    int self_nbr;                   // nranks == 1: periodic self-neighbour (yee.rs:369)
+    double xmin, dx, dt;
+    double *rho, *jx, *jy, *jz;     // current set (deposit target / field kernel source)
+    double *ex, *ey, *ez, *bx, *by, *bz;
+};
+
+// Cell-major gapped buckets: cell c owns slots [start[c], start[c+1]) of which the first
+// count[c] are live.  start[] is 32-slot aligned so a warp's 32-particle chunk is one 256-byte
+// aligned segment per field.
+struct BucketDev {
+    int ncell;
+    const long long* start;
+    int* count;
+    double* f[NF_FULL];
+    double z_star, mass_number;     // ions (ion.rs:236)
+};
+
+struct PhotonDev {
+    int cap;
+    int* n;                         // live count (device)
+    int* cell;
+    double* f[NF_PHOTON];
+};
+
+// device-side counters / sticky error bits, mirrored to pinned host memory after each step
+struct StatusDev {
+    int n_movers;        // records in the mover buffer
+    int n_overflow;      // movers that did not fit their destination bucket
+    int n_out[2];        // records in the left/right outbox
+    int gone[2];         // leaver counts of the last advance (mod.rs:284)
+    unsigned err;        // bit 0: CFL assert, 1: index assert, 2: chi range, 3: buffer capacity
+    int n_new_photons;
+    int pad;
+};
+enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u };
+
+struct StepParams {
+    uint32_t flags;
+    int species;             // opal_species
+    int route_left, route_right;   // what happens to a leaver: 0 = delete (open boundary), 1 = wrap (self), 2 = outbox
+    int mover_cap, out_cap;
+};
+
+// one set of kernel launchers; two instances exist (fast: FMA contraction on, strict: off)
+struct KernelTable {
+    void (*push)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool fused_deposit,
+                 opal_migrant* movers, StatusDev* st);
+    void (*scatter)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool deposit,
+                    const opal_migrant* recs, const int* n_recs, int n_max, long long cell_shift, const int* idx_list,
+                    opal_migrant* outbox_l, opal_migrant* outbox_r, int* overflow_idx, StatusDev* st);
+    void (*deposit)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, StatusDev* st);
+    void (*photon_push)(cudaStream_t, const GridDev&, const PhotonDev& src, const PhotonDev& dst, const StepParams&,
+                        opal_migrant* outbox_l, opal_migrant* outbox_r, StatusDev* st);
+    void (*photon_insert)(cudaStream_t, const PhotonDev& dst, const opal_migrant* recs, const int* n_recs, int n_max,
+                          long long cell_shift, StatusDev* st);
+    void (*emit)(cudaStream_t, const GridDev&, const BucketDev& electrons, const PhotonDev& photons, const StepParams&,
+                 const double* qed_tables, double t, double min_energy, double max_angle, double max_fl,
+                 uint64_t seed, uint64_t call_index, StatusDev* st);
+    void (*sync_bc)(cudaStream_t, const GridDev&, const double* halo_recv /*2 x 8 x 11 or null*/, double laser_y, double laser_z,
+                    const double* laser_dev /*2 doubles or null*/);
+    void (*field)(cudaStream_t, const GridDev& cur, const GridDev& nxt, bool zero_next_j);
+    void (*clear)(cudaStream_t, const GridDev&);
+    void (*halo_pack)(cudaStream_t, const GridDev&, double* out2x8x11);
+    void (*energy)(cudaStream_t, const GridDev&, const BucketDev* electrons, const BucketDev* ions, const PhotonDev* photons,
+                   bool full, double* out4);
+    void (*generate)(cudaStream_t, const BucketDev&, int species, long long npc, double weight, const double* uth3, const double* drift3,
+                     int two_stream, long long global_cell_offset, uint64_t seed, bool full, double dx, double dt);
+    void (*gather_out)(cudaStream_t, const BucketDev&, bool full, int species, const long long* out_offset,
+                       long long* cell, double* const* out_fields /*NF_FULL device ptrs*/);
+    void (*qed_rate)(cudaStream_t, int n, const double* chi, const double* gamma, double* out);
+    void (*qed_sample)(cudaStream_t, int n, const double* qed_tables, const double* chi, const double* gamma, const double* r1,
+                       const double* r2, const double* r3, int classical, double* out3, StatusDev* st);
+    void (*fields_at)(cudaStream_t, const GridDev&, int n, const long long* cell, const double* xi, double* out6, StatusDev* st);
+    void (*copy_buckets)(cudaStream_t, const BucketDev& src, const BucketDev& dst, bool full);
+};
+
+namespace fast { KernelTable table(); }
+namespace strict { KernelTable table(); }
+
+}  // namespace opal

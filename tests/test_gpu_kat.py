@@ -1,0 +1,67 @@
+"""The reference's known-answer tests run through the CUDA library's C ABI (B200)."""
+import numpy as np
+import pytest
+
+import kat
+
+pytestmark = pytest.mark.gpu
+
+
+def test_laser_bc(gpu):
+    em, target, _ = kat.laser_bc(gpu)
+    assert abs(em - target) / target < 1.0e-3
+
+
+def test_conducting_bc(gpu):
+    em, target = kat.conducting_bc(gpu)
+    assert abs(em - target) / target < 1.0e-3
+
+
+def test_periodic_bc(gpu):
+    e1, e2 = kat.periodic_bc(gpu)
+    assert e1 > 0.0 and abs(e1 - e2) / e1 < 1.0e-6
+
+
+def test_maxwell_matches_oracle(gpu, oracle):
+    """same drive, both sides: EM energy after the laser_bc run agrees to 1e-10"""
+    em_g, _, ey_g = kat.laser_bc(gpu)
+    em_o, _, ey_o = kat.laser_bc(oracle)
+    assert abs(em_g - em_o) / em_o < 1.0e-10
+    assert np.max(np.abs(ey_g - ey_o)) < 1.0e-10
+
+
+def test_static_magnetic_field(gpu):
+    p, target = kat.static_magnetic_field(gpu)
+    assert abs(p["gamma"][0] - target) / target < 1.0e-6
+
+
+def test_static_electric_field(gpu):
+    p, target = kat.static_electric_field(gpu)
+    assert abs(p["gamma"][0] - target) / target < 1.0e-6
+
+
+def test_rate_kats(gpu, oracle):
+    got, want = kat.rate_kats(gpu)
+    assert np.all(np.abs(got - want) / want < 1.0e-3)
+    # and against the oracle over the whole domain incl. both asymptotic branches
+    chi = np.logspace(-4, 3, 2000)
+    gamma = np.full_like(chi, 1234.5)
+    assert np.max(np.abs(gpu.rate(chi, gamma) / oracle.rate(chi, gamma) - 1.0)) < 1.0e-12
+
+
+def test_sample_matches_oracle(gpu, oracle):
+    rng = np.random.default_rng(7)
+    n = 20000
+    chi = 10.0 ** rng.uniform(-3.5, 1.9, n)
+    gamma = 10.0 ** rng.uniform(1.0, 4.0, n)
+    r1, r2, r3 = rng.random(n), rng.random(n), rng.random(n)
+    for classical in (False, True):
+        a = gpu.sample(chi, gamma, r1, r2, r3, classical)
+        b = oracle.sample(chi, gamma, r1, r2, r3, classical)
+        # same uniforms -> same photon: the inverse-CDF search stops on a 1e-6 relative criterion
+        # (pwmci.rs:4) so ulp-level libm differences can flip one last iteration
+        rel = np.abs(a - b) / np.maximum(np.abs(b), 1e-300)
+        assert np.quantile(rel[:, 0], 0.999) < 1.0e-9
+        assert np.max(rel[:, 0]) < 1.0e-5
+        assert np.max(np.abs(a[:, 1] - b[:, 1])) < 1.0e-5 * np.max(np.abs(b[:, 1]))
+        assert np.max(rel[:, 2]) < 1.0e-14

@@ -1,0 +1,201 @@
+"""Parity of the CUDA path against the CPU oracle on identical seeded inputs (B200).
+
+Integer/index work (cell keys, per-cell counts, leaver counts, population sizes) is compared
+bit-exactly; x, u, E, B, j within 1e-10 relative per array (north_star's stated tolerance).
+"""
+import math
+
+import numpy as np
+import pytest
+
+from opal_b200.abi import (BDY_ABSORBING, BDY_INTERNAL, BDY_LASER, ELECTRON, FLAG_LEAN_STATE, FLAG_STRICT_FP, ION, PHOTON, Slab)
+from opal_b200.constants import ELECTRON_CHARGE, ELECTRON_MASS, SPEED_OF_LIGHT, VACUUM_PERMITTIVITY
+import pic_cases as pc
+
+pytestmark = pytest.mark.gpu
+C = SPEED_OF_LIGHT
+
+
+def _pair(gpu, oracle, nx, xmin, dx, left=BDY_INTERNAL, right=BDY_INTERNAL, flags=0):
+    a = Slab(gpu, nx, xmin, dx, None, left, right, flags=flags)
+    b = Slab(oracle, nx, xmin, dx, None, left, right)
+    return a, b
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_STRICT_FP])
+def test_two_stream_call_by_call(gpu, oracle, flags):
+    """BASELINE config 1 scaled down (two_stream.yaml): periodic, deposition on, QED off."""
+    nx, npc, dx = 200, 40, 500.0
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, flags=flags)
+    p = pc.two_stream_particles(nx, npc, dx, thermal=0.02)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    t = 0.0
+    for step in range(60):
+        for s in (a, b):
+            pc.step_by_calls(s, t, species=(ELECTRON,))
+        t += a.dt
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        if step in (0, 1, 9, 59):
+            pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "prev_x", "ux", "uy", "uz", "gamma", "y", "z"))
+            pc.compare_fields(a.fields(), b.fields())
+    ea, eb = a.energy(), b.energy()
+    assert abs(ea[0] - eb[0]) <= 1e-10 * abs(eb[0])
+    assert abs(ea[1] - eb[1]) <= 1e-10 * abs(eb[1])
+
+
+def test_strict_mode_is_bitwise_on_push(gpu, oracle):
+    """--fmad=false kernels reproduce the oracle's IEEE arithmetic exactly for one push in static fields."""
+    nx, npc, dx = 64, 30, 1.0e-7
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, flags=FLAG_STRICT_FP)
+    rng = np.random.default_rng(3)
+    f = a.fields()
+    f[:, 5:11] = rng.standard_normal((f.shape[0], 6)) * np.array([1e9, 1e9, 1e9, 1.0, 1.0, 1.0])
+    a.set_fields(f)
+    b.set_fields(f)
+    p = pc.thermal_particles(nx, npc, dx, 0.3, seed=5)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    a.advance(ELECTRON)
+    b.advance(ELECTRON)
+    da, db = pc.canon(a.download(ELECTRON)), pc.canon(b.download(ELECTRON))
+    for k in ("cell", "x", "prev_x", "ux", "uy", "uz", "gamma", "y", "z", "work"):
+        assert np.array_equal(da[k], db[k]), k
+    # chi and tau go through log/exp (libm vs CUDA math): a few ulp
+    assert pc.rel_inf(da["chi"], db["chi"]) < 1e-14
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_LEAN_STATE])
+def test_two_stream_fused_run_steps(gpu, oracle, flags):
+    """the fused push+deposit path (full and lean layouts) against the oracle's call-by-call loop"""
+    nx, npc, dx = 256, 64, 500.0
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, flags=flags)
+    p = pc.two_stream_particles(nx, npc, dx, thermal=0.03)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    done = 0
+    for chunk in (1, 4, 45):
+        a.run_steps(chunk, done * a.dt)
+        b.run_steps(chunk, done * b.dt)
+        done += chunk
+        fields = ("x", "ux", "uy", "uz") if flags & FLAG_LEAN_STATE else ("x", "prev_x", "ux", "uy", "uz", "gamma")
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=fields)
+        pc.compare_fields(a.fields(), b.fields())
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+    ea, eb = a.energy(), b.energy()
+    assert abs(ea[0] - eb[0]) <= 1e-9 * abs(eb[0])
+    assert abs(ea[1] - eb[1]) <= 1e-10 * abs(eb[1])
+
+
+def test_hole_boring_like(gpu, oracle):
+    """BASELINE config 2 scaled down: laser + absorbing boundaries, electrons + C6+ ions."""
+    micro = 1.0e-6
+    nx, dx = 600, 0.02 * micro
+    xmin = -4.0 * micro
+    a, b = _pair(gpu, oracle, nx, xmin, dx, BDY_LASER, BDY_ABSORBING)
+    omega = 2.0 * math.pi * C / (0.8 * micro)
+    a0 = 10.0
+    e0 = a0 * ELECTRON_MASS * C * omega / abs(ELECTRON_CHARGE)
+    ncrit = VACUUM_PERMITTIVITY * ELECTRON_MASS * omega ** 2 / ELECTRON_CHARGE ** 2
+    cells = np.arange(200, 500)                     # plasma slab 0 <= x < 6 um
+    u_th = math.sqrt(500.0 / 0.510999e6)
+    pe = pc.thermal_particles(nx, 20, dx, u_th, seed=11, ne=20.0 * ncrit, cells=cells)
+    pi = pc.thermal_particles(nx, 20, dx, 0.0, seed=12, ne=20.0 * ncrit / 6.0, cells=cells)
+    for s in (a, b):
+        s.set_ion(6.0, 12.0)
+        pc.upload(s, ELECTRON, pe)
+        pc.upload(s, ION, pi)
+
+    def ly(t, x):
+        phi = omega * (t - x / C)
+        return e0 * math.sin(phi) * math.exp(-(phi / (2 * math.pi * 4.0)) ** 2)
+
+    lz = lambda t, x: 0.0
+    t = -3.0 * micro / C
+    for step in range(400):
+        for s in (a, b):
+            pc.step_by_calls(s, t, laser=(ly, lz), species=(ELECTRON, ION))
+        t += a.dt
+        if step in (0, 99, 399):
+            pc.compare_fields(a.fields(), b.fields())
+            pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "prev_x", "ux", "uy", "uz", "gamma"))
+            pc.compare_particles(a.download(ION), b.download(ION), fields=("x", "prev_x", "ux", "uy", "uz", "gamma"))
+    ea, eb = a.energy(), b.energy()
+    for k in range(3):
+        assert abs(ea[k] - eb[k]) <= 1e-9 * abs(eb[k]), (k, ea, eb)
+    assert ea[0] > 0 and ea[2] > 0
+
+
+def test_bucket_relayout_keeps_parity(gpu, oracle, monkeypatch):
+    """Tiny bucket slack forces re-layouts (parked movers, new capacities); results must not change."""
+    monkeypatch.setenv("OPAL_BUCKET_SLACK", "1.0")
+    monkeypatch.setenv("OPAL_BUCKET_PAD", "0")
+    nx, npc, dx = 96, 32, 500.0
+    a, b = _pair(gpu, oracle, nx, 0.0, dx)
+    p = pc.thermal_particles(nx, npc, dx, 0.4, seed=21)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    a.run_steps(25)
+    b.run_steps(25)
+    pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "prev_x", "ux", "uy", "uz"))
+    pc.compare_fields(a.fields(), b.fields())
+    assert a.count(ELECTRON) == nx * npc
+
+
+def test_open_boundaries_delete_leavers(gpu, oracle):
+    nx, dx = 300, 1.0e-8
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, BDY_LASER, BDY_ABSORBING)
+    p = pc.thermal_particles(nx, 10, dx, 2.0, seed=31, ne=1.0e20)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for step in range(40):
+        for s in (a, b):
+            pc.step_by_calls(s, step * s.dt, species=(ELECTRON,))
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+    assert a.count(ELECTRON) == b.count(ELECTRON) < nx * 10
+    pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON))
+    pc.compare_fields(a.fields(), b.fields())
+
+
+def test_photon_push(gpu, oracle):
+    nx, dx = 128, 1.0e-8
+    a, b = _pair(gpu, oracle, nx, 0.0, dx)
+    rng = np.random.default_rng(41)
+    f = a.fields()
+    f[:, 5:11] = rng.standard_normal((f.shape[0], 6)) * np.array([1e12, 1e12, 1e12, 1e3, 1e3, 1e3])
+    a.set_fields(f)
+    b.set_fields(f)
+    n = 5000
+    k = rng.standard_normal((n, 3)) * 100.0
+    cell = rng.integers(0, nx, n)
+    w = 1.0 + 1e-9 * np.arange(n)
+    for s in (a, b):
+        s.upload(PHOTON, cell, rng.random(n) * 0 + np.linspace(0.0, 0.999, n), k[:, 0], k[:, 1], k[:, 2], w)
+    for _ in range(30):
+        a.advance(PHOTON)
+        b.advance(PHOTON)
+        assert a.last_leavers(PHOTON) == b.last_leavers(PHOTON)
+    pc.compare_particles(a.download(PHOTON), b.download(PHOTON), fields=("x", "prev_x", "ux", "uy", "uz", "chi", "y", "z"))
+    assert abs(a.energy()[3] - b.energy()[3]) <= 1e-12 * b.energy()[3]
+
+
+def test_generator_roundtrip_and_lean_run(gpu, oracle):
+    """device-generated thermal plasma (the bench workload, scaled down) -> download -> oracle."""
+    nx, npc, dx = 512, 100, 500.0
+    a = Slab(gpu, nx, 0.0, dx, flags=FLAG_LEAN_STATE)
+    b = Slab(oracle, nx, 0.0, dx)
+    a.generate(ELECTRON, npc, 20.0 * dx / npc, u_th=(0.03128,) * 3)
+    d = a.download(ELECTRON, fields=("cell", "x", "ux", "uy", "uz", "weight"))
+    assert d["cell"].size == nx * npc and np.all(np.bincount(d["cell"], minlength=nx) == npc)
+    assert abs(np.std(d["ux"]) / 0.03128 - 1.0) < 0.02 and abs(np.mean(d["x"]) - 0.5) < 0.01
+    b.upload(ELECTRON, d["cell"], d["x"], d["ux"], d["uy"], d["uz"], d["weight"])
+    a.run_steps(20)
+    b.run_steps(20)
+    da = a.download(ELECTRON, fields=("cell", "x", "ux", "uy", "uz", "weight"))
+    db = b.download(ELECTRON, fields=("cell", "x", "ux", "uy", "uz", "weight"))
+    # identical weights here: match on (cell, x)
+    oa, ob = np.lexsort((da["x"], da["cell"])), np.lexsort((db["x"], db["cell"]))
+    assert np.array_equal(da["cell"][oa], db["cell"][ob])
+    for k in ("x", "ux", "uy", "uz"):
+        assert pc.rel_inf(da[k][oa], db[k][ob]) < 1e-10, k
+    pc.compare_fields(a.fields(), b.fields())
