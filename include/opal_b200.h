@@ -188,6 +188,12 @@ opal_status OPAL_FN(comm_init)(opal_ctx*, const void* id128);     /* ncclCommIni
 opal_status OPAL_FN(stream)(opal_ctx*, void** cuda_stream);
 /* number of kernels this context has launched so far */
 opal_status OPAL_FN(launch_count)(opal_ctx*, int64_t* n);
+/* per-kernel device timing: timing(1) makes the context bracket every launch of the three step
+   kernels with cudaEvents on its stream; kernel_times() synchronises and returns the summed
+   durations [ms] and launch counts for {0: gather+push(+deposit), 1: mover scatter, 2: halo/BC +
+   field update} since timing was enabled.                                                      */
+opal_status OPAL_FN(timing)(opal_ctx*, int enable);
+opal_status OPAL_FN(kernel_times)(opal_ctx*, double ms3[3], int64_t launches3[3]);
 /* device-generated synthetic plasma (BASELINE configs 4/5): npc particles in every cell,
    x uniform in [0,1), u = drift[k]*sign + u_th[k]*N(0,1) from Philox4x32-10 keyed by
    (seed, global particle index) so any slab count yields the same global particle set;

@@ -3,7 +3,7 @@
 `OpalABI(cdll, prefix)` binds every entry point the header declares; `Slab` is one context
 (= one MPI rank of the reference = one x-slab on one GPU) with numpy in/out.  The product
 library is bound with prefix ``opal_`` (see `opal_b200.lib`); the test-suite binds the CPU
-oracle with prefix ``opal_ref_`` through the same class, so parity tests drive both through
+oracle (its own prefix) through the same class, so parity tests drive both through
 identical code.  Nothing in this module knows about the oracle.
 """
 from __future__ import annotations
@@ -64,6 +64,8 @@ SIGNATURES = {
     "comm_init": [_vp, _vp],
     "stream": [_vp, C.POINTER(_vp)],
     "launch_count": [_vp, _pi64],
+    "timing": [_vp, _int],
+    "kernel_times": [_vp, _vp, _vp],
     "particles_generate": [_vp, _int, _i64, _f64, _vp, _vp, _int, _i64, _u64],
     "qed_rate": [_i64, _vp, _vp, _vp],
     "qed_sample": [_i64, _vp, _vp, _vp, _vp, _vp, _int, _vp],
@@ -290,6 +292,14 @@ class Slab:
         n = C.c_int64()
         self._ck(self.abi.launch_count(self._h, C.byref(n)), "launch_count")
         return n.value
+
+    def timing(self, enable=True):
+        self._ck(self.abi.timing(self._h, int(enable)), "timing")
+
+    def kernel_times(self):
+        ms, n = np.zeros(3), np.zeros(3, dtype=np.int64)
+        self._ck(self.abi.kernel_times(self._h, _ptr(ms), _ptr(n)), "kernel_times")
+        return {"push": (ms[0], int(n[0])), "scatter": (ms[1], int(n[1])), "field": (ms[2], int(n[2]))}
 
     def generate(self, species, npc, weight, u_th=(0.0, 0.0, 0.0), drift=(0.0, 0.0, 0.0), two_stream=False,
                  global_cell_offset=0, seed=12345):

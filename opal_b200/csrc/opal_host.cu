@@ -11,6 +11,7 @@
 #include <dlfcn.h>
 #include <limits>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "opal_types.h"
@@ -106,6 +107,10 @@ struct opal_ctx {
     uint64_t emit_calls = 0;
     int64_t launches = 0;
     ncclComm_t comm = nullptr;
+    // optional per-kernel timing (opal_timing): event pairs per category
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev[3];
+    size_t ev_used[3] = {0, 0, 0};
     int status = OPAL_OK;
     std::string err;
     double slack = 1.25; int pad = 64;
@@ -323,6 +328,22 @@ bool nccl_exchange(opal_ctx* c, void* send_l, void* send_r, void* recv_l, void* 
     return true;
 }
 
+struct Timed {   // RAII bracket of one launch with a cudaEvent pair when timing is on
+    opal_ctx* c; int cat; cudaEvent_t stop = nullptr;
+    Timed(opal_ctx* c_, int cat_) : c(c_), cat(cat_) {
+        if (!c->timing) return;
+        if (c->ev_used[cat] == c->ev[cat].size()) {
+            cudaEvent_t a, b;
+            cudaEventCreate(&a); cudaEventCreate(&b);
+            c->ev[cat].push_back({a, b});
+        }
+        auto& p = c->ev[cat][c->ev_used[cat]++];
+        cudaEventRecord(p.first, c->stream);
+        stop = p.second;
+    }
+    ~Timed() { if (stop) cudaEventRecord(stop, c->stream); }
+};
+
 bool remote(opal_ctx* c) { return !c->self_nbr() && (c->has_left() || c->has_right()); }
 
 // insert what the neighbours sent (d_in[side], header + records) into species `sp`
@@ -347,9 +368,9 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check) {
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
     if (!reset_status(c, true)) return false;
     StepParams p = sparams(c, sp);
-    c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_status); c->launches++;
-    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
-                 reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
+    { Timed tm(c, 0); c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_status); c->launches++; }
+    { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                 reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++; }
     if (remote(c)) {
         k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status); c->launches++;
         if (c->comm) {
@@ -421,11 +442,12 @@ bool do_sync(opal_ctx* c, double ly, double lz) {
         halo = c->d_halo_recv;
         c->halo_given[0] = c->halo_given[1] = false;
     }
-    c->k.sync_bc(c->stream, c->g, halo, ly, lz, nullptr); c->launches++;
+    { Timed tm(c, 2); c->k.sync_bc(c->stream, c->g, halo, ly, lz, nullptr); c->launches++; }
     return true;
 }
 
 void do_field(opal_ctx* c) {
+    Timed tm(c, 2);
     GridDev nxt = c->g;
     nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
     c->k.field(c->stream, c->g, nxt, false); c->launches++;
@@ -496,6 +518,7 @@ opal_status opal_destroy(opal_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (int k = 0; k < 3; k++) for (auto& p : c->ev[k]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (int s = 0; s < 2; s++) free_buckets(c->bk[s]);
     for (int w = 0; w < 2; w++) {
         if (c->ph[w].d_n) cudaFree(c->ph[w].d_n);
@@ -947,6 +970,30 @@ opal_status opal_comm_init(opal_ctx* c, const void* id128) {
 opal_status opal_stream(opal_ctx* c, void** s) {
     if (!c || !s) return OPAL_EINVAL;
     *s = (void*)c->stream;
+    return OPAL_OK;
+}
+
+opal_status opal_timing(opal_ctx* c, int enable) {
+    CHECK_CTX(c);
+    CU(cudaStreamSynchronize(c->stream));
+    c->timing = enable != 0;
+    for (int k = 0; k < 3; k++) c->ev_used[k] = 0;
+    return OPAL_OK;
+}
+
+opal_status opal_kernel_times(opal_ctx* c, double ms3[3], int64_t launches3[3]) {
+    CHECK_CTX(c);
+    if (!ms3 || !launches3) return OPAL_EINVAL;
+    CU(cudaStreamSynchronize(c->stream));
+    for (int k = 0; k < 3; k++) {
+        double total = 0.0;
+        for (size_t i = 0; i < c->ev_used[k]; i++) {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, c->ev[k][i].first, c->ev[k][i].second));
+            total += ms;
+        }
+        ms3[k] = total; launches3[k] = (int64_t)c->ev_used[k];
+    }
     return OPAL_OK;
 }
 

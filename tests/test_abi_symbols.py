@@ -1,0 +1,64 @@
+"""CPU-side checks of the drop-in boundary: the header, the ctypes table and both shared
+libraries agree on the exported entry points (no compute calls -- there is no GPU here)."""
+import ctypes
+import pathlib
+import re
+import subprocess
+
+import pytest
+
+from opal_b200 import abi
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+HEADER = (ROOT / "include" / "opal_b200.h").read_text()
+
+
+def declared():
+    return sorted(set(re.findall(r"OPAL_FN\((\w+)\)\s*\(", HEADER)) - {"name"})
+
+
+def test_header_and_binding_table_agree():
+    assert declared() == sorted(abi.SIGNATURES)
+
+
+def test_header_compiles_as_c99(tmp_path):
+    src = tmp_path / "t.c"
+    src.write_text('#include "opal_b200.h"\nint main(void){ return sizeof(opal_migrant) == 128 ? 0 : 1; }\n')
+    exe = tmp_path / "t"
+    subprocess.check_call(["/usr/bin/gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", f"-I{ROOT / 'include'}", str(src), "-o", str(exe)])
+    assert subprocess.call([str(exe)]) == 0
+
+
+def test_product_library_exports_every_symbol():
+    so = ROOT / "opal_b200" / "csrc" / "libopal_b200.so"
+    if not so.exists():
+        subprocess.check_call(["make", "-C", str(so.parent)], stdout=subprocess.DEVNULL)
+    lib = ctypes.CDLL(str(so))
+    for name in declared():
+        assert hasattr(lib, "opal_" + name), name
+    # binding the whole table must succeed too (argtypes/restype set on every entry point)
+    abi.OpalABI(lib, "opal_")
+
+
+def test_product_has_no_cpu_fallback():
+    """Without a CUDA device opal_create must fail with OPAL_ECUDA, not compute on the host."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from opal_b200 import lib
+    a = lib.load()
+    h = ctypes.c_void_p()
+    assert a.create(ctypes.byref(h), 0, 64, 0.0, 1.0, 1e-9, 0, 0, 0, 1, 0, 0) == abi.ECUDA
+    with pytest.raises(abi.OpalError):
+        abi.Slab(a, 64, 0.0, 1.0)
+
+
+def test_product_never_references_the_oracle():
+    for path in list((ROOT / "opal_b200").rglob("*.py")) + list((ROOT / "opal_b200" / "csrc").glob("*.cu")) + list((ROOT / "opal_b200" / "csrc").glob("*.h")):
+        text = path.read_text()
+        assert "opal_ref_" not in text and "libopal_oracle" not in text, path
+
+
+def test_oracle_exports_every_symbol(oracle_cdll):
+    for name in declared():
+        assert hasattr(oracle_cdll, "opal_ref_" + name), name

@@ -112,14 +112,30 @@ def test_hole_boring_like(gpu, oracle):
 
     lz = lambda t, x: 0.0
     t = -3.0 * micro / C
+    efields = ("x", "prev_x", "ux", "uy", "uz", "gamma")
     for step in range(400):
+        if step in (100, 250, 399):
+            # Per-step parity in the developed (strongly driven, chaotic) state: restart BOTH sides
+            # from the oracle's current state, take one step, compare at 1e-10.  (Round-off-level
+            # differences in summation order grow exponentially in a laser-driven plasma, so the
+            # free-running comparison below uses the drift tolerance instead.)
+            fo = b.fields()
+            do_e, do_i = b.download(ELECTRON), b.download(ION)
+            for s in (a, b):
+                s.set_fields(fo)
+                s.upload(ELECTRON, do_e["cell"], do_e["x"], do_e["ux"], do_e["uy"], do_e["uz"], do_e["weight"])
+                s.upload(ION, do_i["cell"], do_i["x"], do_i["ux"], do_i["uy"], do_i["uz"], do_i["weight"])
         for s in (a, b):
             pc.step_by_calls(s, t, laser=(ly, lz), species=(ELECTRON, ION))
         t += a.dt
-        if step in (0, 99, 399):
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        if step in (0, 100, 250, 399):
             pc.compare_fields(a.fields(), b.fields())
-            pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "prev_x", "ux", "uy", "uz", "gamma"))
-            pc.compare_particles(a.download(ION), b.download(ION), fields=("x", "prev_x", "ux", "uy", "uz", "gamma"))
+            pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=efields)
+            pc.compare_particles(a.download(ION), b.download(ION), fields=efields)
+        elif step in (50, 99, 249, 398):
+            # free-running for up to 150 steps since the last common state: no drift beyond 1e-5
+            pc.compare_fields(a.fields(), b.fields(), tol=1e-5)
     ea, eb = a.energy(), b.energy()
     for k in range(3):
         assert abs(ea[k] - eb[k]) <= 1e-9 * abs(eb[k]), (k, ea, eb)
