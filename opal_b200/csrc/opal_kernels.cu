@@ -211,6 +211,162 @@ __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepPara
     if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
 }
 
+#ifdef OPAL_FAST
+// --------------------------------------------------------------------------------------------
+// K1f: the headline kernel -- electrons, lean (x, u, w) layout, fused gather + Vay push + deposit,
+// fast build only.  Same mathematics as k_push<ELECTRON,false,true>, reorganised for the FP64
+// pipe (which, not HBM, bounds this kernel -- see DESIGN.md):
+//   * the order-2 spline is evaluated through R(d), the fraction of the particle's triangle to the
+//     right of a face at displacement d:  W(node j) = R(j-1/2-x) - R(j+1/2-x) and
+//     Cell::flux(x_i, x_f) = R(x_f) - R(x_i)  (verified to 3e-16 against yee.rs:140-204), so the 7
+//     gather weights, the 3 non-zero fluxes of a stayer and the 4 deposit weights come from three
+//     R values per position instead of 7 + 5 + 4 branchy evaluations;
+//   * every division by gamma, dt, dx becomes a multiplication by a reciprocal (rsqrt for 1/gamma);
+//     the per-particle factors q/dt, q/dx, q c/dx are applied once per CELL after the reduction.
+// Results differ from the literal formulas only by re-association (<= 1e-15 relative), far inside the
+// 1e-10 parity tolerance; the strict build keeps the literal arithmetic.
+// --------------------------------------------------------------------------------------------
+struct RFaces { double a, b, c; };   // R at the faces -1/2, +1/2, +3/2 of the particle's cell
+__device__ __forceinline__ RFaces r_faces(double x) {
+    const double h = x - 0.5, q = 0.5 * (h * h);
+    const double hp = 1.0 + h, hm = 1.0 - h;
+    const bool lo = x < 0.5;
+    RFaces r;
+    r.a = lo ? 1.0 - q : 1.0;
+    r.b = lo ? 0.5 * (hp * hp) : 1.0 - 0.5 * (hm * hm);
+    r.c = lo ? 0.0 : q;
+    return r;
+}
+
+__global__ void __launch_bounds__(BLOCK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
+                                                           int* __restrict__ seg_count, StatusDev* __restrict__ st) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int warps_total = gridDim.x * WARPS_PER_BLOCK;
+    const double alpha = OPAL_QE * g.dt / (2.0 * OPAL_ME * OPAL_C);
+    const double ac = alpha * OPAL_C;
+    const double kdt = OPAL_C * g.dt / g.dx;
+    bool cfl = false, cap_err = false;
+    double* const fx = b.f[F_X]; double* const fux = b.f[F_UX]; double* const fuy = b.f[F_UY]; double* const fuz = b.f[F_UZ];
+    double* const fw = b.f[F_W];
+
+    for (int c = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
+        const int n = b.count[c];
+        if (n == 0) continue;
+        const long long base = b.start[c];
+        const int j = c + g.left;
+        CellFields cf;
+        load_cell_fields(g, j, cf);
+        const V3 tau = {ac * cf.bx, 0.0, 0.0};   // x component only: By, Bz vary with the particle
+        double sjx0 = 0.0, sjx1 = 0.0, sjx2 = 0.0, sjy0 = 0.0, sjy1 = 0.0, sjy2 = 0.0, sjz0 = 0.0, sjz1 = 0.0, sjz2 = 0.0;
+        double sr0 = 0.0, sr1 = 0.0, sr2 = 0.0, sr3 = 0.0;
+
+        double nx0 = 0.0, nx1 = 0.0, nx2 = 0.0, nx3 = 0.0, nx4 = 0.0;
+        if (lane < n) { const long long s = base + lane; nx0 = fx[s]; nx1 = fux[s]; nx2 = fuy[s]; nx3 = fuz[s]; nx4 = fw[s]; }
+        int written = 0;
+        for (int k0 = 0; k0 < n; k0 += 32) {
+            const int i = k0 + lane;
+            const bool valid = i < n;
+            const double x = nx0, W = nx4;
+            V3 u = {nx1, nx2, nx3};
+            {
+                const int in = i + 32;
+                if (in < n) { const long long s = base + in; nx0 = fx[s]; nx1 = fux[s]; nx2 = fuy[s]; nx3 = fuz[s]; nx4 = fw[s]; }
+            }
+            // ---- gather (yee.rs:499-529) ----
+            const RFaces ro = r_faces(x);
+            const double wn0 = 1.0 - ro.a, wn1 = ro.a - ro.b, wn2 = ro.b - ro.c, wn3 = ro.c;
+            const double xm = 1.0 - x;
+            const double wc0 = 0.5 * (xm * xm), wc2 = 0.5 * (x * x), wc1 = (1.0 - wc0) - wc2;
+            V3 E, B;
+            E.x = cf.ex[0] * wc0 + cf.ex[1] * wc1 + cf.ex[2] * wc2;
+            E.y = cf.ey[0] * wn0 + cf.ey[1] * wn1 + cf.ey[2] * wn2 + cf.ey[3] * wn3;
+            E.z = cf.ez[0] * wn0 + cf.ez[1] * wn1 + cf.ez[2] * wn2 + cf.ez[3] * wn3;
+            B.x = cf.bx;
+            B.y = cf.by[0] * wc0 + cf.by[1] * wc1 + cf.by[2] * wc2;
+            B.z = cf.bz[0] * wc0 + cf.bz[1] * wc1 + cf.bz[2] * wc2;
+            // ---- Vay push (electron.rs:268-330) ----
+            const double ig = rsqrt(1.0 + dot(u, u));
+            const V3 v = (OPAL_C * ig) * u;
+            const V3 u_half = u + alpha * (E + cross(v, B));
+            const V3 u_prime = u_half + alpha * E;
+            const double gp2 = 1.0 + dot(u_prime, u_prime);
+            const V3 tv = {tau.x, ac * B.y, ac * B.z};
+            const double u_star = dot(u_prime, tv);
+            const double tau2 = dot(tv, tv);
+            const double sigma = gp2 - tau2;
+            const double gam2 = 0.5 * sigma + sqrt(0.25 * (sigma * sigma) + tau2 + u_star * u_star);
+            const double igam = rsqrt(gam2);
+            const V3 t = igam * tv;
+            const double s_ = 1.0 / (1.0 + dot(t, t));
+            u = s_ * (u_prime + dot(u_prime, t) * t + cross(u_prime, t));
+            const double dxi = kdt * u.x * igam;
+            if (valid && !(dxi < 1.0)) cfl = true;
+            double xn = x + dxi;
+            const double fl = floor(xn);
+            const int d = fl < 0.0 ? -1 : (fl > 0.0 ? 1 : 0);
+            xn -= fl;
+
+            const bool stay = valid && d == 0;
+            const bool move = valid && d != 0;
+            const unsigned m_stay = __ballot_sync(FULLMASK, stay);
+            const unsigned m_move = __ballot_sync(FULLMASK, move);
+            int mbase = 0;
+            const int seg = c & (OPAL_MOVER_SEGMENTS - 1);
+            if (m_move) {
+                const int leader = __ffs(m_move) - 1;
+                if (lane == leader) mbase = atomicAdd(seg_count + seg, __popc(m_move));
+                mbase = __shfl_sync(FULLMASK, mbase, leader);
+            }
+            if (stay) {
+                const int pos = written + __popc(m_stay & lt_mask);
+                const long long s = base + pos;
+                fx[s] = xn; fux[s] = u.x; fuy[s] = u.y; fuz[s] = u.z;
+                if (pos != i) fw[s] = W;
+                // ---- deposit of a stayer (yee.rs:584-609) ----
+                const RFaces rn = r_faces(xn);
+                sjx0 += W * (rn.a - ro.a); sjx1 += W * (rn.b - ro.b); sjx2 += W * (rn.c - ro.c);
+                const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
+                sr0 += W * w3; sr1 += W * w0; sr2 += W * w1; sr3 += W * w2;
+                const double tw = W * igam, ty = tw * u.y, tz = tw * u.z;
+                sjy0 += ty * w0; sjy1 += ty * w1; sjy2 += ty * w2;
+                sjz0 += tz * w0; sjz1 += tz * w1; sjz2 += tz * w2;
+            }
+            if (move) {
+                const int r = mbase + __popc(m_move & lt_mask);
+                if (r < sp.mover_cap) {
+                    opal_migrant m;
+                    m.cell = (long long)c + d; m.x = xn; m.prev_x = x - fl; m.u[0] = u.x; m.u[1] = u.y; m.u[2] = u.z; m.weight = W;
+                    m.gamma = gam2 * igam; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0;
+                    m.pad[0] = 0.0; m.pad[1] = 0.0;
+                    movers[(long long)seg * sp.mover_cap + r] = m;
+                } else cap_err = true;
+            }
+            written += __popc(m_stay);
+        }
+        if (lane == 0) b.count[c] = written;
+
+        const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
+        double v13[13] = {kx * sjx0, kx * sjx1, kx * sjx2, ky * sjy0, ky * sjy1, ky * sjy2, ky * sjz0, ky * sjz1, ky * sjz2,
+                          kr * sr0, kr * sr1, kr * sr2, kr * sr3};
+#pragma unroll
+        for (int k = 0; k < 13; k++) v13[k] = warp_sum(v13[k]);
+        double mine = 0.0;
+        double* dst = nullptr;
+#pragma unroll
+        for (int k = 0; k < 13; k++) {
+            if (lane == k) {
+                mine = v13[k];
+                dst = k < 3 ? g.jx + j - 1 + k : (k < 6 ? g.jy + j - 1 + (k - 3) : (k < 9 ? g.jz + j - 1 + (k - 6) : g.rho + j - 2 + (k - 9)));
+            }
+        }
+        if (dst && mine != 0.0) atomicAdd(dst, mine);
+    }
+    if (cfl) atomicOr(&st->err, ERR_CFL);
+    if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
+}
+#endif  // OPAL_FAST
+
 // ============================================================================================
 // K2: scatter of boundary-crossing particles: local movers of K1, migrants received from a
 //     neighbour slab, or the retry list after a re-layout.  Routes slab leavers (periodic wrap /
@@ -1039,6 +1195,9 @@ static void l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     // the per-segment counters live directly behind the StatusDev block (see host: status + seg counters)
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
+#ifdef OPAL_FAST
+    if (sp.species == OPAL_ELECTRON && !full && dep) { k_push_lean_fast<<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st); return; }
+#endif
 #define LAUNCH(SP, F, D) k_push<SP, F, D><<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st)
     if (sp.species == OPAL_ELECTRON) {
         if (full) { if (dep) LAUNCH(OPAL_ELECTRON, true, true); else LAUNCH(OPAL_ELECTRON, true, false); }
