@@ -238,11 +238,17 @@ __device__ __forceinline__ RFaces r_faces(double x) {
     return r;
 }
 
-__global__ void __launch_bounds__(BLOCK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
+#ifndef OPAL_PUSH_WPB
+#define OPAL_PUSH_WPB 4
+#endif
+#ifndef OPAL_PUSH_MINBLK
+#define OPAL_PUSH_MINBLK 3
+#endif
+__global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StatusDev* __restrict__ st) {
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
-    const int warps_total = gridDim.x * WARPS_PER_BLOCK;
+    const int warps_total = gridDim.x * OPAL_PUSH_WPB;
     const double alpha = OPAL_QE * g.dt / (2.0 * OPAL_ME * OPAL_C);
     const double ac = alpha * OPAL_C;
     const double kdt = OPAL_C * g.dt / g.dx;
@@ -250,7 +256,7 @@ __global__ void __launch_bounds__(BLOCK) k_push_lean_fast(GridDev g, BucketDev b
     double* const fx = b.f[F_X]; double* const fux = b.f[F_UX]; double* const fuy = b.f[F_UY]; double* const fuz = b.f[F_UZ];
     double* const fw = b.f[F_W];
 
-    for (int c = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
+    for (int c = blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
         const int n = b.count[c];
         if (n == 0) continue;
         const long long base = b.start[c];
@@ -1196,7 +1202,11 @@ static void l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
-    if (sp.species == OPAL_ELECTRON && !full && dep) { k_push_lean_fast<<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st); return; }
+    if (sp.species == OPAL_ELECTRON && !full && dep) {
+        long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
+        k_push_lean_fast<<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, st);
+        return;
+    }
 #endif
 #define LAUNCH(SP, F, D) k_push<SP, F, D><<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st)
     if (sp.species == OPAL_ELECTRON) {

@@ -19,8 +19,9 @@ _abi = None
 def load() -> OpalABI:
     global _abi
     if _abi is None:
-        if not LIB_PATH.exists():
-            raise RuntimeError(f"{LIB_PATH} not built: run `make -C {_HERE / 'csrc'}` "
+        path = pathlib.Path(os.environ.get("OPAL_B200_LIB", LIB_PATH))   # development: alternative builds
+        if not path.exists():
+            raise RuntimeError(f"{path} not built: run `make -C {_HERE / 'csrc'}` "
                                "(or python -c 'import __graft_entry__ as g; g.build()'); there is no CPU fallback")
-        _abi = OpalABI(ctypes.CDLL(os.fspath(LIB_PATH), mode=ctypes.RTLD_GLOBAL), "opal_")
+        _abi = OpalABI(ctypes.CDLL(os.fspath(path), mode=ctypes.RTLD_GLOBAL), "opal_")
     return _abi
