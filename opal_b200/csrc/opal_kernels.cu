@@ -241,11 +241,19 @@ __device__ __forceinline__ RFaces r_faces(double x) {
 #ifndef OPAL_PUSH_WPB
 #define OPAL_PUSH_WPB 4
 #endif
+#ifndef OPAL_PUSH_SMEM_FIELDS
+#define OPAL_PUSH_SMEM_FIELDS 1
+#endif
+#ifndef OPAL_PUSH_ILP
+#define OPAL_PUSH_ILP 1
+#endif
 #ifndef OPAL_PUSH_MINBLK
-#define OPAL_PUSH_MINBLK 3
+#define OPAL_PUSH_MINBLK 4
 #endif
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StatusDev* __restrict__ st) {
+    constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
+    constexpr int CH = 32 * ILP;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * OPAL_PUSH_WPB;
@@ -261,97 +269,133 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         if (n == 0) continue;
         const long long base = b.start[c];
         const int j = c + g.left;
+#if OPAL_PUSH_SMEM_FIELDS
+        // the 18 field values every lane of this warp gathers from: one copy per warp in shared memory
+        __shared__ CellFields s_cf[OPAL_PUSH_WPB];
+        CellFields& cf = s_cf[threadIdx.x >> 5];
+        __syncwarp();
+        if (lane < 3) { cf.ex[lane] = __ldg(g.ex + j - 1 + lane); cf.by[lane] = __ldg(g.by + j - 1 + lane); cf.bz[lane] = __ldg(g.bz + j - 1 + lane); }
+        if (lane < 4) { cf.ey[lane] = __ldg(g.ey + j - 1 + lane); cf.ez[lane] = __ldg(g.ez + j - 1 + lane); }
+        if (lane == 0) cf.bx = __ldg(g.bx + j);
+        __syncwarp();
+#else
         CellFields cf;
         load_cell_fields(g, j, cf);
-        const V3 tau = {ac * cf.bx, 0.0, 0.0};   // x component only: By, Bz vary with the particle
+#endif
+        const double taux = ac * cf.bx;
         double sjx0 = 0.0, sjx1 = 0.0, sjx2 = 0.0, sjy0 = 0.0, sjy1 = 0.0, sjy2 = 0.0, sjz0 = 0.0, sjz1 = 0.0, sjz2 = 0.0;
         double sr0 = 0.0, sr1 = 0.0, sr2 = 0.0, sr3 = 0.0;
 
-        double nx0 = 0.0, nx1 = 0.0, nx2 = 0.0, nx3 = 0.0, nx4 = 0.0;
-        if (lane < n) { const long long s = base + lane; nx0 = fx[s]; nx1 = fux[s]; nx2 = fuy[s]; nx3 = fuz[s]; nx4 = fw[s]; }
+        // software pipeline: the next iteration's loads are issued before this iteration's stores
+        double nx0[ILP], nx1[ILP], nx2[ILP], nx3[ILP], nx4[ILP];
+#pragma unroll
+        for (int q = 0; q < ILP; q++) {
+            nx0[q] = nx1[q] = nx2[q] = nx3[q] = nx4[q] = 0.0;
+            const int i = q * 32 + lane;
+            if (i < n) { const long long s = base + i; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
+        }
         int written = 0;
-        for (int k0 = 0; k0 < n; k0 += 32) {
-            const int i = k0 + lane;
-            const bool valid = i < n;
-            const double x = nx0, W = nx4;
-            V3 u = {nx1, nx2, nx3};
-            {
-                const int in = i + 32;
-                if (in < n) { const long long s = base + in; nx0 = fx[s]; nx1 = fux[s]; nx2 = fuy[s]; nx3 = fuz[s]; nx4 = fw[s]; }
+        for (int k0 = 0; k0 < n; k0 += CH) {
+            double x[ILP], W[ILP], xn[ILP], igam[ILP], gam2[ILP], fl[ILP];
+            V3 u[ILP];
+            RFaces ro[ILP];
+            int d[ILP];
+            bool valid[ILP];
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                x[q] = nx0[q]; u[q] = {nx1[q], nx2[q], nx3[q]}; W[q] = nx4[q];
+                valid[q] = k0 + q * 32 + lane < n;
             }
-            // ---- gather (yee.rs:499-529) ----
-            const RFaces ro = r_faces(x);
-            const double wn0 = 1.0 - ro.a, wn1 = ro.a - ro.b, wn2 = ro.b - ro.c, wn3 = ro.c;
-            const double xm = 1.0 - x;
-            const double wc0 = 0.5 * (xm * xm), wc2 = 0.5 * (x * x), wc1 = (1.0 - wc0) - wc2;
-            V3 E, B;
-            E.x = cf.ex[0] * wc0 + cf.ex[1] * wc1 + cf.ex[2] * wc2;
-            E.y = cf.ey[0] * wn0 + cf.ey[1] * wn1 + cf.ey[2] * wn2 + cf.ey[3] * wn3;
-            E.z = cf.ez[0] * wn0 + cf.ez[1] * wn1 + cf.ez[2] * wn2 + cf.ez[3] * wn3;
-            B.x = cf.bx;
-            B.y = cf.by[0] * wc0 + cf.by[1] * wc1 + cf.by[2] * wc2;
-            B.z = cf.bz[0] * wc0 + cf.bz[1] * wc1 + cf.bz[2] * wc2;
-            // ---- Vay push (electron.rs:268-330) ----
-            const double ig = rsqrt(1.0 + dot(u, u));
-            const V3 v = (OPAL_C * ig) * u;
-            const V3 u_half = u + alpha * (E + cross(v, B));
-            const V3 u_prime = u_half + alpha * E;
-            const double gp2 = 1.0 + dot(u_prime, u_prime);
-            const V3 tv = {tau.x, ac * B.y, ac * B.z};
-            const double u_star = dot(u_prime, tv);
-            const double tau2 = dot(tv, tv);
-            const double sigma = gp2 - tau2;
-            const double gam2 = 0.5 * sigma + sqrt(0.25 * (sigma * sigma) + tau2 + u_star * u_star);
-            const double igam = rsqrt(gam2);
-            const V3 t = igam * tv;
-            const double s_ = 1.0 / (1.0 + dot(t, t));
-            u = s_ * (u_prime + dot(u_prime, t) * t + cross(u_prime, t));
-            const double dxi = kdt * u.x * igam;
-            if (valid && !(dxi < 1.0)) cfl = true;
-            double xn = x + dxi;
-            const double fl = floor(xn);
-            const int d = fl < 0.0 ? -1 : (fl > 0.0 ? 1 : 0);
-            xn -= fl;
-
-            const bool stay = valid && d == 0;
-            const bool move = valid && d != 0;
-            const unsigned m_stay = __ballot_sync(FULLMASK, stay);
-            const unsigned m_move = __ballot_sync(FULLMASK, move);
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                const int in = k0 + CH + q * 32 + lane;
+                if (in < n) { const long long s = base + in; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
+            }
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                // ---- gather (yee.rs:499-529) ----
+                ro[q] = r_faces(x[q]);
+                const double wn0 = 1.0 - ro[q].a, wn1 = ro[q].a - ro[q].b, wn2 = ro[q].b - ro[q].c, wn3 = ro[q].c;
+                const double xm = 1.0 - x[q];
+                const double wc0 = 0.5 * (xm * xm), wc2 = 0.5 * (x[q] * x[q]), wc1 = (1.0 - wc0) - wc2;
+                V3 E, B;
+                E.x = cf.ex[0] * wc0 + cf.ex[1] * wc1 + cf.ex[2] * wc2;
+                E.y = cf.ey[0] * wn0 + cf.ey[1] * wn1 + cf.ey[2] * wn2 + cf.ey[3] * wn3;
+                E.z = cf.ez[0] * wn0 + cf.ez[1] * wn1 + cf.ez[2] * wn2 + cf.ez[3] * wn3;
+                B.x = cf.bx;
+                B.y = cf.by[0] * wc0 + cf.by[1] * wc1 + cf.by[2] * wc2;
+                B.z = cf.bz[0] * wc0 + cf.bz[1] * wc1 + cf.bz[2] * wc2;
+                // ---- Vay push (electron.rs:268-330) ----
+                const double ig = rsqrt(1.0 + dot(u[q], u[q]));
+                const V3 v = (OPAL_C * ig) * u[q];
+                const V3 u_half = u[q] + alpha * (E + cross(v, B));
+                const V3 u_prime = u_half + alpha * E;
+                const double gp2 = 1.0 + dot(u_prime, u_prime);
+                const V3 tv = {taux, ac * B.y, ac * B.z};
+                const double u_star = dot(u_prime, tv);
+                const double tau2 = dot(tv, tv);
+                const double sigma = gp2 - tau2;
+                gam2[q] = 0.5 * sigma + sqrt(0.25 * (sigma * sigma) + tau2 + u_star * u_star);
+                igam[q] = rsqrt(gam2[q]);
+                const V3 t = igam[q] * tv;
+                const double s_ = 1.0 / (1.0 + dot(t, t));
+                u[q] = s_ * (u_prime + dot(u_prime, t) * t + cross(u_prime, t));
+                const double dxi = kdt * u[q].x * igam[q];
+                if (valid[q] && !(dxi < 1.0)) cfl = true;
+                xn[q] = x[q] + dxi;
+                fl[q] = floor(xn[q]);
+                d[q] = fl[q] < 0.0 ? -1 : (fl[q] > 0.0 ? 1 : 0);
+                xn[q] -= fl[q];
+            }
+            unsigned m_stay[ILP], m_move[ILP];
+            int n_move = 0;
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                m_stay[q] = __ballot_sync(FULLMASK, valid[q] && d[q] == 0);
+                m_move[q] = __ballot_sync(FULLMASK, valid[q] && d[q] != 0);
+                n_move += __popc(m_move[q]);
+            }
+            // reserve mover slots early (one atomic per iteration that has movers, on one of
+            // OPAL_MOVER_SEGMENTS counters) so its latency overlaps the stayers' deposit below
             int mbase = 0;
             const int seg = c & (OPAL_MOVER_SEGMENTS - 1);
-            if (m_move) {
-                const int leader = __ffs(m_move) - 1;
-                if (lane == leader) mbase = atomicAdd(seg_count + seg, __popc(m_move));
-                mbase = __shfl_sync(FULLMASK, mbase, leader);
+            if (n_move) {
+                if (lane == 0) mbase = atomicAdd(seg_count + seg, n_move);
+                mbase = __shfl_sync(FULLMASK, mbase, 0);
             }
-            if (stay) {
-                const int pos = written + __popc(m_stay & lt_mask);
-                const long long s = base + pos;
-                fx[s] = xn; fux[s] = u.x; fuy[s] = u.y; fuz[s] = u.z;
-                if (pos != i) fw[s] = W;
-                // ---- deposit of a stayer (yee.rs:584-609) ----
-                const RFaces rn = r_faces(xn);
-                sjx0 += W * (rn.a - ro.a); sjx1 += W * (rn.b - ro.b); sjx2 += W * (rn.c - ro.c);
-                const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
-                sr0 += W * w3; sr1 += W * w0; sr2 += W * w1; sr3 += W * w2;
-                const double tw = W * igam, ty = tw * u.y, tz = tw * u.z;
-                sjy0 += ty * w0; sjy1 += ty * w1; sjy2 += ty * w2;
-                sjz0 += tz * w0; sjz1 += tz * w1; sjz2 += tz * w2;
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                const int i = k0 + q * 32 + lane;
+                if (valid[q] && d[q] == 0) {
+                    const int pos = written + __popc(m_stay[q] & lt_mask);
+                    const long long s = base + pos;
+                    fx[s] = xn[q]; fux[s] = u[q].x; fuy[s] = u[q].y; fuz[s] = u[q].z;
+                    if (pos != i) fw[s] = W[q];
+                    // ---- deposit of a stayer (yee.rs:584-609) ----
+                    const RFaces rn = r_faces(xn[q]);
+                    sjx0 += W[q] * (rn.a - ro[q].a); sjx1 += W[q] * (rn.b - ro[q].b); sjx2 += W[q] * (rn.c - ro[q].c);
+                    const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
+                    sr0 += W[q] * w3; sr1 += W[q] * w0; sr2 += W[q] * w1; sr3 += W[q] * w2;
+                    const double tw = W[q] * igam[q], ty = tw * u[q].y, tz = tw * u[q].z;
+                    sjy0 += ty * w0; sjy1 += ty * w1; sjy2 += ty * w2;
+                    sjz0 += tz * w0; sjz1 += tz * w1; sjz2 += tz * w2;
+                } else if (valid[q]) {
+                    const int r = mbase + __popc(m_move[q] & lt_mask);
+                    if (r < sp.mover_cap) {
+                        opal_migrant m;
+                        m.cell = (long long)c + d[q]; m.x = xn[q]; m.prev_x = x[q] - fl[q]; m.u[0] = u[q].x; m.u[1] = u[q].y; m.u[2] = u[q].z;
+                        m.weight = W[q]; m.gamma = gam2[q] * igam[q]; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0;
+                        m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                        movers[(long long)seg * sp.mover_cap + r] = m;
+                    } else cap_err = true;
+                }
+                written += __popc(m_stay[q]);
+                mbase += __popc(m_move[q]);
             }
-            if (move) {
-                const int r = mbase + __popc(m_move & lt_mask);
-                if (r < sp.mover_cap) {
-                    opal_migrant m;
-                    m.cell = (long long)c + d; m.x = xn; m.prev_x = x - fl; m.u[0] = u.x; m.u[1] = u.y; m.u[2] = u.z; m.weight = W;
-                    m.gamma = gam2 * igam; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0;
-                    m.pad[0] = 0.0; m.pad[1] = 0.0;
-                    movers[(long long)seg * sp.mover_cap + r] = m;
-                } else cap_err = true;
-            }
-            written += __popc(m_stay);
         }
         if (lane == 0) b.count[c] = written;
 
+        // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
         const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
         double v13[13] = {kx * sjx0, kx * sjx1, kx * sjx2, ky * sjy0, ky * sjy1, ky * sjy2, ky * sjz0, ky * sjz1, ky * sjz2,
                           kr * sr0, kr * sr1, kr * sr2, kr * sr3};
