@@ -90,6 +90,7 @@ struct opal_ctx {
     // exchange / mover buffers
     opal_migrant* d_movers = nullptr; int mover_seg_cap = 0;
     opal_migrant* d_overflow = nullptr;
+    StripRec* d_cmovers = nullptr; int* d_cmcount = nullptr; int cell_mover_cap = 0;   // per-cell left/right mover strips (lean electrons)
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
     opal_migrant* d_in[2] = {nullptr, nullptr};
     int out_cap = 0;
@@ -156,6 +157,7 @@ StepParams sparams(opal_ctx* c, int species) {
     sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap;
+    sp.cell_mover_cap = (species == OPAL_ELECTRON) ? c->cell_mover_cap : 0;
     return sp;
 }
 
@@ -200,6 +202,25 @@ bool ensure_movers(opal_ctx* c, long long n_particles) {
     CUB(cudaMalloc(&c->d_movers, (size_t)seg_cap * OPAL_MOVER_SEGMENTS * sizeof(opal_migrant)));
     CUB(cudaMalloc(&c->d_overflow, (size_t)seg_cap * sizeof(opal_migrant)));
     c->mover_seg_cap = (int)seg_cap;
+    return true;
+}
+
+// per-cell mover strips for the lean fused electron kernel: MC records per cell, sized for the expected
+// crossing fraction (thermal plasma at 0.95 CFL: a few % of a cell's particles per step)
+bool ensure_cell_movers(opal_ctx* c, long long n_particles) {
+    if (c->full || (c->flags & OPAL_FLAG_STRICT_FP)) return true;
+    const double ppc = (double)n_particles / (double)c->g.nx;
+    long long mc = (long long)std::ceil((env_double("OPAL_CELL_MOVER_FRACTION", 0.02) * ppc + 12.0) / 16.0) * 16;   // per direction
+    if (mc < 16) mc = 16;
+    if (mc > 256) mc = 256;
+    if (c->d_cmovers && mc <= c->cell_mover_cap) return true;
+    if (c->d_cmovers) cudaFree(c->d_cmovers);
+    if (c->d_cmcount) cudaFree(c->d_cmcount);
+    c->d_cmovers = nullptr; c->d_cmcount = nullptr;
+    CUB(cudaMalloc(&c->d_cmovers, (size_t)mc * 2 * c->g.nx * sizeof(StripRec)));
+    CUB(cudaMalloc(&c->d_cmcount, (size_t)2 * c->g.nx * sizeof(int)));
+    CUB(cudaMemset(c->d_cmcount, 0, (size_t)2 * c->g.nx * sizeof(int)));
+    c->cell_mover_cap = (int)mc;
     return true;
 }
 
@@ -368,7 +389,10 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check) {
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
     if (!reset_status(c, true)) return false;
     StepParams p = sparams(c, sp);
-    { Timed tm(c, 0); c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_status); c->launches++; }
+    bool strips = false;
+    { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status); c->launches++; }
+    if (strips) { Timed tm(c, 1); c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1,
+                 c->d_overflow, c->d_status); c->launches++; }
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++; }
     if (remote(c)) {
@@ -525,7 +549,7 @@ opal_status opal_destroy(opal_ctx* c) {
         if (c->ph[w].d_cell) cudaFree(c->ph[w].d_cell);
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
-    void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
+    void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_cmovers, c->d_cmcount, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
                      c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables};
     for (void* p : frees) if (p) cudaFree(p);
     if (c->h_status) cudaFreeHost(c->h_status);
@@ -594,6 +618,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = n;
     if (!ensure_movers(c, n)) return (opal_status)c->status;
+    if (species == OPAL_ELECTRON && !ensure_cell_movers(c, n)) return (opal_status)c->status;
     // host-side bucketing into the slot layout (stable: keeps the caller's order inside a cell)
     const int nf = c->full ? NF_FULL : NF_LEAN;
     std::vector<std::vector<double>> hf(nf, std::vector<double>((size_t)B.slots, 0.0));
@@ -634,6 +659,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = npc * (long long)c->g.nx;
     if (!ensure_movers(c, B.n_hint)) return (opal_status)c->status;
+    if (species == OPAL_ELECTRON && !ensure_cell_movers(c, B.n_hint)) return (opal_status)c->status;
     c->k.generate(c->stream, bdev(c, species), species, npc, weight, u_th, drift, two_stream, global_cell_offset, seed, c->full, c->g.dx, c->g.dt);
     c->launches++;
     CU(cudaStreamSynchronize(c->stream));

@@ -251,7 +251,8 @@ __device__ __forceinline__ RFaces r_faces(double x) {
 #define OPAL_PUSH_MINBLK 4
 #endif
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
-                                                           int* __restrict__ seg_count, StatusDev* __restrict__ st) {
+                                                           int* __restrict__ seg_count, StripRec* __restrict__ strips,
+                                                           int* __restrict__ scount, StatusDev* __restrict__ st) {
     constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
     constexpr int CH = 32 * ILP;
     const int lane = threadIdx.x & 31;
@@ -264,11 +265,13 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     double* const fx = b.f[F_X]; double* const fux = b.f[F_UX]; double* const fuy = b.f[F_UY]; double* const fuz = b.f[F_UZ];
     double* const fw = b.f[F_W];
 
+    const int MC = sp.cell_mover_cap;
     for (int c = blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
         const int n = b.count[c];
-        if (n == 0) continue;
+        if (n == 0) { if (lane < 2) scount[2 * c + lane] = 0; continue; }
         const long long base = b.start[c];
         const int j = c + g.left;
+        int mloc_l = 0, mloc_r = 0;   // left / right movers of this cell so far (warp-uniform): slots in its two strips
 #if OPAL_PUSH_SMEM_FIELDS
         // the 18 field values every lane of this warp gathers from: one copy per warp in shared memory
         __shared__ CellFields s_cf[OPAL_PUSH_WPB];
@@ -347,22 +350,28 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 d[q] = fl[q] < 0.0 ? -1 : (fl[q] > 0.0 ? 1 : 0);
                 xn[q] -= fl[q];
             }
-            unsigned m_stay[ILP], m_move[ILP];
-            int n_move = 0;
+            unsigned m_stay[ILP], m_l[ILP], m_r[ILP];
+            int n_l = 0, n_r = 0;
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
                 m_stay[q] = __ballot_sync(FULLMASK, valid[q] && d[q] == 0);
-                m_move[q] = __ballot_sync(FULLMASK, valid[q] && d[q] != 0);
-                n_move += __popc(m_move[q]);
+                m_l[q] = __ballot_sync(FULLMASK, valid[q] && d[q] < 0);
+                m_r[q] = __ballot_sync(FULLMASK, valid[q] && d[q] > 0);
+                n_l += __popc(m_l[q]); n_r += __popc(m_r[q]);
             }
-            // reserve mover slots early (one atomic per iteration that has movers, on one of
-            // OPAL_MOVER_SEGMENTS counters) so its latency overlaps the stayers' deposit below
-            int mbase = 0;
+            // Movers go to this cell's private left / right strip of MC records each (no atomics, no
+            // latency); only the excess beyond MC is appended to the shared segmented buffer.
+            int base_l = mloc_l, base_r = mloc_r;
+            int gbase = 0;
             const int seg = c & (OPAL_MOVER_SEGMENTS - 1);
-            if (n_move) {
-                if (lane == 0) mbase = atomicAdd(seg_count + seg, n_move);
-                mbase = __shfl_sync(FULLMASK, mbase, 0);
+            const int first_over_l = mloc_l > MC ? mloc_l : MC, first_over_r = mloc_r > MC ? mloc_r : MC;
+            const int over_l = mloc_l + n_l > first_over_l ? mloc_l + n_l - first_over_l : 0;
+            const int over_r = mloc_r + n_r > first_over_r ? mloc_r + n_r - first_over_r : 0;
+            if (over_l + over_r) {
+                if (lane == 0) gbase = atomicAdd(seg_count + seg, over_l + over_r);
+                gbase = __shfl_sync(FULLMASK, gbase, 0);
             }
+            mloc_l += n_l; mloc_r += n_r;
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
                 const int i = k0 + q * 32 + lane;
@@ -380,20 +389,31 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                     sjy0 += ty * w0; sjy1 += ty * w1; sjy2 += ty * w2;
                     sjz0 += tz * w0; sjz1 += tz * w1; sjz2 += tz * w2;
                 } else if (valid[q]) {
-                    const int r = mbase + __popc(m_move[q] & lt_mask);
-                    if (r < sp.mover_cap) {
-                        opal_migrant m;
-                        m.cell = (long long)c + d[q]; m.x = xn[q]; m.prev_x = x[q] - fl[q]; m.u[0] = u[q].x; m.u[1] = u[q].y; m.u[2] = u[q].z;
-                        m.weight = W[q]; m.gamma = gam2[q] * igam[q]; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0;
-                        m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
-                        movers[(long long)seg * sp.mover_cap + r] = m;
-                    } else cap_err = true;
+                    const bool left = d[q] < 0;
+                    const int r = left ? base_l + __popc(m_l[q] & lt_mask) : base_r + __popc(m_r[q] & lt_mask);
+                    const double gam = gam2[q] * igam[q], px = x[q] - fl[q];
+                    if (r < MC) {
+                        StripRec rec = {xn[q], px, u[q].x, u[q].y, u[q].z, W[q], gam, 0.0};
+                        strips[((long long)c * 2 + (left ? 0 : 1)) * MC + r] = rec;
+                    } else {
+                        const int rg = gbase + (left ? r - first_over_l : over_l + (r - first_over_r));
+                        if (rg < sp.mover_cap) {
+                            opal_migrant m;
+                            m.cell = (long long)c + d[q]; m.x = xn[q]; m.prev_x = px; m.u[0] = u[q].x; m.u[1] = u[q].y; m.u[2] = u[q].z;
+                            m.weight = W[q]; m.gamma = gam; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0;
+                            m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                            movers[(long long)seg * sp.mover_cap + rg] = m;
+                        } else cap_err = true;
+                    }
                 }
                 written += __popc(m_stay[q]);
-                mbase += __popc(m_move[q]);
+                base_l += __popc(m_l[q]); base_r += __popc(m_r[q]);
             }
         }
-        if (lane == 0) b.count[c] = written;
+        if (lane == 0) {
+            b.count[c] = written;
+            scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC;
+        }
 
         // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
         const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
@@ -414,6 +434,119 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
     if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
+}
+
+// K2p: pull.  One warp per DESTINATION cell c: it reads the right-mover strip of cell c-1 and the
+// left-mover strip of cell c+1 (all destined to c, |dxi| < 1), appends them to bucket c -- the
+// warp owns count[c], so no slot atomics -- and accumulates their deposit (yee.rs:584-609) in
+// registers: one shuffle reduction + <= 15 atomics per cell.  Edge cells route through the slab
+// boundary (mod.rs:290-373): periodic self-neighbour => the strips of the opposite edge; remote
+// neighbour => the edge strips are copied to the outbox here and arrive through the inbox path.
+__global__ void __launch_bounds__(256) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
+                                               const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
+                                               opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
+                                               StatusDev* __restrict__ st) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int warps_total = gridDim.x * 8;
+    const int MC = sp.cell_mover_cap;
+    const int nc = b.ncell;
+    for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < nc; c += warps_total) {
+        // source strips: right-movers of the left neighbour cell, left-movers of the right neighbour cell
+        int src_l = c - 1, src_r = c + 1;
+        if (src_l < 0) src_l = sp.route_left == 1 ? nc - 1 : -1;
+        if (src_r >= nc) src_r = sp.route_right == 1 ? 0 : -1;
+        const int n_from_l = src_l >= 0 ? scount[2 * src_l + 1] : 0;
+        const int n_from_r = src_r >= 0 ? scount[2 * src_r] : 0;
+        // leavers of the edge cells: counted (mod.rs:284) and, with a remote neighbour, sent
+        if (c == 0) {
+            const int n = scount[0];
+            if (lane == 0 && n) atomicAdd(&st->gone[0], n);
+            if (sp.route_left == 2 && n) {
+                int o = 0;
+                if (lane == 0) o = atomicAdd(&st->n_out[0], n);
+                o = __shfl_sync(FULLMASK, o, 0);
+                for (int i = lane; i < n; i += 32) {
+                    const StripRec r = strips[(long long)0 * MC + i];
+                    if (o + i < sp.out_cap) {
+                        opal_migrant m;
+                        m.cell = -1; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                        out_l[o + i] = m;
+                    } else atomicOr(&st->err, ERR_CAPACITY);
+                }
+            }
+        }
+        if (c == nc - 1) {
+            const int n = scount[2 * c + 1];
+            if (lane == 0 && n) atomicAdd(&st->gone[1], n);
+            if (sp.route_right == 2 && n) {
+                int o = 0;
+                if (lane == 0) o = atomicAdd(&st->n_out[1], n);
+                o = __shfl_sync(FULLMASK, o, 0);
+                for (int i = lane; i < n; i += 32) {
+                    const StripRec r = strips[((long long)c * 2 + 1) * MC + i];
+                    if (o + i < sp.out_cap) {
+                        opal_migrant m;
+                        m.cell = 0; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                        out_r[o + i] = m;
+                    } else atomicOr(&st->err, ERR_CAPACITY);
+                }
+            }
+        }
+        const int n_in = n_from_l + n_from_r;
+        if (n_in == 0) continue;
+        const int cnt = b.count[c];
+        const long long bstart = b.start[c];
+        const int cap = (int)(b.start[c + 1] - bstart);
+        const int idx = c + g.left;
+        double acc[15];
+#pragma unroll
+        for (int k = 0; k < 15; k++) acc[k] = 0.0;
+        for (int i0 = 0; i0 < n_in; i0 += 32) {
+            const int i = i0 + lane;
+            if (i < n_in) {
+                const StripRec r = i < n_from_l ? strips[((long long)src_l * 2 + 1) * MC + i]
+                                                : strips[((long long)src_r * 2) * MC + (i - n_from_l)];
+                const int slot = cnt + i;
+                if (slot < cap) {
+                    const long long s = bstart + slot;
+                    b.f[F_X][s] = r.x; b.f[F_UX][s] = r.ux; b.f[F_UY][s] = r.uy; b.f[F_UZ][s] = r.uz; b.f[F_W][s] = r.w;
+                } else {
+                    // bucket full: park; the host re-lays the buckets out (count[c] keeps the demand)
+                    int o = atomicAdd(&st->n_overflow, 1);
+                    if (o < sp.mover_cap) {
+                        opal_migrant m;
+                        m.cell = c; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                        overflow[o] = m;
+                    } else atomicOr(&st->err, ERR_CAPACITY);
+                }
+                if (slot < cap) {
+                    const double ig = 1.0 / r.gamma;
+                    double t[15];
+                    deposit_terms(r.w * OPAL_QE, r.prev_x, r.x, OPAL_C * r.uy * ig, OPAL_C * r.uz * ig, g.dx, g.dt, t);
+#pragma unroll
+                    for (int k = 0; k < 15; k++) acc[k] += t[k];
+                }
+            }
+        }
+        if (lane == 0) b.count[c] = cnt + n_in;
+#pragma unroll
+        for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]);
+        double mine = 0.0;
+        double* dst = nullptr;
+#pragma unroll
+        for (int k = 0; k < 15; k++) {
+            if (lane == k) {
+                mine = acc[k];
+                dst = k < 5 ? g.jx + idx - 2 + k : (k < 8 ? g.jy + idx - 1 + (k - 5) : (k < 11 ? g.jz + idx - 1 + (k - 8) : g.rho + idx - 2 + (k - 11)));
+            }
+        }
+        if (dst && mine != 0.0) atomicAdd(dst, mine);
+    }
+    (void)lt_mask;
 }
 #endif  // OPAL_FAST
 
@@ -1240,16 +1373,16 @@ static inline int cell_grid(int ncell) {
     return (int)blocks;
 }
 
-static void l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, bool full, bool dep,
-                   opal_migrant* movers, StatusDev* st) {
+static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, bool full, bool dep,
+                   opal_migrant* movers, StripRec* strips, int* scount, StatusDev* st) {
     // the per-segment counters live directly behind the StatusDev block (see host: status + seg counters)
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
-    if (sp.species == OPAL_ELECTRON && !full && dep) {
+    if (sp.species == OPAL_ELECTRON && !full && dep && strips && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
-        k_push_lean_fast<<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, st);
-        return;
+        k_push_lean_fast<<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
+        return true;
     }
 #endif
 #define LAUNCH(SP, F, D) k_push<SP, F, D><<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st)
@@ -1261,6 +1394,15 @@ static void l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
         else { if (dep) LAUNCH(OPAL_ION, false, true); else LAUNCH(OPAL_ION, false, false); }
     }
 #undef LAUNCH
+    return false;
+}
+
+static void l_pull(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, const StripRec* strips,
+                   const int* scount, opal_migrant* out_l, opal_migrant* out_r, opal_migrant* overflow, StatusDev* st) {
+#ifdef OPAL_FAST
+    long long blocks = ((long long)b.ncell + 7) / 8;
+    k_pull<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(g, b, sp, strips, scount, out_l, out_r, overflow, st);
+#endif
 }
 
 static void l_scatter(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, bool full, bool dep,
@@ -1384,7 +1526,7 @@ static void l_copy_buckets(cudaStream_t s, const BucketDev& src, const BucketDev
 
 KernelTable table() {
     KernelTable t;
-    t.push = l_push; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
+    t.push = l_push; t.pull = l_pull; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
     t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets;

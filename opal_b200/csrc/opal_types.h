@@ -56,17 +56,27 @@ struct StatusDev {
 };
 enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u };
 
+// compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout);
+// the destination (c-1 / c+1) is implied by the strip it sits in
+struct StripRec { double x, prev_x, ux, uy, uz, w, gamma, pad; };   // 64 bytes
+
 struct StepParams {
     uint32_t flags;
     int species;             // opal_species
     int route_left, route_right;   // what happens to a leaver: 0 = delete (open boundary), 1 = wrap (self), 2 = outbox
     int mover_cap, out_cap;
+    int cell_mover_cap;      // records per cell and direction in the mover strips (0: strips not in use)
 };
 
 // one set of kernel launchers; two instances exist (fast: FMA contraction on, strict: off)
 struct KernelTable {
-    void (*push)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool fused_deposit,
-                 opal_migrant* movers, StatusDev* st);
+    // returns true when the kernel used the per-cell mover strips (then scatter_cells must follow)
+    bool (*push)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool fused_deposit,
+                 opal_migrant* movers, StripRec* strips, int* strip_count, StatusDev* st);
+    // pull the strips' movers into their destination buckets (+ their deposit); inbox_*: strips received from the
+    // left / right neighbour slab (remote case), may be null
+    void (*pull)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, const StripRec* strips,
+                 const int* strip_count, opal_migrant* outbox_l, opal_migrant* outbox_r, opal_migrant* overflow, StatusDev* st);
     void (*scatter)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool deposit,
                     const opal_migrant* recs, const int* n_recs, int n_max, long long cell_shift, const int* idx_list,
                     opal_migrant* outbox_l, opal_migrant* outbox_r, int* overflow_idx, StatusDev* st);

@@ -215,3 +215,21 @@ def test_generator_roundtrip_and_lean_run(gpu, oracle):
     for k in ("x", "ux", "uy", "uz"):
         assert pc.rel_inf(da[k][oa], db[k][ob]) < 1e-10, k
     pc.compare_fields(a.fields(), b.fields())
+
+
+def test_lean_hot_plasma_mover_strip_overflow(gpu, oracle):
+    """Hot plasma (about a third of every cell crosses per step) in the lean fused path: the per-cell
+    mover strips overflow into the shared segmented buffer every step; results must not change."""
+    nx, npc, dx = 160, 200, 500.0
+    a = Slab(gpu, nx, 0.0, dx, flags=FLAG_LEAN_STATE)
+    b = Slab(oracle, nx, 0.0, dx)
+    p = pc.thermal_particles(nx, npc, dx, 0.6, seed=77)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for chunk in (1, 9):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
+        pc.compare_fields(a.fields(), b.fields())
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+    assert a.count(ELECTRON) == nx * npc
