@@ -524,17 +524,30 @@ __global__ void __launch_bounds__(256) k_pull(GridDev g, BucketDev b, StepParams
                     } else atomicOr(&st->err, ERR_CAPACITY);
                 }
                 if (slot < cap) {
-                    const double ig = 1.0 / r.gamma;
-                    double t[15];
-                    deposit_terms(r.w * OPAL_QE, r.prev_x, r.x, OPAL_C * r.uy * ig, OPAL_C * r.uz * ig, g.dx, g.dt, t);
-#pragma unroll
-                    for (int k = 0; k < 15; k++) acc[k] += t[k];
+                    // R-face form of the mover's deposit in the frame of its new cell c (faces -3/2..+5/2):
+                    // new position: R = (1, a, b, c, 0); old position one cell to the left: (a_o, b_o, c_o, 0, 0),
+                    // one cell to the right: (1, 1, a_o, b_o, c_o);  flux = R_new - R_old  (== Cell::flux, yee.rs:185)
+                    const bool from_l = i < n_from_l;
+                    const RFaces rn = r_faces(r.x);
+                    const RFaces ro = r_faces(from_l ? r.prev_x + 1.0 : r.prev_x - 1.0);
+                    const double f0 = from_l ? 1.0 - ro.a : 0.0;
+                    const double f1 = rn.a - (from_l ? ro.b : 1.0);
+                    const double f2 = rn.b - (from_l ? ro.c : ro.a);
+                    const double f3 = rn.c - (from_l ? 0.0 : ro.b);
+                    const double f4 = from_l ? 0.0 : -ro.c;
+                    acc[0] += r.w * f0; acc[1] += r.w * f1; acc[2] += r.w * f2; acc[3] += r.w * f3; acc[4] += r.w * f4;
+                    const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
+                    const double tw = r.w / r.gamma, ty = tw * r.uy, tz = tw * r.uz;
+                    acc[5] += ty * w0; acc[6] += ty * w1; acc[7] += ty * w2;
+                    acc[8] += tz * w0; acc[9] += tz * w1; acc[10] += tz * w2;
+                    acc[11] += r.w * w3; acc[12] += r.w * w0; acc[13] += r.w * w1; acc[14] += r.w * w2;
                 }
             }
         }
         if (lane == 0) b.count[c] = cnt + n_in;
+        const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
 #pragma unroll
-        for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]);
+        for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]) * (k < 5 ? kx : (k < 11 ? ky : kr));
         double mine = 0.0;
         double* dst = nullptr;
 #pragma unroll
