@@ -240,12 +240,10 @@ def main():
         push_ms, push_n = kt["push"]
         achieved = (B_ALG * n_local / (push_ms / push_n * 1e-3)) / 1e9 if push_n else None
         traffic = None
-        tfile = ROOT / "profiles" / "push_traffic_bytes_per_launch.json"
-        if tfile.exists():
+        tfile = ROOT / "profiles" / "push_traffic.json"
+        if tfile.exists() and not args.full_state:
             try:
-                tj = json.loads(tfile.read_text())
-                if tj.get("particles_per_launch") == n_local:
-                    traffic = tj.get("dram_bytes_per_launch")
+                traffic = json.loads(tfile.read_text())["dram_bytes_per_particle"] * n_local   # ncu dram bytes per launch
             except Exception:
                 pass
         line = {
