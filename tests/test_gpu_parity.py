@@ -233,3 +233,18 @@ def test_lean_hot_plasma_mover_strip_overflow(gpu, oracle):
         pc.compare_fields(a.fields(), b.fields())
         assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
     assert a.count(ELECTRON) == nx * npc
+
+
+def test_two_gpu_nccl_ring_matches_single_oracle_slab():
+    """needs >= 2 GPUs on the box (gpurun --gpus 2); skipped otherwise"""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import pathlib
+    script = pathlib.Path(__file__).with_name("mgpu_check.py")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                          "--master-port", "29531", str(script)], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert out.stdout.count("MGPU OK") == 3, out.stdout[-3000:]
