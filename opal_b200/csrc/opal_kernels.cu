@@ -226,6 +226,16 @@ __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepPara
 // Results differ from the literal formulas only by re-association (<= 1e-15 relative), far inside the
 // 1e-10 parity tolerance; the strict build keeps the literal arithmetic.
 // --------------------------------------------------------------------------------------------
+#ifndef OPAL_PUSH_STAGES
+#define OPAL_PUSH_STAGES 4
+#endif
+__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 struct RFaces { double a, b, c; };   // R at the faces -1/2, +1/2, +3/2 of the particle's cell
 __device__ __forceinline__ RFaces r_faces(double x) {
     const double h = x - 0.5, q = 0.5 * (h * h);
@@ -289,6 +299,32 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         double sjx0 = 0.0, sjx1 = 0.0, sjx2 = 0.0, sjy0 = 0.0, sjy1 = 0.0, sjy2 = 0.0, sjz0 = 0.0, sjz1 = 0.0, sjz2 = 0.0;
         double sr0 = 0.0, sr1 = 0.0, sr2 = 0.0, sr3 = 0.0;
 
+#if OPAL_PUSH_STAGES > 0
+        // cp.async ring: the five particle streams of the next OPAL_PUSH_STAGES-1 iterations are in flight
+        // into this warp's shared-memory stages (LDGSTS, no registers held); every lane reads back only
+        // the element it copied itself, so per-thread wait_group is the only synchronisation needed.
+        // In-place safety: chunk k is waited for at the top of iteration k, before any store of iteration k,
+        // and earlier iterations only store below slot 32k.
+        constexpr int NST = OPAL_PUSH_STAGES;
+        __shared__ double s_ring[OPAL_PUSH_WPB][NST][5][CH];
+        double (*ring)[5][CH] = s_ring[threadIdx.x >> 5];
+        __syncwarp();
+#pragma unroll
+        for (int st_ = 0; st_ < NST - 1; st_++) {
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                const int i = st_ * CH + q * 32 + lane;
+                if (i < n) {
+                    const long long s = base + i;
+                    cp_async8(&ring[st_][0][q * 32 + lane], fx + s); cp_async8(&ring[st_][1][q * 32 + lane], fux + s);
+                    cp_async8(&ring[st_][2][q * 32 + lane], fuy + s); cp_async8(&ring[st_][3][q * 32 + lane], fuz + s);
+                    cp_async8(&ring[st_][4][q * 32 + lane], fw + s);
+                }
+            }
+            cp_async_commit();
+        }
+        int stage = 0;
+#else
         // software pipeline: the next iteration's loads are issued before this iteration's stores
         double nx0[ILP], nx1[ILP], nx2[ILP], nx3[ILP], nx4[ILP];
 #pragma unroll
@@ -297,6 +333,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             const int i = q * 32 + lane;
             if (i < n) { const long long s = base + i; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
         }
+#endif
         int written = 0;
         for (int k0 = 0; k0 < n; k0 += CH) {
             double x[ILP], W[ILP], xn[ILP], igam[ILP], gam2[ILP], fl[ILP];
@@ -304,6 +341,32 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             RFaces ro[ILP];
             int d[ILP];
             bool valid[ILP];
+#if OPAL_PUSH_STAGES > 0
+            cp_async_wait<NST - 2>();
+#pragma unroll
+            for (int q = 0; q < ILP; q++) {
+                valid[q] = k0 + q * 32 + lane < n;
+                const int e = q * 32 + lane;
+                x[q] = valid[q] ? ring[stage][0][e] : 0.0;
+                u[q] = {valid[q] ? ring[stage][1][e] : 0.0, valid[q] ? ring[stage][2][e] : 0.0, valid[q] ? ring[stage][3][e] : 0.0};
+                W[q] = valid[q] ? ring[stage][4][e] : 0.0;
+            }
+            {
+                const int pst = stage == 0 ? NST - 1 : stage - 1;     // the stage consumed in the previous iteration
+#pragma unroll
+                for (int q = 0; q < ILP; q++) {
+                    const int in = k0 + (NST - 1) * CH + q * 32 + lane;
+                    if (in < n) {
+                        const long long s = base + in;
+                        cp_async8(&ring[pst][0][q * 32 + lane], fx + s); cp_async8(&ring[pst][1][q * 32 + lane], fux + s);
+                        cp_async8(&ring[pst][2][q * 32 + lane], fuy + s); cp_async8(&ring[pst][3][q * 32 + lane], fuz + s);
+                        cp_async8(&ring[pst][4][q * 32 + lane], fw + s);
+                    }
+                }
+                cp_async_commit();
+                stage = stage == NST - 1 ? 0 : stage + 1;
+            }
+#else
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
                 x[q] = nx0[q]; u[q] = {nx1[q], nx2[q], nx3[q]}; W[q] = nx4[q];
@@ -314,6 +377,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 const int in = k0 + CH + q * 32 + lane;
                 if (in < n) { const long long s = base + in; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
             }
+#endif
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
                 // ---- gather (yee.rs:499-529) ----
@@ -414,6 +478,9 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             b.count[c] = written;
             scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC;
         }
+#if OPAL_PUSH_STAGES > 0
+        cp_async_wait<0>();
+#endif
 
         // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
         const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
