@@ -78,6 +78,7 @@ struct opal_ctx {
     uint32_t flags = 0;
     uint64_t seed = 0;
     bool full = true;
+    bool bx_zero = true;     // no non-zero B_x was ever uploaded (the solver never changes B_x): selects the BX0 push kernel
     cudaStream_t stream = nullptr;
     KernelTable k;
     GridDev g;              // current E/B buffers
@@ -153,7 +154,7 @@ PhotonDev pdev(opal_ctx* c, int which) {
 }
 StepParams sparams(opal_ctx* c, int species) {
     StepParams sp;
-    sp.flags = c->flags; sp.species = species;
+    sp.flags = c->flags | (c->bx_zero ? OPAL_STEP_BX_ZERO : 0u); sp.species = species;
     sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap;
@@ -785,6 +786,8 @@ opal_status opal_fields_upload(opal_ctx* c, const double* cells11) {
     std::vector<double> soa((size_t)10 * len);
     for (int i = 0; i < len; i++)
         for (int k = 0; k < 10; k++) soa[(size_t)k * len + i] = cells11[(size_t)i * 11 + 1 + k];
+    c->bx_zero = true;
+    for (int i = 0; i < len; i++) if (soa[(size_t)7 * len + i] != 0.0) { c->bx_zero = false; break; }
     double* dst[10] = {c->g.rho, c->g.jx, c->g.jy, c->g.jz, c->g.ex, c->g.ey, c->g.ez, c->g.bx, c->g.by, c->g.bz};
     for (int k = 0; k < 10; k++) CU(cudaMemcpyAsync(dst[k], soa.data() + (size_t)k * len, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));

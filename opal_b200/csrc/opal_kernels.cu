@@ -237,16 +237,60 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 struct RFaces { double a, b, c; };   // R at the faces -1/2, +1/2, +3/2 of the particle's cell
+// 8 FP64 instructions: |h| enters through the operand modifier, the two branches of the spline share
+// one square ((1 - |h|)^2 is (1+h)^2 left of the cell centre and (1-h)^2 right of it).
 __device__ __forceinline__ RFaces r_faces(double x) {
-    const double h = x - 0.5, q = 0.5 * (h * h);
-    const double hp = 1.0 + h, hm = 1.0 - h;
-    const bool lo = x < 0.5;
+    const double h = x - 0.5;
+    const bool lo = h < 0.0;
+    const double q = 0.5 * (h * h);
+    const double t = 1.0 - fabs(h);
+    const double tt = 0.5 * (t * t);
     RFaces r;
     r.a = lo ? 1.0 - q : 1.0;
-    r.b = lo ? 0.5 * (hp * hp) : 1.0 - 0.5 * (hm * hm);
+    r.b = lo ? tt : 1.0 - tt;
     r.c = lo ? 0.0 : q;
     return r;
 }
+
+// MUFU.RSQ64H / MUFU.RCP64H seeds (~2^-20 relative: they see only the high word of the operand) refined
+// by ONE third-order step, error ~ e^3 < 2^-58: 5 (rsqrt, +1 for sqrt) / 3 (rcp) FP64 instructions
+// instead of the ~10 of the IEEE-rounded library sequences with their slow-path branches.  Operands here are
+// gamma^2-like quantities in [1, 1e300): no zero / denormal / infinity handling is needed.
+__device__ __forceinline__ double rsqrt_seed(double x) { double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
+__device__ __forceinline__ double rcp_seed(double x) { double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
+__device__ __forceinline__ double fast_rsqrt(double x) {
+    const double y0 = rsqrt_seed(x);
+    const double t = x * y0;
+    const double e = fma(-t, y0, 1.0);             // 1 - x y0^2
+    const double pe = fma(0.375, e, 0.5) * e;      // rsqrt(x) = y0 (1 + e/2 + 3 e^2/8 + O(e^3))
+    return fma(y0, pe, y0);
+}
+__device__ __forceinline__ void fast_rsqrt_sqrt(double x, double& rs, double& sq) {
+    const double y0 = rsqrt_seed(x);
+    const double t = x * y0;                       // ~ sqrt(x)
+    const double e = fma(-t, y0, 1.0);
+    const double pe = fma(0.375, e, 0.5) * e;
+    rs = fma(y0, pe, y0);
+    sq = fma(t, pe, t);
+}
+__device__ __forceinline__ double fast_sqrt(double x) { double rs, sq; fast_rsqrt_sqrt(x, rs, sq); return sq; }
+__device__ __forceinline__ double fast_rcp(double x) {
+    const double y0 = rcp_seed(x);
+    const double e = fma(-x, y0, 1.0);             // 1/x = y0 (1 + e + e^2 + O(e^3))
+    return fma(y0, fma(e, e, e), y0);
+}
+
+// Per-cell gather coefficients of the fast kernel (one copy per warp in shared memory).  With the R-face
+// values a, b, c of a particle at offset x and xm = 1 - x:
+//   alpha E_x   = ex1 + xm^2 dex0 + x^2 dex2        (dex0 = alpha/2 (Ex[j-1]-Ex[j]), dex2 = alpha/2 (Ex[j+1]-Ex[j]))
+//   alpha E_y   = ey0 + a dey0 + b dey1 + c dey2     (dey_k = alpha (Ey[j+k]-Ey[j-1+k]))
+//   alpha c B_y = ty1 + xm^2 dty0 + x^2 dty2, ...    (the Vay rotation vector tau directly)
+// i.e. the spline weights (yee.rs:499-529) with the partition of unity folded into per-cell differences,
+// and alpha = q dt / 2 m c (electron.rs:273) applied once per cell instead of once per particle.
+struct CellPre { double ex1, dex0, dex2, ey0, dey[3], ez0, dez[3], tx, ty1, dty0, dty2, tz1, dtz0, dtz2; };
+__constant__ signed char c_pre_ia[18] = {1, 0, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 12, 14, 16, 15, 17};
+__constant__ signed char c_pre_ib[18] = {18, 1, 1, 18, 3, 4, 5, 18, 7, 8, 9, 18, 18, 13, 13, 18, 16, 16};
+__constant__ signed char c_pre_k[18] = {0, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 2, 2, 3, 3, 2, 3, 3};   // alpha, alpha/2, alpha c, alpha c/2
 
 #ifndef OPAL_PUSH_WPB
 #define OPAL_PUSH_WPB 4
@@ -260,6 +304,7 @@ __device__ __forceinline__ RFaces r_faces(double x) {
 #ifndef OPAL_PUSH_MINBLK
 #define OPAL_PUSH_MINBLK 4
 #endif
+template <bool BX0>   // BX0: B_x == 0 on the whole grid (the solver never updates it, yee.rs:839-848) => tau_x terms drop out
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StripRec* __restrict__ strips,
                                                            int* __restrict__ scount, StatusDev* __restrict__ st) {
@@ -282,20 +327,23 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         const long long base = b.start[c];
         const int j = c + g.left;
         int mloc_l = 0, mloc_r = 0;   // left / right movers of this cell so far (warp-uniform): slots in its two strips
-#if OPAL_PUSH_SMEM_FIELDS
-        // the 18 field values every lane of this warp gathers from: one copy per warp in shared memory
-        __shared__ CellFields s_cf[OPAL_PUSH_WPB];
-        CellFields& cf = s_cf[threadIdx.x >> 5];
+        // the 18 field values every lane of this warp gathers from -> 18 per-cell gather coefficients (CellPre),
+        // one copy per warp in shared memory
+        __shared__ double s_raw[OPAL_PUSH_WPB][20];
+        __shared__ CellPre s_pre[OPAL_PUSH_WPB];
+        double* const raw = s_raw[threadIdx.x >> 5];
+        CellPre& P = s_pre[threadIdx.x >> 5];
         __syncwarp();
-        if (lane < 3) { cf.ex[lane] = __ldg(g.ex + j - 1 + lane); cf.by[lane] = __ldg(g.by + j - 1 + lane); cf.bz[lane] = __ldg(g.bz + j - 1 + lane); }
-        if (lane < 4) { cf.ey[lane] = __ldg(g.ey + j - 1 + lane); cf.ez[lane] = __ldg(g.ez + j - 1 + lane); }
-        if (lane == 0) cf.bx = __ldg(g.bx + j);
+        if (lane < 3) { raw[lane] = __ldg(g.ex + j - 1 + lane); raw[12 + lane] = __ldg(g.by + j - 1 + lane); raw[15 + lane] = __ldg(g.bz + j - 1 + lane); }
+        if (lane < 4) { raw[3 + lane] = __ldg(g.ey + j - 1 + lane); raw[7 + lane] = __ldg(g.ez + j - 1 + lane); }
+        if (lane == 0) { raw[11] = BX0 ? 0.0 : __ldg(g.bx + j); raw[18] = 0.0; }
         __syncwarp();
-#else
-        CellFields cf;
-        load_cell_fields(g, j, cf);
-#endif
-        const double taux = ac * cf.bx;
+        if (lane < 18) {
+            const int k = c_pre_k[lane];
+            const double coef = (k & 2 ? ac : alpha) * (k & 1 ? 0.5 : 1.0);
+            reinterpret_cast<double*>(&P)[lane] = coef * (raw[c_pre_ia[lane]] - raw[c_pre_ib[lane]]);
+        }
+        __syncwarp();
         double sjx0 = 0.0, sjx1 = 0.0, sjx2 = 0.0, sjy0 = 0.0, sjy1 = 0.0, sjy2 = 0.0, sjz0 = 0.0, sjz1 = 0.0, sjz2 = 0.0;
         double sr0 = 0.0, sr1 = 0.0, sr2 = 0.0, sr3 = 0.0;
 
@@ -380,34 +428,37 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 #endif
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
-                // ---- gather (yee.rs:499-529) ----
+                // ---- gather (yee.rs:499-529): alpha E and tau = alpha c B from the per-cell coefficients ----
                 ro[q] = r_faces(x[q]);
-                const double wn0 = 1.0 - ro[q].a, wn1 = ro[q].a - ro[q].b, wn2 = ro[q].b - ro[q].c, wn3 = ro[q].c;
-                const double xm = 1.0 - x[q];
-                const double wc0 = 0.5 * (xm * xm), wc2 = 0.5 * (x[q] * x[q]), wc1 = (1.0 - wc0) - wc2;
-                V3 E, B;
-                E.x = cf.ex[0] * wc0 + cf.ex[1] * wc1 + cf.ex[2] * wc2;
-                E.y = cf.ey[0] * wn0 + cf.ey[1] * wn1 + cf.ey[2] * wn2 + cf.ey[3] * wn3;
-                E.z = cf.ez[0] * wn0 + cf.ez[1] * wn1 + cf.ez[2] * wn2 + cf.ez[3] * wn3;
-                B.x = cf.bx;
-                B.y = cf.by[0] * wc0 + cf.by[1] * wc1 + cf.by[2] * wc2;
-                B.z = cf.bz[0] * wc0 + cf.bz[1] * wc1 + cf.bz[2] * wc2;
+                const double xm = 1.0 - x[q], xm2 = xm * xm, x2 = x[q] * x[q];
+                V3 aE, tv;
+                aE.x = fma(x2, P.dex2, fma(xm2, P.dex0, P.ex1));
+                aE.y = fma(ro[q].c, P.dey[2], fma(ro[q].b, P.dey[1], fma(ro[q].a, P.dey[0], P.ey0)));
+                aE.z = fma(ro[q].c, P.dez[2], fma(ro[q].b, P.dez[1], fma(ro[q].a, P.dez[0], P.ez0)));
+                tv.x = BX0 ? 0.0 : P.tx;
+                tv.y = fma(x2, P.dty2, fma(xm2, P.dty0, P.ty1));
+                tv.z = fma(x2, P.dtz2, fma(xm2, P.dtz0, P.tz1));
                 // ---- Vay push (electron.rs:268-330) ----
-                const double ig = rsqrt(1.0 + dot(u[q], u[q]));
-                const V3 v = (OPAL_C * ig) * u[q];
-                const V3 u_half = u[q] + alpha * (E + cross(v, B));
-                const V3 u_prime = u_half + alpha * E;
-                const double gp2 = 1.0 + dot(u_prime, u_prime);
-                const V3 tv = {taux, ac * B.y, ac * B.z};
-                const double u_star = dot(u_prime, tv);
-                const double tau2 = dot(tv, tv);
-                const double sigma = gp2 - tau2;
-                gam2[q] = 0.5 * sigma + sqrt(0.25 * (sigma * sigma) + tau2 + u_star * u_star);
-                igam[q] = rsqrt(gam2[q]);
-                const V3 t = igam[q] * tv;
-                const double s_ = 1.0 / (1.0 + dot(t, t));
-                u[q] = s_ * (u_prime + dot(u_prime, t) * t + cross(u_prime, t));
-                const double dxi = kdt * u[q].x * igam[q];
+                // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma
+                const double ig = fast_rsqrt(fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0))));
+                const V3 uxt = BX0 ? V3{u[q].y * tv.z - u[q].z * tv.y, -(u[q].x * tv.z), u[q].x * tv.y} : cross(u[q], tv);
+                const V3 ue = u[q] + aE;
+                const V3 u_prime = {fma(ig, uxt.x, ue.x) + aE.x, fma(ig, uxt.y, ue.y) + aE.y, fma(ig, uxt.z, ue.z) + aE.z};
+                const double gp2 = fma(u_prime.x, u_prime.x, fma(u_prime.y, u_prime.y, fma(u_prime.z, u_prime.z, 1.0)));
+                const double u_star = BX0 ? fma(u_prime.y, tv.y, u_prime.z * tv.z) : dot(u_prime, tv);
+                const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
+                const double hs = 0.5 * (gp2 - tau2);
+                gam2[q] = hs + fast_sqrt(fma(hs, hs, fma(u_star, u_star, tau2)));
+                double gam;
+                fast_rsqrt_sqrt(gam2[q], igam[q], gam);
+                // u = s (u' + (u'.t) t + u' x t), t = tau/gamma, s = 1/(1+t^2)   ==   (gamma^2 u' + (u'.tau) tau + gamma u' x tau) / (gamma^2 + tau^2)
+                const double inv = fast_rcp(gam2[q] + tau2);
+                const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
+                V3 w = {fma(gam, pxt.x, gam2[q] * u_prime.x), fma(gam, pxt.y, gam2[q] * u_prime.y), fma(gam, pxt.z, gam2[q] * u_prime.z)};
+                if (!BX0) w.x = fma(u_star, tv.x, w.x);
+                w.y = fma(u_star, tv.y, w.y); w.z = fma(u_star, tv.z, w.z);
+                u[q] = inv * w;
+                const double dxi = (kdt * igam[q]) * u[q].x;
                 if (valid[q] && !(dxi < 1.0)) cfl = true;
                 xn[q] = x[q] + dxi;
                 fl[q] = floor(xn[q]);
@@ -1461,7 +1512,8 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
 #ifdef OPAL_FAST
     if (sp.species == OPAL_ELECTRON && !full && dep && strips && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
-        k_push_lean_fast<<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
+        if (sp.flags & OPAL_STEP_BX_ZERO) k_push_lean_fast<true><<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
+        else k_push_lean_fast<false><<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
         return true;
     }
 #endif

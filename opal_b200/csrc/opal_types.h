@@ -60,6 +60,9 @@ enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u };
 // the destination (c-1 / c+1) is implied by the strip it sits in
 struct StripRec { double x, prev_x, ux, uy, uz, w, gamma, pad; };   // 64 bytes
 
+// internal StepParams.flags bit (above the public OPAL_FLAG_* bits): B_x is zero on the whole grid
+#define OPAL_STEP_BX_ZERO (1u << 31)
+
 struct StepParams {
     uint32_t flags;
     int species;             // opal_species
