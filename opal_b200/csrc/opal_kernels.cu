@@ -560,7 +560,10 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 // registers: one shuffle reduction + <= 15 atomics per cell.  Edge cells route through the slab
 // boundary (mod.rs:290-373): periodic self-neighbour => the strips of the opposite edge; remote
 // neighbour => the edge strips are copied to the outbox here and arrive through the inbox path.
-__global__ void __launch_bounds__(256) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
+#ifndef OPAL_PULL_MINBLK
+#define OPAL_PULL_MINBLK 3
+#endif
+__global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
                                                const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
                                                opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
                                                StatusDev* __restrict__ st) {

@@ -235,6 +235,32 @@ def test_lean_hot_plasma_mover_strip_overflow(gpu, oracle):
     assert a.count(ELECTRON) == nx * npc
 
 
+def test_lean_expanding_slab_hole_fill(gpu, oracle):
+    """Lean fused path on a plasma slab expanding into vacuum (plus a density step and a non-zero B_x, which
+    selects the general rotation kernel): edge cells lose more particles than they gain (tail particles move
+    into the holes), vacuum cells only gain (append), hot cells overflow the hole list."""
+    nx, dx = 192, 500.0
+    a = Slab(gpu, nx, 0.0, dx, flags=FLAG_LEAN_STATE)
+    b = Slab(oracle, nx, 0.0, dx)
+    p1 = pc.thermal_particles(nx, 300, dx, 0.25, seed=5, cells=np.arange(40, 90))
+    p2 = pc.thermal_particles(nx, 37, dx, 0.25, seed=6, cells=np.arange(90, 150))
+    p2["weight"] = p2["weight"] * 1.000123
+    p = {k: np.concatenate([p1[k], p2[k]]) for k in p1}
+    f = b.fields()
+    f[:, pc.FIELD_NAMES.index("Bx")] = 2.0e-7
+    f[:, pc.FIELD_NAMES.index("By")] = 1.0e-7 * np.cos(np.arange(f.shape[0]) * 0.05)
+    for s_ in (a, b):
+        s_.set_fields(f)
+        pc.upload(s_, ELECTRON, p)
+    for chunk in (1, 2, 12):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
+        pc.compare_fields(a.fields(), b.fields())
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+    assert a.count(ELECTRON) == p["cell"].size
+
+
 def test_two_gpu_nccl_ring_matches_single_oracle_slab():
     """needs >= 2 GPUs on the box (gpurun --gpus 2); skipped otherwise"""
     import subprocess
