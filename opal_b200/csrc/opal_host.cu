@@ -101,7 +101,8 @@ struct opal_ctx {
     bool halo_given[2] = {false, false};
     StatusDev* d_status = nullptr;   // followed by OPAL_MOVER_SEGMENTS ints
     StatusDev* h_status = nullptr;   // pinned
-    double* d_energy = nullptr;      // 4 doubles
+    double* d_energy = nullptr;      // 4 doubles + [4]: electron kinetic energy accumulated by the last fused push
+    bool ke_fused = false;           // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
     double* d_qed_tables = nullptr;
@@ -385,13 +386,19 @@ bool insert_inbox(opal_ctx* c, int sp, int side, bool dep) {
 }
 
 // gather + push + re-bucket + migrate one charged species (mod.rs:247-376); dep: fused deposit
-bool advance_charged(opal_ctx* c, int sp, bool dep, bool check) {
+bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = false) {
     Buckets& B = c->bk[sp];
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
     if (!reset_status(c, true)) return false;
     StepParams p = sparams(c, sp);
     bool strips = false;
-    { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status); c->launches++; }
+    double* ke_out = nullptr;
+    if (want_ke && sp == OPAL_ELECTRON) {
+        ke_out = c->d_energy + 4;
+        CUB(cudaMemsetAsync(ke_out, 0, sizeof(double), c->stream));
+    }
+    { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status, ke_out); c->launches++; }
+    if (ke_out && strips) c->ke_fused = true;
     if (strips) { Timed tm(c, 1); c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1,
                  c->d_overflow, c->d_status); c->launches++; }
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
@@ -520,8 +527,8 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     CU(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
     CU(cudaMallocHost(&c->h_status, sizeof(StatusDev)));
     memset(c->h_status, 0, sizeof(StatusDev));
-    CU(cudaMalloc(&c->d_energy, 4 * sizeof(double)));
-    CU(cudaMallocHost(&c->h_energy, 4 * sizeof(double)));
+    CU(cudaMalloc(&c->d_energy, 8 * sizeof(double)));
+    CU(cudaMallocHost(&c->h_energy, 8 * sizeof(double)));
     CU(cudaMalloc(&c->d_tmp_int, 8 * sizeof(int)));
     c->out_cap = (int)env_ll("OPAL_EXCHANGE_CAP", 4096);
     for (int s = 0; s < 2; s++) {
@@ -579,6 +586,7 @@ opal_status opal_set_ion(opal_ctx* c, double z_star, double a) {
 opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int64_t* cell, const double* x, const double* ux,
                                   const double* uy, const double* uz, const double* w, const double* tau) {
     CHECK_CTX(c);
+    c->ke_fused = false;
     if (n < 0 || n > (1ll << 31) - 64 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
     const double dx = c->g.dx, dt = c->g.dt;
     const double inf = std::numeric_limits<double>::infinity();
@@ -652,6 +660,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
 opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, double weight, const double u_th[3], const double drift[3],
                                     int two_stream, int64_t global_cell_offset, uint64_t seed) {
     CHECK_CTX(c);
+    c->ke_fused = false;
     if ((species != OPAL_ELECTRON && species != OPAL_ION) || npc < 1 || !u_th || !drift) return OPAL_EINVAL;
     Buckets& B = c->bk[species];
     free_buckets(B);
@@ -810,6 +819,7 @@ opal_status opal_fields_download(opal_ctx* c, double* cells11) {
 
 opal_status opal_advance(opal_ctx* c, int species) {
     CHECK_CTX(c);
+    c->ke_fused = false;
     if (species == OPAL_PHOTON) { advance_photons(c, true); return (opal_status)c->status; }
     if (species != OPAL_ELECTRON && species != OPAL_ION) return OPAL_EINVAL;
     if (!c->full) return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context: only opal_run_steps is available"), c->status);
@@ -845,6 +855,7 @@ opal_status opal_migrants_take(opal_ctx* c, int species, int side, int64_t cap, 
 
 opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, const opal_migrant* in) {
     CHECK_CTX(c);
+    c->ke_fused = false;
     if (side != OPAL_LEFT && side != OPAL_RIGHT || n < 0 || species < 0 || species > 2) return OPAL_EINVAL;
     if (n == 0) return OPAL_OK;
     if (n > c->out_cap) return OPAL_ECAPACITY;
@@ -867,6 +878,7 @@ opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, co
 
 opal_status opal_emit_radiation(opal_ctx* c, double t, const double* min_energy_mev, const double* max_angle, const double* max_fl) {
     CHECK_CTX(c);
+    c->ke_fused = false;
     const double nan = std::numeric_limits<double>::quiet_NaN();
     do_emit(c, t, min_energy_mev ? *min_energy_mev : nan, max_angle ? *max_angle : nan, max_fl ? *max_fl : nan);
     return (opal_status)c->status;
@@ -936,9 +948,11 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     const double nan = std::numeric_limits<double>::quiet_NaN();
     const bool fused = current_deposition && !photon_emission;
     double t = t0;
+    c->ke_fused = false;
     for (int64_t s = 0; s < nsteps; s++) {   // main.rs:238-267
         if (current_deposition) { c->k.clear(c->stream, c->g); c->launches++; }
-        if (!advance_charged(c, OPAL_ELECTRON, fused, true)) break;
+        // the last step of the call also sums the electrons' kinetic energy (lean strip kernel): opal_energy then needs no particle pass
+        if (!advance_charged(c, OPAL_ELECTRON, fused, true, s == nsteps - 1 && !photon_emission)) break;
         if (!advance_charged(c, OPAL_ION, fused, true)) break;
         if (!advance_photons(c, c->ph[0].cap > 0)) break;
         if (photon_emission) { if (!do_emit(c, t, f3 ? f3[0] : nan, f3 ? f3[1] : nan, f3 ? f3[2] : nan)) break; }
@@ -962,16 +976,17 @@ opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, dou
     CHECK_CTX(c);
     BucketDev be, bi;
     PhotonDev pp;
-    const bool he = c->bk[0].allocated, hi = c->bk[1].allocated, hp = c->ph[0].cap > 0;
+    const bool fused_ke = c->ke_fused && c->bk[0].allocated;
+    const bool he = c->bk[0].allocated && !fused_ke, hi = c->bk[1].allocated, hp = c->ph[0].cap > 0;
     if (he) be = bdev(c, 0);
     if (hi) bi = bdev(c, 1);
     if (hp) pp = pdev(c, c->ph_cur);
     c->k.energy(c->stream, c->g, he ? &be : nullptr, hi ? &bi : nullptr, hp ? &pp : nullptr, c->full, c->d_energy);
     c->launches += 1 + (he ? 1 : 0) + (hi ? 1 : 0) + (hp ? 1 : 0);
-    CU(cudaMemcpyAsync(c->h_energy, c->d_energy, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(c->h_energy, c->d_energy, 5 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     if (em) *em = c->h_energy[0];
-    if (ke_e) *ke_e = c->h_energy[1];
+    if (ke_e) *ke_e = fused_ke ? c->h_energy[4] : c->h_energy[1];
     if (ke_i) *ke_i = c->h_energy[2];
     if (ke_ph) *ke_ph = c->h_energy[3];
     return OPAL_OK;

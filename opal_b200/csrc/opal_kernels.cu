@@ -304,10 +304,13 @@ __constant__ signed char c_pre_k[18] = {0, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 2, 2, 3
 #ifndef OPAL_PUSH_MINBLK
 #define OPAL_PUSH_MINBLK 4
 #endif
-template <bool BX0>   // BX0: B_x == 0 on the whole grid (the solver never updates it, yee.rs:839-848) => tau_x terms drop out
+// BX0: B_x == 0 on the whole grid (the solver never updates it, yee.rs:839-848) => tau_x terms drop out.
+// KE:  also accumulate total_kinetic_energy (electron.rs:122-126: w u^2 mc^2 / (gamma + 1), mod.rs:227-240) of the
+//      pushed particles into *ke_out, so the energy diagnostic that follows a step costs no second pass over HBM.
+template <bool BX0, bool KE>
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StripRec* __restrict__ strips,
-                                                           int* __restrict__ scount, StatusDev* __restrict__ st) {
+                                                           int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out) {
     constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
     constexpr int CH = 32 * ILP;
     const int lane = threadIdx.x & 31;
@@ -317,6 +320,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     const double ac = alpha * OPAL_C;
     const double kdt = OPAL_C * g.dt / g.dx;
     bool cfl = false, cap_err = false;
+    double ske = 0.0;
     double* const fx = b.f[F_X]; double* const fux = b.f[F_UX]; double* const fuy = b.f[F_UY]; double* const fuz = b.f[F_UZ];
     double* const fw = b.f[F_W];
 
@@ -464,6 +468,13 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 fl[q] = floor(xn[q]);
                 d[q] = fl[q] < 0.0 ? -1 : (fl[q] > 0.0 ? 1 : 0);
                 xn[q] -= fl[q];
+                if (KE) {
+                    // leavers through an open slab edge are deleted (mod.rs:372-373): not part of the population any more
+                    const bool dead = (c == 0 && d[q] < 0 && sp.route_left == 0) || (c == b.ncell - 1 && d[q] > 0 && sp.route_right == 0);
+                    const double u2 = fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, u[q].z * u[q].z));
+                    const double e = (W[q] * u2) * fast_rcp(gam + 1.0);      // invalid lanes carry W = 0, u = 0
+                    ske += dead ? 0.0 : e;
+                }
             }
             unsigned m_stay[ILP], m_l[ILP], m_r[ILP];
             int n_l = 0, n_r = 0;
@@ -552,6 +563,10 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
     if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
+    if (KE) {
+        ske = warp_sum(ske) * (1.0e6 * OPAL_ME_MEV * OPAL_E);
+        if (lane == 0 && ske != 0.0) atomicAdd(ke_out, ske);
+    }
 }
 
 // K2p: pull.  One warp per DESTINATION cell c: it reads the right-mover strip of cell c-1 and the
@@ -1508,15 +1523,18 @@ static inline int cell_grid(int ncell) {
 }
 
 static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, bool full, bool dep,
-                   opal_migrant* movers, StripRec* strips, int* scount, StatusDev* st) {
+                   opal_migrant* movers, StripRec* strips, int* scount, StatusDev* st, double* ke_out) {
     // the per-segment counters live directly behind the StatusDev block (see host: status + seg counters)
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
     if (sp.species == OPAL_ELECTRON && !full && dep && strips && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
-        if (sp.flags & OPAL_STEP_BX_ZERO) k_push_lean_fast<true><<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
-        else k_push_lean_fast<false><<<(int)(blocks < 1 ? 1 : blocks), OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st);
+        const int gr = (int)(blocks < 1 ? 1 : blocks);
+#define LAUNCHF(B0, K) k_push_lean_fast<B0, K><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out)
+        if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
+        else { if (ke_out) LAUNCHF(false, true); else LAUNCHF(false, false); }
+#undef LAUNCHF
         return true;
     }
 #endif

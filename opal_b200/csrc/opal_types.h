@@ -75,7 +75,8 @@ struct StepParams {
 struct KernelTable {
     // returns true when the kernel used the per-cell mover strips (then scatter_cells must follow)
     bool (*push)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool fused_deposit,
-                 opal_migrant* movers, StripRec* strips, int* strip_count, StatusDev* st);
+                 opal_migrant* movers, StripRec* strips, int* strip_count, StatusDev* st,
+                 double* ke_out /* null, or accumulator for the pushed particles' kinetic energy (strip kernel only) */);
     // pull the strips' movers into their destination buckets (+ their deposit); inbox_*: strips received from the
     // left / right neighbour slab (remote case), may be null
     void (*pull)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, const StripRec* strips,

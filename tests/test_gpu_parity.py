@@ -22,6 +22,13 @@ def _pair(gpu, oracle, nx, xmin, dx, left=BDY_INTERNAL, right=BDY_INTERNAL, flag
     return a, b
 
 
+def _same_energies(a, b, tol=1e-10):
+    """em_field_energy (yee.rs:787) and total_kinetic_energy (mod.rs:227) of both sides"""
+    ea, eb = a.energy(), b.energy()
+    for k in range(4):
+        assert abs(ea[k] - eb[k]) <= tol * abs(eb[k]) + 1e-300, (k, ea, eb)
+
+
 @pytest.mark.parametrize("flags", [0, FLAG_STRICT_FP])
 def test_two_stream_call_by_call(gpu, oracle, flags):
     """BASELINE config 1 scaled down (two_stream.yaml): periodic, deposition on, QED off."""
@@ -215,6 +222,7 @@ def test_generator_roundtrip_and_lean_run(gpu, oracle):
     for k in ("x", "ux", "uy", "uz"):
         assert pc.rel_inf(da[k][oa], db[k][ob]) < 1e-10, k
     pc.compare_fields(a.fields(), b.fields())
+    _same_energies(a, b)
 
 
 def test_lean_hot_plasma_mover_strip_overflow(gpu, oracle):
@@ -232,6 +240,7 @@ def test_lean_hot_plasma_mover_strip_overflow(gpu, oracle):
         pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
         pc.compare_fields(a.fields(), b.fields())
         assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        _same_energies(a, b)
     assert a.count(ELECTRON) == nx * npc
 
 
@@ -258,7 +267,31 @@ def test_lean_expanding_slab_hole_fill(gpu, oracle):
         pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
         pc.compare_fields(a.fields(), b.fields())
         assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        _same_energies(a, b)
     assert a.count(ELECTRON) == p["cell"].size
+
+
+def test_lean_open_boundaries_energy_excludes_deleted_leavers(gpu, oracle):
+    """Lean fused path between a laser and an absorbing boundary: electrons that leave through an open edge are
+    deleted (mod.rs:372-373); the kinetic energy summed inside the push kernel must not count them, and a second
+    opal_energy call (which re-reads the buckets) must agree with the first (which used the fused sum)."""
+    nx, dx = 256, 1.0e-8
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, BDY_LASER, BDY_ABSORBING, flags=FLAG_LEAN_STATE)
+    p = pc.thermal_particles(nx, 60, dx, 0.5, seed=41, ne=1.0e20)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for chunk in (1, 3, 20):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        _same_energies(a, b)
+        assert a.count(ELECTRON) == b.count(ELECTRON)
+    assert a.count(ELECTRON) < nx * 60
+    first = a.energy()       # electrons' term: summed by the push kernel of the last step
+    a.run_steps(0)           # invalidates the fused sum
+    second = a.energy()      # electrons' term: k_kinetic over the buckets
+    assert abs(first[1] - second[1]) <= 1e-12 * second[1] and first[0] == second[0]
+    pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
 
 
 def test_two_gpu_nccl_ring_matches_single_oracle_slab():
