@@ -142,8 +142,8 @@ def main():
     ap.add_argument("--nx", type=int, default=1_000_000, help="cells per GPU")
     ap.add_argument("--npc", type=int, default=1000)
     ap.add_argument("--workload", default="thermal", choices=["thermal", "two_stream"])
-    ap.add_argument("--cpu-nx", type=int, default=4000, help="cells of the bounded CPU sample")
-    ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--cpu-nx", type=int, default=40000, help="cells of the bounded CPU sample (x npc particles; about 10-30 s of host work)")
+    ap.add_argument("--cpu-steps", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--full-state", action="store_true", help="keep all reference per-particle fields (152 B/particle-step)")
     args = ap.parse_args()

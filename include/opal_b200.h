@@ -112,7 +112,12 @@ opal_status OPAL_FN(grid_shape)(opal_ctx*, int64_t* ncells_total, int64_t* left_
 
 /* Population<T>::new's inner T::create(...) (electron.rs:85, ion.rs:81, photon.rs:95): gamma and
    prev_x are derived exactly as create() does; tau NULL => +inf (electron.rs:99).  `cell` is
-   slab-local.  Any order; the library buckets by cell.  Replaces the species' previous content. */
+   slab-local.  Any order; the library buckets by cell.  Replaces the species' previous content.
+   n == 0: on a lone slab (nranks == 1) the species is absent and later calls skip it; on a slab of a
+   multi-slab run it is "present but empty here": the slab still takes part in every per-step
+   neighbour exchange (mod.rs:308-354).  A species must be uploaded (possibly with n == 0) on EVERY
+   slab or on none -- mixing the two deadlocks the ring, exactly as a rank skipping
+   Population::advance would in the reference.                                                  */
 opal_status OPAL_FN(particles_upload)(opal_ctx*, int species, int64_t n, const int64_t* cell,
                                       const double* x, const double* ux, const double* uy, const double* uz,
                                       const double* weight, const double* tau);

@@ -447,6 +447,8 @@ bool advance_photons(opal_ctx* c, bool check) {
 
 bool do_emit(opal_ctx* c, double t, double min_e, double max_a, double max_fl) {
     Buckets& E = c->bk[OPAL_ELECTRON];
+    // multi-slab: a slab that emits nothing itself still has to take part in the photon exchange of the next advance
+    if (remote(c) && !ensure_photons(c, 1)) return false;
     if (!E.allocated) return true;
     if (!E.full) return fail(c, OPAL_EINVAL, "emit_radiation needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)");
     int nph = 0;
@@ -617,7 +619,10 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
     Buckets& B = c->bk[species];
     free_buckets(B);
     B = Buckets();
-    if (n == 0) return OPAL_OK;
+    // n == 0 on a lone slab: the species does not exist and every later call skips it.  On a slab of a multi-slab run the
+    // species may live on a neighbour: allocate empty buckets so this slab takes part in the per-step neighbour exchange
+    // (every rank of the reference exchanges every step, mod.rs:308-354) and can receive migrants.
+    if (n == 0 && c->nranks == 1) return OPAL_OK;
     const int ncell = c->g.nx;
     std::vector<long long> demand(ncell, 0);
     for (int64_t i = 0; i < n; i++) {

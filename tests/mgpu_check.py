@@ -27,7 +27,9 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     gpu = lib.load()
     ok = True
-    for case, flags, fused in (("periodic", FLAG_LEAN_STATE, True), ("periodic", 0, True), ("laser", 0, False)):
+    cases = (("periodic", FLAG_LEAN_STATE, True), ("periodic", 0, True), ("laser", 0, False), ("laser_sparse", 0, False),
+             ("laser_sparse", 0, True))
+    for case, flags, fused in cases:
         g = w.global_case(case)
         design = GridDesign.unbalanced(world, g["nx"], g["xmin"], g["dx"], left=g["left"], right=g["right"])
         ring = SlabRing(gpu, design, rank, flags=flags, device=local, exchange="nccl", dist=dist)
@@ -37,7 +39,11 @@ def main():
         ring.slab.upload(ELECTRON, p["cell"][mine] - off, p["x"][mine], p["ux"][mine], p["uy"][mine], p["uz"][mine], p["weight"][mine])
         laser = w.laser_fns(g["laser"]) if g["laser"] else None
         steps = g["steps"]
-        if fused:
+        if fused and laser:
+            x2, dt = ring.slab.laser_x(), ring.slab.dt       # host-evaluated amplitudes, one per step (yee.rs:456-462; t += dt, main.rs:266)
+            ts = np.cumsum(np.concatenate([[0.0], np.full(steps - 1, dt)]))
+            ring.slab.run_steps(steps, 0.0, laser_y=[laser[0](t_, x2) for t_ in ts], laser_z=[laser[1](t_, x2) for t_ in ts])
+        elif fused:
             ring.slab.run_steps(steps)
         else:
             t = 0.0

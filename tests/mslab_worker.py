@@ -23,6 +23,11 @@ def global_case(case):
         nx, dx = 120, 2.0e-8
         p = pc.thermal_particles(nx, 12, dx, 0.4, seed=9, ne=5.0e26, cells=np.arange(30, 100))
         return dict(nx=nx, dx=dx, xmin=-1.0e-6, left=BDY_LASER, right=BDY_ABSORBING, particles=p, steps=60, laser=3.0e12)
+    if case == "laser_sparse":
+        # plasma only in a few cells left of the domain centre: the right-hand slabs start EMPTY and fill by migration
+        nx, dx = 120, 2.0e-8
+        p = pc.thermal_particles(nx, 12, dx, 0.4, seed=11, ne=5.0e26, cells=np.arange(45, 60))
+        return dict(nx=nx, dx=dx, xmin=-1.0e-6, left=BDY_LASER, right=BDY_ABSORBING, particles=p, steps=60, laser=3.0e12)
     raise ValueError(case)
 
 
