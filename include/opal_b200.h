@@ -184,6 +184,27 @@ opal_status OPAL_FN(run_steps)(opal_ctx*, int64_t nsteps, double t0, const doubl
    photon.rs:224), joules.  The caller sums over slabs (the reference: reduce_into_root).      */
 opal_status OPAL_FN(energy)(opal_ctx*, double* em, double* electrons, double* ions, double* photons);
 
+/* ---- output: distribution functions (particle/hgram.rs, particle/mod.rs:383-568) ---- */
+/* the per-particle outputs of Population::write_data (mod.rs:388-449), in the reference's units */
+typedef enum { OPAL_Q_X = 0, OPAL_Q_R, OPAL_Q_ENERGY, OPAL_Q_PX, OPAL_Q_PY, OPAL_Q_PZ, OPAL_Q_P_PERP, OPAL_Q_THETA,
+               OPAL_Q_PHI, OPAL_Q_LONGITUDE, OPAL_Q_LATITUDE, OPAL_Q_WORK, OPAL_Q_CHI, OPAL_Q_COUNT_ } opal_quantity;
+typedef enum { OPAL_W_WEIGHT = 0, OPAL_W_ENERGY = 1 } opal_hgram_weight;   /* mod.rs:496-500 */
+/* Pass 1 of Histogram::generate_1d/_2d (hgram.rs:103-124,186-204,290-316): this slab's min and max of
+   each of the ndim (1 or 2) axis quantities over its FINITE values -- ln() applied first on a log-scaled
+   axis -- and its particle count.  An empty slab returns (DBL_MAX, -DBL_MAX, 0) like hgram.rs:189.
+   The caller reduces (min, max, sum) over slabs as the reference does with all_reduce.            */
+opal_status OPAL_FN(hgram_minmax)(opal_ctx*, int species, int ndim, const int* quantity, const int* log_scaled,
+                                  double* min, double* max, int64_t* n);
+/* Pass 2 (hgram.rs:222-258, 333-366): bin this slab's particles on the GLOBAL grid (gmin, bin_sz, nbins per
+   axis; bin_sz == 0 => bin 0).  counts[] (nbins[0]*nbins[1] doubles, host) receives the weighted counts of
+   this slab BEFORE the division by the bin volume; flat index = bin[1]*nbins[1] + bin[0] as hgram.rs:357
+   (1-D: bin[0]); indices >= the array length are dropped (a value equal to the maximum, hgram.rs:253).
+   *total = sum of all weights, binned or not (hgram.rs:232).  log_density_adjust != 0 applies the
+   re-weighting of log-scaled axes, hgram.rs:236-238 / 349-355.                                     */
+opal_status OPAL_FN(hgram_bin)(opal_ctx*, int species, int ndim, const int* quantity, const int* log_scaled,
+                               const double* gmin, const double* bin_sz, const int64_t* nbins, int weight_kind,
+                               int log_density_adjust, double* counts, double* total);
+
 /* ---- multi-GPU: NCCL ring of slabs (replaces rsmpi p2p) -------------------- */
 opal_status OPAL_FN(comm_unique_id)(void* id128);                 /* ncclGetUniqueId; 128 bytes */
 opal_status OPAL_FN(comm_init)(opal_ctx*, const void* id128);     /* ncclCommInitRank(rank,nranks of create) */

@@ -60,6 +60,8 @@ SIGNATURES = {
     "field_advance": [_vp],
     "run_steps": [_vp, _i64, _f64, _vp, _vp, _int, _int, _vp],
     "energy": [_vp, _pf64, _pf64, _pf64, _pf64],
+    "hgram_minmax": [_vp, _int, _int, _vp, _vp, _vp, _vp, _pi64],
+    "hgram_bin": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _int, _int, _vp, _pf64],
     "comm_unique_id": [_vp],
     "comm_init": [_vp, _vp],
     "stream": [_vp, C.POINTER(_vp)],
@@ -121,6 +123,12 @@ class OpalABI:
             raise OpalError(st, "qed_sample")
         return out
 
+
+# opal_quantity (particle/mod.rs:455-470) and their units (mod.rs:475-486)
+QUANTITIES = ("x", "r", "energy", "px", "py", "pz", "p_perp", "theta", "phi", "longitude", "latitude", "work", "chi")
+QUANTITY_UNITS = {"x": "m", "r": "m", "energy": "MeV", "px": "MeV/c", "py": "MeV/c", "pz": "MeV/c", "p_perp": "MeV/c", "theta": "rad",
+                  "phi": "rad", "longitude": "rad", "latitude": "rad", "work": "J", "chi": "1"}
+W_WEIGHT, W_ENERGY = 0, 1
 
 PARTICLE_FIELDS = ("cell", "x", "prev_x", "ux", "uy", "uz", "weight", "gamma", "chi", "tau", "work", "y", "z", "birth_time")
 
@@ -270,6 +278,28 @@ class Slab:
         v = [C.c_double() for _ in range(4)]
         self._ck(self.abi.energy(self._h, *[C.byref(x) for x in v]), "energy")
         return tuple(x.value for x in v)   # (em, electrons, ions, photons), joules, this slab
+
+    def hgram_minmax(self, species, quantities, log_scaled=None):
+        """pass 1 of Histogram::generate_* (hgram.rs:186-204): (min[], max[], n) of this slab"""
+        nd = len(quantities)
+        q = np.array([QUANTITIES.index(v) if isinstance(v, str) else int(v) for v in quantities], dtype=np.int32)
+        lg = np.array([int(bool(v)) for v in (log_scaled or [0] * nd)], dtype=np.int32)
+        mn, mx, n = np.zeros(2), np.zeros(2), C.c_int64(0)
+        self._ck(self.abi.hgram_minmax(self._h, species, nd, _ptr(q), _ptr(lg), _ptr(mn), _ptr(mx), C.byref(n)), "hgram_minmax")
+        return mn[:nd].copy(), mx[:nd].copy(), n.value
+
+    def hgram_bin(self, species, quantities, gmin, bin_sz, nbins, log_scaled=None, weight=W_WEIGHT, log_density_adjust=True):
+        """pass 2 (hgram.rs:222-258 / 333-366): (weighted counts of this slab before /bin volume, flat; total weight)"""
+        nd = len(quantities)
+        q = np.array([QUANTITIES.index(v) if isinstance(v, str) else int(v) for v in quantities], dtype=np.int32)
+        lg = np.array([int(bool(v)) for v in (log_scaled or [0] * nd)], dtype=np.int32)
+        gmin, bin_sz = _f64arr(np.atleast_1d(gmin), nd), _f64arr(np.atleast_1d(bin_sz), nd)
+        nb = np.ascontiguousarray(np.atleast_1d(nbins), dtype=np.int64)
+        counts = np.zeros(int(np.prod(nb)))
+        total = C.c_double(0.0)
+        self._ck(self.abi.hgram_bin(self._h, species, nd, _ptr(q), _ptr(lg), _ptr(gmin), _ptr(bin_sz), _ptr(nb), int(weight),
+                                    int(bool(log_density_adjust)), _ptr(counts), C.byref(total)), "hgram_bin")
+        return counts, total.value
 
     def fields_at(self, cell, xi):
         cell = np.ascontiguousarray(np.atleast_1d(cell), dtype=np.int64)

@@ -73,6 +73,16 @@ struct Photons {
 
 }  // namespace
 
+namespace opal {   // opal_hgram.cu
+void hgram_minmax_charged(cudaStream_t, const GridDev&, const BucketDev&, int species, bool full, int ndim, const int* q, const int* lg,
+                          unsigned long long* d_mm, double* d_out4);
+void hgram_minmax_photon(cudaStream_t, const GridDev&, const PhotonDev&, int ndim, const int* q, const int* lg, unsigned long long* d_mm, double* d_out4);
+void hgram_bin_charged(cudaStream_t, const GridDev&, const BucketDev&, int species, bool full, int ndim, const int* q, const int* lg,
+                       const double* gmin, const double* bin_sz, const long long* nbins, int weight_kind, int log_adjust, double* d_counts, double* d_total);
+void hgram_bin_photon(cudaStream_t, const GridDev&, const PhotonDev&, int ndim, const int* q, const int* lg, const double* gmin,
+                      const double* bin_sz, const long long* nbins, int weight_kind, int log_adjust, double* d_counts, double* d_total);
+}
+
 struct opal_ctx {
     int device = 0, rank = 0, nranks = 1;
     uint32_t flags = 0;
@@ -975,6 +985,64 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
         if (e != cudaSuccess) fail(c, OPAL_ECUDA, std::string("run_steps: ") + cudaGetErrorString(e));
     }
     return (opal_status)c->status;
+}
+
+static bool hgram_args_ok(int species, int ndim, const int* q) {
+    if (species < 0 || species > 2 || (ndim != 1 && ndim != 2) || !q) return false;
+    for (int d = 0; d < ndim; d++) if (q[d] < 0 || q[d] >= OPAL_Q_COUNT_) return false;
+    return true;
+}
+
+opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, const int* lg, double* mn, double* mx, int64_t* n) {
+    CHECK_CTX(c);
+    if (!hgram_args_ok(species, ndim, q) || !mn || !mx || !n) return OPAL_EINVAL;
+    for (int d = 0; d < ndim; d++) { mn[d] = std::numeric_limits<double>::max(); mx[d] = -std::numeric_limits<double>::max(); }   // hgram.rs:189
+    opal_status st = opal_particles_count(c, species, n);
+    if (st != OPAL_OK || *n == 0) return st;
+    unsigned long long* d_mm = nullptr;
+    CU(cudaMalloc(&d_mm, 4 * sizeof(unsigned long long) + 4 * sizeof(double)));
+    double* d_out = reinterpret_cast<double*>(d_mm + 4);
+    if (species == OPAL_PHOTON) hgram_minmax_photon(c->stream, c->g, pdev(c, c->ph_cur), ndim, q, lg, d_mm, d_out);
+    else hgram_minmax_charged(c->stream, c->g, bdev(c, species), species, c->bk[species].full, ndim, q, lg, d_mm, d_out);
+    c->launches += 3;
+    double h[4];
+    CU(cudaMemcpyAsync(h, d_out, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(d_mm);
+    for (int d = 0; d < ndim; d++) { mn[d] = h[2 * d]; mx[d] = h[2 * d + 1]; }
+    return OPAL_OK;
+}
+
+opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
+                           const int64_t* nbins, int weight_kind, int log_density_adjust, double* counts, double* total) {
+    CHECK_CTX(c);
+    if (!hgram_args_ok(species, ndim, q) || !gmin || !bin_sz || !nbins || !counts || !total) return OPAL_EINVAL;
+    if (weight_kind != OPAL_W_WEIGHT && weight_kind != OPAL_W_ENERGY) return OPAL_EINVAL;
+    long long nb[2] = {1, 1};
+    size_t len = 1;
+    for (int d = 0; d < ndim; d++) {
+        if (nbins[d] < 1 || nbins[d] > (1ll << 28)) return OPAL_EINVAL;
+        nb[d] = nbins[d];
+        len *= (size_t)nbins[d];
+    }
+    if (len > (1ull << 30)) return OPAL_EINVAL;
+    for (size_t i = 0; i < len; i++) counts[i] = 0.0;
+    *total = 0.0;
+    int64_t n = 0;
+    opal_status st = opal_particles_count(c, species, &n);
+    if (st != OPAL_OK || n == 0) return st;
+    double* d_counts = nullptr;
+    CU(cudaMalloc(&d_counts, (len + 1) * sizeof(double)));
+    CU(cudaMemsetAsync(d_counts, 0, (len + 1) * sizeof(double), c->stream));
+    if (species == OPAL_PHOTON) hgram_bin_photon(c->stream, c->g, pdev(c, c->ph_cur), ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust, d_counts, d_counts + len);
+    else hgram_bin_charged(c->stream, c->g, bdev(c, species), species, c->bk[species].full, ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust,
+                           d_counts, d_counts + len);
+    c->launches++;
+    CU(cudaMemcpyAsync(counts, d_counts, len * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(total, d_counts + len, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaFree(d_counts);
+    return OPAL_OK;
 }
 
 opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, double* ke_ph) {

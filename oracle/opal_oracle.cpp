@@ -1207,6 +1207,115 @@ opal_status opal_ref_energy(opal_ctx* g, double* em, double* ke_e, double* ke_i,
     return OPAL_OK;
 }
 
+// ---- output histograms: particle/hgram.rs + the accessors of particle/mod.rs:388-449 -----------
+extern "C++" {
+namespace {
+struct PtOut { double pos, r, energy, p[3], work, chi, weight; };
+inline PtOut pt_out(const opal_ctx* g, const Electron& e) {
+    PtOut t; const double x0 = g->cell[(size_t)g->left_size].x;          // Grid::xmin, yee.rs:531
+    t.pos = x0 + ((double)e.cell + e.x) * g->dx;                        // mod.rs:388-391
+    t.r = std::hypot(e.y, e.z); t.energy = e.gamma * ELECTRON_MASS_MEV;   // electron.rs:109,117
+    Vec3 p = e.u * ELECTRON_MASS_MEV; t.p[0] = p.x; t.p[1] = p.y; t.p[2] = p.z;   // electron.rs:156
+    t.work = e.work; t.chi = e.chi; t.weight = e.weight; return t;
+}
+inline PtOut pt_out(const opal_ctx* g, const Ion& i) {
+    PtOut t; const double x0 = g->cell[(size_t)g->left_size].x;
+    t.pos = x0 + ((double)i.cell + i.x) * g->dx;
+    t.r = 0.0; t.energy = i.gamma_m1 * (i.A * PROTON_MASS / ELECTRON_MASS) * ELECTRON_MASS_MEV;   // ion.rs:107,128
+    Vec3 p = i.u * (i.A * PROTON_MASS / ELECTRON_MASS) * ELECTRON_MASS_MEV; t.p[0] = p.x; t.p[1] = p.y; t.p[2] = p.z;   // ion.rs:140
+    t.work = i.work; t.chi = 0.0; t.weight = i.weight; return t;
+}
+inline PtOut pt_out(const opal_ctx* g, const Photon& ph) {
+    PtOut t; const double x0 = g->cell[(size_t)g->left_size].x;
+    t.pos = x0 + ((double)ph.cell + ph.x) * g->dx;
+    t.r = std::hypot(ph.y, ph.z); t.energy = std::sqrt(norm_sqr(ph.k)) * ELECTRON_MASS_MEV;   // photon.rs:189,216
+    Vec3 p = ph.k * ELECTRON_MASS_MEV; t.p[0] = p.x; t.p[1] = p.y; t.p[2] = p.z;               // photon.rs:205
+    t.work = 0.0; t.chi = ph.chi; t.weight = ph.weight; return t;
+}
+inline double quantity(const PtOut& t, int q) {
+    switch (q) {
+        case OPAL_Q_X: return t.pos;
+        case OPAL_Q_R: return t.r;
+        case OPAL_Q_ENERGY: return t.energy;
+        case OPAL_Q_PX: return t.p[0];
+        case OPAL_Q_PY: return t.p[1];
+        case OPAL_Q_PZ: return t.p[2];
+        case OPAL_Q_P_PERP: return std::hypot(t.p[1], t.p[2]);                                   // mod.rs:417-420
+        case OPAL_Q_THETA: { double mag = std::sqrt(t.p[0] * t.p[0] + t.p[1] * t.p[1] + t.p[2] * t.p[2]); return std::acos(t.p[0] / mag); }
+        case OPAL_Q_PHI: return std::atan2(t.p[2], t.p[1]);
+        case OPAL_Q_LONGITUDE: return std::atan2(t.p[1], -t.p[0]);
+        case OPAL_Q_LATITUDE: { double mag = std::sqrt(t.p[0] * t.p[0] + t.p[1] * t.p[1] + t.p[2] * t.p[2]); return std::asin(t.p[2] / mag); }
+        case OPAL_Q_WORK: return t.work;
+        default: return t.chi;
+    }
+}
+inline size_t as_usize(double v) {   // Rust's saturating float -> usize cast
+    if (!(v > 0.0)) return 0;
+    if (v >= 18446744073709551615.0) return ~(size_t)0;
+    return (size_t)v;
+}
+template <class T> void hgram_minmax(const opal_ctx* g, const Population<T>& pop, int ndim, const int* q, const int* lg, double* mn, double* mx) {
+    // min_max_by, hgram.rs:103-124 (over finite values; the first element's seeding of min/max is immaterial for finite data)
+    for (const T& pt : pop.store) {
+        const PtOut t = pt_out(g, pt);
+        for (int d = 0; d < ndim; d++) {
+            double v = quantity(t, q[d]);
+            if (lg && lg[d]) v = std::log(v);
+            if (std::isfinite(v)) { mn[d] = std::fmin(mn[d], v); mx[d] = std::fmax(mx[d], v); }
+        }
+    }
+}
+template <class T> void hgram_bin(const opal_ctx* g, const Population<T>& pop, int ndim, const int* q, const int* lg, const double* gmin,
+                                  const double* bin_sz, const int64_t* nbins, int weight_kind, int adjust, double* counts, size_t len, double* total) {
+    for (const T& pt : pop.store) {                                       // hgram.rs:222-258, 333-366
+        const PtOut t = pt_out(g, pt);
+        double w = weight_kind == OPAL_W_ENERGY ? t.energy * t.weight : t.weight;   // mod.rs:496-499
+        *total = *total + w;
+        double v[2] = {0.0, 0.0};
+        bool finite = true;
+        for (int d = 0; d < ndim; d++) {
+            v[d] = quantity(t, q[d]);
+            if (lg && lg[d]) v[d] = std::log(v[d]);
+            finite = finite && std::isfinite(v[d]);
+        }
+        if (!finite) continue;
+        size_t bin[2] = {0, 0};
+        for (int d = 0; d < ndim; d++) {
+            bin[d] = bin_sz[d] == 0.0 ? 0 : as_usize(std::floor((v[d] - gmin[d]) / bin_sz[d]));
+            if (lg && lg[d] && adjust)
+                w *= bin_sz[d] == 0.0 ? 1.0 : bin_sz[d] / (std::exp(gmin[d] + (double)bin[d] * bin_sz[d]) * std::expm1(bin_sz[d]));   // hgram.rs:126-128
+        }
+        const size_t fbin = ndim == 1 ? bin[0] : bin[1] * (size_t)nbins[1] + bin[0];   // hgram.rs:357
+        if (fbin < len) counts[fbin] = counts[fbin] + w;
+    }
+}
+}  // namespace
+}  // extern "C++"
+
+opal_status opal_ref_hgram_minmax(opal_ctx* g, int species, int ndim, const int* q, const int* lg, double* mn, double* mx, int64_t* n) {
+    CHECK_CTX(g);
+    if (species < 0 || species > 2 || (ndim != 1 && ndim != 2) || !q || !mn || !mx || !n) return OPAL_EINVAL;
+    for (int d = 0; d < ndim; d++) { if (q[d] < 0 || q[d] >= OPAL_Q_COUNT_) return OPAL_EINVAL; mn[d] = std::numeric_limits<double>::max(); mx[d] = -mn[d]; }
+    if (species == OPAL_ELECTRON) { *n = (int64_t)g->electrons.store.size(); hgram_minmax(g, g->electrons, ndim, q, lg, mn, mx); }
+    else if (species == OPAL_ION) { *n = (int64_t)g->ions.store.size(); hgram_minmax(g, g->ions, ndim, q, lg, mn, mx); }
+    else { *n = (int64_t)g->photons.store.size(); hgram_minmax(g, g->photons, ndim, q, lg, mn, mx); }
+    return OPAL_OK;
+}
+
+opal_status opal_ref_hgram_bin(opal_ctx* g, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
+                               const int64_t* nbins, int weight_kind, int adjust, double* counts, double* total) {
+    CHECK_CTX(g);
+    if (species < 0 || species > 2 || (ndim != 1 && ndim != 2) || !q || !gmin || !bin_sz || !nbins || !counts || !total) return OPAL_EINVAL;
+    size_t len = 1;
+    for (int d = 0; d < ndim; d++) { if (nbins[d] < 1 || q[d] < 0 || q[d] >= OPAL_Q_COUNT_) return OPAL_EINVAL; len *= (size_t)nbins[d]; }
+    for (size_t i = 0; i < len; i++) counts[i] = 0.0;
+    *total = 0.0;
+    if (species == OPAL_ELECTRON) hgram_bin(g, g->electrons, ndim, q, lg, gmin, bin_sz, nbins, weight_kind, adjust, counts, len, total);
+    else if (species == OPAL_ION) hgram_bin(g, g->ions, ndim, q, lg, gmin, bin_sz, nbins, weight_kind, adjust, counts, len, total);
+    else hgram_bin(g, g->photons, ndim, q, lg, gmin, bin_sz, nbins, weight_kind, adjust, counts, len, total);
+    return OPAL_OK;
+}
+
 opal_status opal_ref_comm_unique_id(void*) { return OPAL_ENCCL; }
 opal_status opal_ref_comm_init(opal_ctx*, const void*) { return OPAL_ENCCL; }
 opal_status opal_ref_stream(opal_ctx*, void** s) { if (s) *s = nullptr; return OPAL_OK; }
