@@ -1,0 +1,240 @@
+// main.cpp -- the opal driver over the C ABI: src/main.rs:47-286 with every hot-path call replaced by its
+// libopal_b200.so entry point (include/opal_b200.h).  The reference's driver is Rust; no Rust toolchain exists in
+// this image, so the host side is C++ (INTEGRATION.md shows the Rust `extern "C"` block for the same calls).
+//
+//   opal_b200_driver input.yaml [--ranks N] [--device D] [--lean] [--outputs K] [--quiet]
+//
+// --ranks N    one process per GPU (the reference: mpirun -n N), x-slabs from GridDesign, NCCL ring inside the library
+// --lean       keep only (x, u, w) per particle (QED off, deposition on, no r/work/chi outputs): the 80 B/particle-step layout
+// --outputs K  stop after output K (for tests; default: run to `end`)
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "config.h"
+#include "constants.h"
+#include "grid_design.h"
+#include "loader.h"
+#include "output.h"
+#include "ranks.h"
+
+using namespace opal_driver;
+
+namespace {
+
+void ck(opal_status st, opal_ctx* ctx, const char* where) {
+    if (st != OPAL_OK) {
+        const char* msg = ctx ? OPAL_FN(last_error)(ctx) : "";
+        throw std::runtime_error(std::string(where) + " failed (status " + std::to_string((int)st) + "): " + (msg ? msg : ""));
+    }
+}
+
+template <class F> bool optional_read(F f) {      // `.ok()` / `.unwrap_or()` of main.rs:72-82
+    try { f(); return true; } catch (const ConfigError&) { return false; }
+}
+
+struct Options {
+    std::string input;
+    int ranks = 1, device = -1;
+    bool lean = false, quiet = false;
+    long outputs = -1;
+};
+
+int run(const Options& opt, Ranks& ranks) {
+    const int id = ranks.rank(), np = ranks.nranks();
+    Xoshiro256StarStar rng((uint64_t)id);                                           // main.rs:53
+
+    std::string output_dir = ".";                                                   // main.rs:61 (an empty parent means the cwd here)
+    {
+        const size_t slash = opt.input.find_last_of('/');
+        if (slash != std::string::npos) output_dir = slash == 0 ? "/" : opt.input.substr(0, slash);
+    }
+
+    Config input = Config::from_file(opt.input);                                    // main.rs:65-66
+    input.with_context("constants");
+
+    const size_t nx = input.read_usize("control", "nx");                           // main.rs:68-76
+    const double xmin = input.read_f64("control", "xmin");
+    const double dx = input.read_f64("control", "dx");
+    const double dt = 0.95 * dx / constants::SPEED_OF_LIGHT;
+    const double tstart = input.read_f64("control", "start");
+    const double tend = input.read_f64("control", "end");
+    const bool current_deposition = input.read_bool("control", "current_deposition");
+    const size_t output_frequency = input.read_usize("control", "n_outputs");
+    bool balance = true;
+    optional_read([&] { balance = input.read_bool("control", "balance"); });
+
+    const bool photon_emission = input.read_bool("qed", "photon_emission");         // main.rs:78-79
+    const bool photon_absorption = input.read_bool("qed", "photon_absorption");
+    double photon_energy_min = 0.0, photon_angle_max = 0.0, max_formation_length = 0.0;
+    const bool has_emin = optional_read([&] { photon_energy_min = 1.0e-6 * input.read_f64("qed", "photon_energy_min") / constants::ELEMENTARY_CHARGE; });
+    const bool has_amax = optional_read([&] { photon_angle_max = input.read_f64("qed", "photon_angle_max"); });
+    const bool has_fl = optional_read([&] { max_formation_length = input.read_f64("qed", "max_formation_length"); });
+    if (photon_absorption)
+        throw std::runtime_error("qed.photon_absorption: photon absorption / stimulated emission (interactions.rs:145-340) is outside this build's hot path");
+
+    // laser (main.rs:88-104): both components or a config error; no laser section => periodic
+    std::function<double(double, double)> laser_y, laser_z;
+    int left_bdy = OPAL_BDY_INTERNAL, right_bdy = OPAL_BDY_INTERNAL;
+    if (input.contains("laser")) {
+        laser_y = input.func2("laser", "Ey", "t", "x");
+        laser_z = input.func2("laser", "Ez", "t", "x");
+        left_bdy = OPAL_BDY_LASER;
+        right_bdy = OPAL_BDY_ABSORBING;
+    }
+
+    const size_t min_size = 2 * OPAL_GHOST_SIZE;                                    // YeeGrid::min_size, yee.rs:782-784
+    GridDesign design = balance ? GridDesign::balanced(np, nx, xmin, dx, min_size, input.func("electrons", "ne", "x"))   // main.rs:108-113
+                                : GridDesign::unbalanced(np, nx, xmin, dx, min_size);
+    const size_t my_nx = design.nx[(size_t)id];
+    const double my_xmin = xmin + design.offset[(size_t)id];
+
+    // ---- the slab context (YeeGrid::build, yee.rs:272-319) ----
+    const uint32_t flags = opt.lean ? OPAL_FLAG_LEAN_STATE : 0u;
+    opal_ctx* ctx = nullptr;
+    const int device = opt.device >= 0 ? opt.device + id : id;
+    ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, flags), nullptr, "opal_create");
+    ranks.connect(ctx);                                                             // NCCL ring (np > 1)
+
+    // ---- particle initialisation (main.rs:117-168) ----
+    auto upload = [&](int species, const ParticleArrays& p) {
+        ck(OPAL_FN(particles_upload)(ctx, species, (int64_t)p.size(), p.cell.data(), p.x.data(), p.ux.data(), p.uy.data(), p.uz.data(),
+                                     p.weight.data(), p.tau.empty() ? nullptr : p.tau.data()), ctx, "particles_upload");
+    };
+    const size_t epc = input.read_usize("electrons", "npc");
+    const std::vector<std::string> eospec = input.read_strings("electrons", "output");
+    if (epc > 0) {
+        upload(OPAL_ELECTRON, load_population(epc, input.func("electrons", "ne", "x"), input.func3("electrons", "ux", "x", "urand", "nrand"),
+                                              input.func3("electrons", "uy", "x", "urand", "nrand"), input.func3("electrons", "uz", "x", "urand", "nrand"),
+                                              (int64_t)my_nx, my_xmin, dx, rng, true));
+    }
+    const size_t ipc = input.read_usize("ions", "npc");
+    std::vector<std::string> iospec;
+    std::string ion_name;
+    if (ipc > 0) {
+        iospec = input.read_strings("ions", "output");
+        ion_name = input.read_string("ions", "name");
+        const double ion_charge = input.read_f64("ions", "Z");
+        const double ion_mass = input.read_f64("ions", "A");
+        ck(OPAL_FN(set_ion)(ctx, ion_charge, ion_mass), ctx, "set_ion");            // with_charge_state, main.rs:145-147
+        upload(OPAL_ION, load_population(ipc, input.func("ions", "ni", "x"), input.func3("ions", "ux", "x", "urand", "nrand"),
+                                         input.func3("ions", "uy", "x", "urand", "nrand"), input.func3("ions", "uz", "x", "urand", "nrand"),
+                                         (int64_t)my_nx, my_xmin, dx, rng, false));
+    }
+    std::vector<std::string> pospec;
+    bool photons_on = false;
+    if (photon_emission || photon_absorption) {                                     // main.rs:154-170
+        const size_t ppc = input.read_usize("photons", "npc");
+        pospec = input.read_strings("photons", "output");
+        photons_on = true;
+        ParticleArrays p;
+        if (ppc > 0) {
+            p = load_population(ppc, input.func("photons", "nph", "x"), input.func3("photons", "ux", "x", "urand", "nrand"),
+                                input.func3("photons", "uy", "x", "urand", "nrand"), input.func3("photons", "uz", "x", "urand", "nrand"),
+                                (int64_t)my_nx, my_xmin, dx, rng, true);
+        }
+        if (ppc > 0 || np > 1) upload(OPAL_PHOTON, p);
+    }
+
+    // ---- time loop (main.rs:184-267) ----
+    double t = tstart;
+    const size_t total_steps = (size_t)((tend - tstart) / dt);
+    const size_t steps_bt_output = total_steps / output_frequency;
+    double x2 = 0.0;
+    ck(OPAL_FN(laser_x)(ctx, &x2), ctx, "laser_x");
+    if (id == 0 && !opt.quiet)
+        std::printf("Running %d task%s on %d GPU%s (libopal_b200: one x-slab per GPU)...\n", np, np > 1 ? "s" : "", np, np > 1 ? "s" : "");
+
+    auto write_all = [&](size_t index) {                                             // main.rs:218-222
+        write_grid(ctx, output_dir, index, ranks);
+        write_population(ctx, OPAL_ELECTRON, "electron", eospec, output_dir, index, ranks);
+        if (ipc > 0) write_population(ctx, OPAL_ION, ion_name, iospec, output_dir, index, ranks);
+        if (photons_on) write_population(ctx, OPAL_PHOTON, "photon", pospec, output_dir, index, ranks);
+        write_energies(ctx, output_dir, index, ranks);
+    };
+
+    double filters[3];
+    const double nan = std::nan("");
+    filters[0] = has_emin ? photon_energy_min : nan;
+    filters[1] = has_amax ? photon_angle_max : nan;
+    filters[2] = has_fl ? max_formation_length : nan;
+
+    const auto wall0 = std::chrono::steady_clock::now();
+    double loop_seconds = 0.0;
+    int64_t particle_steps = 0;
+    std::vector<double> ly(steps_bt_output, 0.0), lz(steps_bt_output, 0.0);
+    size_t i = 0;
+    for (; i < output_frequency; i++) {
+        write_all(i);
+        if (id == 0 && !opt.quiet) {
+            const double rt = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+            std::printf("Output %4zu at t = %.6e s, RT = %.2f s...\n", i, t, rt);
+            std::fflush(stdout);
+        }
+        if (opt.outputs >= 0 && (long)i >= opt.outputs) break;
+        // the laser amplitudes of the next steps_bt_output steps, at the times main.rs:266 accumulates
+        const double t0 = t;
+        for (size_t j = 0; j < steps_bt_output; j++) {
+            if (left_bdy == OPAL_BDY_LASER && id == 0) { ly[j] = laser_y(t, x2); lz[j] = laser_z(t, x2); }   // yee.rs:456-462
+            t += dt;
+        }
+        int64_t n_e = 0, n_i = 0;
+        OPAL_FN(particles_count)(ctx, OPAL_ELECTRON, &n_e);
+        OPAL_FN(particles_count)(ctx, OPAL_ION, &n_i);
+        const auto c0 = std::chrono::steady_clock::now();
+        ck(OPAL_FN(run_steps)(ctx, (int64_t)steps_bt_output, t0, ly.data(), lz.data(), current_deposition ? 1 : 0, photon_emission ? 1 : 0, filters),
+           ctx, "run_steps");                                                        // main.rs:238-267, steps_bt_output times
+        loop_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();
+        particle_steps += (n_e + n_i) * (int64_t)steps_bt_output;
+    }
+    if (i == output_frequency) {
+        write_all(output_frequency);                                                 // main.rs:271-276
+        if (id == 0 && !opt.quiet) {
+            const double rt = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
+            std::printf("Output %4zu at t = %.6e s, RT = %.2f s\n", output_frequency, t, rt);
+        }
+    }
+    double ps[2] = {(double)particle_steps, 0.0};
+    ranks.sum(ps, 1);
+    if (id == 0 && !opt.quiet && loop_seconds > 0.0)
+        std::printf("time loop: %.3f s, %.4e charged-particle-steps/s\n", loop_seconds, ps[0] / loop_seconds);
+    OPAL_FN(destroy)(ctx);
+    return 0;
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+    Options opt;
+    for (int a = 1; a < argc; a++) {
+        const std::string s = argv[a];
+        if (s == "--ranks" && a + 1 < argc) opt.ranks = std::atoi(argv[++a]);
+        else if (s == "--device" && a + 1 < argc) opt.device = std::atoi(argv[++a]);
+        else if (s == "--outputs" && a + 1 < argc) opt.outputs = std::atol(argv[++a]);
+        else if (s == "--lean") opt.lean = true;
+        else if (s == "--quiet") opt.quiet = true;
+        else if (!s.empty() && s[0] != '-' && opt.input.empty()) opt.input = s;
+        else { std::fprintf(stderr, "unknown argument %s\n", s.c_str()); return 2; }
+    }
+    if (opt.input.empty()) {                                                         // main.rs:57-59
+        std::fprintf(stderr, "%s\n", ConfigError{ConfigErrorKind::MissingFile, "", ""}.message().c_str());
+        return 1;
+    }
+    if (opt.ranks < 1) opt.ranks = 1;
+    return launch_ranks(opt.ranks, [&](Ranks& ranks) -> int {
+        try {
+            return run(opt, ranks);
+        } catch (const ConfigError& e) {
+            std::fprintf(stderr, "Error: %s\n", e.message().c_str());
+        } catch (const std::exception& e) {
+            std::fprintf(stderr, "Error: %s\n", e.what());
+        }
+        return 1;
+    });
+}

@@ -1,0 +1,281 @@
+"""Host side of the driver (opal_b200/driver): the input reader (setup.rs), the meval-compatible expression evaluator,
+Rust-style number formatting, output-spec parsing (particle/mod.rs:451-540), the FITS writer (hgram.rs:394-426), and a
+small end-to-end run of the driver built against the CPU oracle (oracle/opal_ref_driver).  No GPU."""
+import ctypes as C
+import math
+import pathlib
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+DRV = ROOT / "opal_b200" / "driver"
+
+
+@pytest.fixture(scope="module")
+def host():
+    subprocess.check_call(["make", "-C", str(DRV), "libopal_driver_host.so"], stdout=subprocess.DEVNULL)
+    lib = C.CDLL(str(DRV / "libopal_driver_host.so"))
+    lib.opal_drv_config_read.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_double, C.c_double, C.c_double,
+                                         C.POINTER(C.c_double), C.c_char_p, C.c_int]
+    lib.opal_drv_expr_eval.argtypes = [C.c_char_p, C.POINTER(C.c_double)]
+    lib.opal_drv_format.argtypes = [C.c_int, C.c_double, C.c_char_p, C.c_int]
+    lib.opal_drv_output_spec.argtypes = [C.c_char_p, C.c_char_p, C.c_long, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+    lib.opal_drv_write_fits.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
+    lib.opal_drv_rng_stream.argtypes = [C.c_ulonglong, C.c_long, C.c_void_p]
+    return lib
+
+
+def read(host, yaml, section, field, kind=0, arg=b"x", x=0.0, y=0.0, z=0.0):
+    out, buf = C.c_double(0.0), C.create_string_buffer(4096)
+    rc = host.opal_drv_config_read(yaml.encode(), section.encode(), field.encode(), kind, arg, x, y, z, C.byref(out), buf, 4096)
+    return rc, out.value, buf.value.decode()
+
+
+def ev(host, text):
+    out = C.c_double(0.0)
+    rc = host.opal_drv_expr_eval(text.encode(), C.byref(out))
+    return None if rc else out.value
+
+
+# the reference's own parser test, setup.rs:446-484 (text verbatim, including its indentation)
+CONFIG_PARSER = """---
+        control:
+          dx: 0.001
+          nx: 4000
+          ne: sin(a * x)
+          ib: a * b^3
+
+        extra:
+          dx: 160
+
+        constants:
+          a: 2.0 * pi
+          b: 17.0
+        """
+
+
+def test_reference_config_parser_golden(host):
+    assert read(host, CONFIG_PARSER, "control", "dx") == (0, 0.001, "")
+    assert read(host, CONFIG_PARSER, "control", "nx", kind=1)[:2] == (0, 4000.0)
+    assert read(host, CONFIG_PARSER, "control", "ib")[1] == 2.0 * math.pi * 17.0 ** 3          # assert_eq! in the reference
+    assert read(host, CONFIG_PARSER, "extra", "dx")[:2] == (0, 160.0)                            # integer -> f64
+    assert read(host, CONFIG_PARSER, "control", "ne", kind=4, x=0.6)[1] == math.sin(2.0 * math.pi * 0.6)
+
+
+def test_config_errors_and_type_dispatch(host):
+    y = "control:\n nx: 10\n dx: 1.5\n flag: true\n name: abc\n expr: 2*micro\n\nconstants:\n k: 3\n r: 2.5\n s: r + 1\n"
+    assert read(host, y, "nope", "nx")[0] == 2 and 'Could not find section "nope"' in read(host, y, "nope", "nx")[2]
+    assert read(host, y, "control", "zz")[0] == 3
+    assert read(host, y, "control", "dx", kind=1)[0] == 4            # Real is not an integer (setup.rs:302-310)
+    assert read(host, y, "control", "nx", kind=2)[0] == 4
+    assert read(host, y, "control", "flag", kind=2)[:2] == (0, 1.0)
+    assert read(host, y, "control", "name")[0] == 4                  # unknown variable
+    assert read(host, y, "control", "expr")[1] == 2 * 1.0e-6
+    # constants: integers are ignored (setup.rs:164-175), a constant cannot use another constant (setup.rs:160)
+    y2 = y.replace("expr: 2*micro", "expr: k")
+    assert read(host, y2, "control", "expr")[0] == 4
+    assert read(host, y.replace("expr: 2*micro", "expr: r"), "control", "expr")[1] == 2.5
+    assert read(host, y.replace("expr: 2*micro", "expr: s"), "control", "expr")[0] == 4
+    assert read(host, y, "laser", "", kind=7)[1] == 0.0 and read(host, y, "control", "", kind=7)[1] == 1.0
+
+
+def test_expression_semantics(host):
+    assert ev(host, "1 + 2 * 3") == 7.0
+    assert ev(host, "-2^2") == -4.0                    # unary minus binds weaker than ^
+    assert ev(host, "2^-1") == 0.5
+    assert ev(host, "2^3^2") == 512.0                  # right associative
+    assert ev(host, "7 % 4") == 3.0
+    assert ev(host, "10 - 4 - 3") == 3.0 and ev(host, "16 / 4 / 2") == 2.0
+    assert ev(host, "max(1, 5, 3) + min(4, 2)") == 7.0
+    assert ev(host, "sqrt(16) + abs(-3) + floor(2.7) + ceil(2.1) + round(2.5) + signum(-4)") == 4 + 3 + 2 + 3 + 3 - 1
+    assert ev(host, "exp(ln(2.0))") == pytest.approx(2.0, rel=1e-15)
+    assert ev(host, "atan2(1, 1)") == math.atan2(1, 1)
+    assert ev(host, "3!") == 6.0
+    assert ev(host, "2.5e-3 * 4") == 0.01
+    assert ev(host, "pi") == math.pi and ev(host, "e") == math.e      # meval's own e; opal's context overrides it (setup.rs:140)
+    for bad in ("1 +", "(1", "1)", "foo(1)", "1 2", "*3", "unknown"):
+        assert ev(host, bad) is None, bad
+
+
+def test_example_inputs_read_like_the_reference(host):
+    """the three BASELINE example files (embedded here: /root/reference does not travel)"""
+    c, e, me, eps0 = 2.997925e8, 1.602177e-19, 9.109383e-31, 8.854188e-12
+    two = "---\ncontrol:\n dx: 500\n nx: 1000\n xmin: 0.0\n\nelectrons:\n npc: 100\n ne: 20.0\n ux: drift_u * (1.0 + 0.001 * nrand) * (2.0 * floor(urand - 0.5) + 1.0)\n output: x:px\n\nions:\n npc: 0\n \nconstants:\n drift_u: 2.5e-24 / (me * c)\n"
+    assert read(host, two, "control", "dx")[1] == 500.0
+    assert read(host, two, "electrons", "ne", kind=4, x=3.0)[1] == 20.0
+    d = 2.5e-24 / (me * c)
+    assert read(host, two, "electrons", "ux", kind=5, x=0.0, y=0.75, z=2.0)[1] == d * (1.0 + 0.001 * 2.0) * (2.0 * math.floor(0.75 - 0.5) + 1.0)
+    assert read(host, two, "electrons", "ux", kind=5, x=0.0, y=0.25, z=2.0)[1] == d * (1.0 + 0.001 * 2.0) * (2.0 * math.floor(0.25 - 0.5) + 1.0)
+    assert read(host, two, "electrons", "output", kind=3)[2] == "x:px"
+    hb = ("control:\n dx: micro / 1000\n xmin: -10*micro\n start: -20.0e-6/c\n\nelectrons:\n ne: density * critical(omega) * step(x,xmin,xmax)\n"
+          " ux: sqrt(kT/(m*c^2)) * nrand\n output: [x:px, x:p_perp, py:pz]\n\nions:\n name: carbon\n Z: Z\n\nlaser:\n"
+          " Ey: (a0*me*c*omega/e) * gauss_pulse_re(t,x,omega,sigma)\n\nconstants:\n density: 100.0\n a0: 300.0\n omega: 2*pi*c/0.8e-6\n"
+          " sigma: pi * 4.0 / sqrt(ln(2.0))\n xmin: 0.0 * micro\n xmax: 5.0 * micro\n Z: 6.0\n kT: 500 * eV\n")
+    omega = 2 * math.pi * c / 0.8e-6
+    assert read(host, hb, "control", "dx")[1] == 1.0e-6 / 1000
+    assert read(host, hb, "control", "xmin")[1] == -10 * 1.0e-6
+    assert read(host, hb, "control", "start")[1] == -20.0e-6 / c
+    crit = eps0 * me * omega ** 2 / e ** 2
+    assert read(host, hb, "electrons", "ne", kind=4, x=1.0e-6)[1] == pytest.approx(100.0 * crit, rel=1e-15)
+    assert read(host, hb, "electrons", "ne", kind=4, x=5.0e-6)[1] == 0.0 and read(host, hb, "electrons", "ne", kind=4, x=-1e-9)[1] == 0.0
+    assert read(host, hb, "electrons", "ux", kind=5, x=0.0, y=0.0, z=1.5)[1] == pytest.approx(math.sqrt(500 * e / (me * c * c)) * 1.5, rel=1e-15)
+    assert read(host, hb, "electrons", "output", kind=3)[2].split("\n") == ["x:px", "x:p_perp", "py:pz"]
+    assert read(host, hb, "ions", "Z")[1] == 6.0
+    sigma = math.pi * 4.0 / math.sqrt(math.log(2.0))
+    t, x = 1.0e-15, 2.0e-7
+    phi = omega * (t - x / c)
+    want = (300.0 * me * c * omega / e) * (math.sin(phi) + phi * math.cos(phi) / sigma ** 2) * math.exp(-phi ** 2 / (2 * sigma ** 2))
+    assert read(host, hb, "laser", "Ey", kind=6, x=t, y=x)[1] == pytest.approx(want, rel=1e-13)
+    cb = ("qed:\n photon_angle_max: 50 * milli\n\nphotons:\n output: [x, energy, energy:(log;energy), longitude:latitude, longitude:latitude:(energy)]\n\n"
+          "laser:\n Ey: >\n  (a0*m*c*omega/e)\n  *sin(omega*(t-x/c))\n  *exp(-ln(2.0)*(omega*(t-x/c))^2/(2.0*pi^2*ncycles^2))\n Ez: 0.0\n\n"
+          "constants:\n a0: 20.0\n omega: 2*pi*c/0.8e-6\n ncycles: 4.0\n xmin: (20 - 2.5) * micro\n")
+    assert read(host, cb, "qed", "photon_angle_max")[1] == 50 * 1.0e-3
+    assert read(host, cb, "photons", "output", kind=3)[2].split("\n") == ["x", "energy", "energy:(log;energy)", "longitude:latitude",
+                                                                           "longitude:latitude:(energy)"]
+    want = (20.0 * me * c * omega / e) * math.sin(phi) * math.exp(-math.log(2.0) * phi ** 2 / (2.0 * math.pi ** 2 * 16.0))
+    assert read(host, cb, "laser", "Ey", kind=6, x=t, y=x)[1] == pytest.approx(want, rel=1e-13)
+    assert read(host, cb, "laser", "Ez", kind=6, x=t, y=x)[1] == 0.0
+
+
+def test_rust_number_formats(host):
+    def f(kind, v):
+        buf = C.create_string_buffer(400)
+        host.opal_drv_format(kind, v, buf, 400)
+        return buf.value.decode()
+    # {:e}: shortest round-trip digits, no exponent padding
+    assert [f(0, v) for v in (0.0, 1.0, 500.0, 1.5e-7, -2.5, 1.0e21, 0.1, 123456.789)] == \
+        ["0e0", "1e0", "5e2", "1.5e-7", "-2.5e0", "1e21", "1e-1", "1.23456789e5"]
+    assert f(0, 3.393773386715751e-5) == "3.393773386715751e-5"
+    # {:.6e}
+    assert [f(1, v) for v in (0.0, 1.2001353e-6, 6.350928e-15, 12345678.9)] == ["0.000000e0", "1.200135e-6", "6.350928e-15", "1.234568e7"]
+    # {}: positional
+    assert [f(2, v) for v in (0.0, 1.0, 0.00015, -12.5, 1.0e21, 1.0e-7)] == ["0", "1", "0.00015", "-12.5", "1000000000000000000000", "0.0000001"]
+    assert f(0, float("nan")) == "NaN" and f(2, float("inf")) == "inf"
+
+
+def test_output_spec_parsing_and_file_names(host):
+    def spec(entry, species="electron", index=3):
+        info, file = C.create_string_buffer(256), C.create_string_buffer(512)
+        ok = host.opal_drv_output_spec(entry.encode(), b"out", index, species.encode(), info, 256, file, 512)
+        return ok, info.value.decode().split(), file.value.decode()
+    ok, info, file = spec("x:px")
+    assert ok and info[:4] == ["2", "0", "3", "0"] and info[6] == "0" and file == "!out/3_electron_x-px.fits"
+    ok, info, file = spec("energy:(log;energy)", "photon")
+    assert ok and info[:4] == ["1", "2", "-1", "1"] and info[6] == "1" and file == "!out/3_photon_energy_energy_log.fits"
+    ok, info, file = spec("longitude:latitude:(energy)", "photon")
+    assert ok and info[:4] == ["2", "9", "10", "0"] and info[6] == "1" and file == "!out/3_photon_longitude-latitude_energy.fits"
+    ok, info, file = spec("x:(50;auto)")
+    assert ok and info[3] == "2" and info[4] == "50" and file == "!out/3_electron_x_auto.fits"          # FixedNumber; weight name != "weight" is appended
+    ok, info, file = spec("px:(0.5;weight)")
+    assert ok and info[3] == "3" and float(info[5]) == 0.5 and file == "!out/3_electron_px.fits"
+    assert spec("chi")[0] == 1 and spec("foo")[0] == 0 and spec("x:px:py")[0] == 0 and spec("x:(energy2)")[0] == 0
+
+
+def parse_fits(path):
+    b = pathlib.Path(path).read_bytes()
+    assert len(b) % 2880 == 0
+    cards, n = {}, 0
+    while True:
+        block = b[n:n + 2880].decode("ascii")
+        n += 2880
+        done = False
+        for i in range(0, 2880, 80):
+            c = block[i:i + 80]
+            if c.startswith("END"):
+                done = True
+                break
+            if c[8:10] == "= ":
+                v = c[10:].strip()
+                cards[c[:8].strip()] = v[1:v.index("'", 1)].rstrip() if v.startswith("'") else v.split("/")[0].strip()
+        if done:
+            break
+    shape = [int(cards[f"NAXIS{k + 1}"]) for k in range(int(cards["NAXIS"]))]
+    data = np.frombuffer(b[n:n + 8 * int(np.prod(shape))], dtype=">f8").reshape(shape[::-1])
+    return cards, data
+
+
+def test_fits_writer_roundtrip(host, tmp_path):
+    bins = np.array([4, 3], dtype=np.int64)
+    cts = np.arange(12, dtype=np.float64) * 1.5 - 2.0
+    mn, sz = np.array([-1.0, 10.0]), np.array([0.5, 2.0])
+    p = tmp_path / "h.fits"
+    p.write_bytes(b"stale")
+    assert host.opal_drv_write_fits(("!" + str(p)).encode(), 2, bins.ctypes.data, mn.ctypes.data, sz.ctypes.data, cts.ctypes.data, 42.5) == 0
+    cards, data = parse_fits(p)
+    assert cards["SIMPLE"] == "T" and cards["BITPIX"] == "-64" and cards["NAXIS"] == "2"
+    assert (cards["NAXIS1"], cards["NAXIS2"]) == ("3", "4")          # fitsio reverses the row-major dimensions (hgram.rs:396-399)
+    assert float(cards["CRPIX1"]) == 1.0 and float(cards["CRVAL1"]) == -0.75 and float(cards["CDELT1"]) == 0.5
+    assert float(cards["CRVAL2"]) == 11.0 and float(cards["CDELT2"]) == 2.0
+    assert cards["CNAME1"] == "x" and cards["CUNIT2"] == "MeV/c" and cards["BUNIT"] == "1/(m.MeV/c)" and cards["OBJECT"] == "hgram/density/x_px"
+    assert float(cards["TOTAL"]) == 42.5 and float(cards["DATAMIN"]) == -2.0 and float(cards["DATAMAX"]) == 14.5
+    assert np.array_equal(data.ravel(), cts)
+
+
+SMALL = """---
+control:
+ dx: 500
+ nx: 64
+ xmin: 0.0
+ start: 0.0
+ end: {end}
+ current_deposition: true
+ n_outputs: 2
+
+qed:
+ photon_emission: false
+ photon_absorption: false
+
+electrons:
+ npc: 20
+ ne: 20.0 * step(x, 0, 16000)
+ ux: drift_u * (1.0 + 0.001 * nrand) * (2.0 * floor(urand - 0.5) + 1.0)
+ uy: 0.0
+ uz: 0.01 * nrand
+ output: [x:px, energy, "px:(8;energy)", bogus]
+
+ions:
+ npc: 0
+
+constants:
+ drift_u: 2.5e-24 / (me * c)
+"""
+
+
+def test_oracle_driver_end_to_end(tmp_path):
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    dt = 0.95 * 500 / 2.997925e8
+    (tmp_path / "in.yaml").write_text(SMALL.format(end=repr(20.5 * dt)))
+    out = subprocess.run([str(ROOT / "oracle" / "opal_ref_driver"), str(tmp_path / "in.yaml")], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # 20 steps, 2 outputs -> 10 steps between outputs; files 0, 1, 2 (main.rs:186-187, 216-276)
+    for idx in (0, 1, 2):
+        for name in ("grid.dat", "energy.dat", "electron_x-px.fits", "electron_energy.fits", "electron_px_energy.fits"):
+            assert (tmp_path / f"{idx}_{name}").exists(), (idx, name)
+    assert not list(tmp_path.glob("*bogus*")) and not (tmp_path / "3_energy.dat").exists()
+    rows = np.loadtxt(tmp_path / "2_grid.dat")
+    assert rows.shape == (64, 11) and np.array_equal(rows[:, 0], 500.0 * np.arange(64))
+    en = dict(line.split() for line in (tmp_path / "2_energy.dat").read_text().splitlines())
+    assert set(en) == {"em_field", "electrons", "ions", "photons"} and float(en["electrons"]) > 0 and en["ions"] == "0.000000e0"
+    cards, data = parse_fits(tmp_path / "0_electron_x-px.fits")
+    n = 32 * 20                                                         # plasma in the cells with 0 <= x < 16000
+    nb = math.ceil(2 * n ** (1 / 3))
+    assert data.shape == (nb, nb) and float(cards["TOTAL"]) == pytest.approx(20.0 * 500 * 32, rel=1e-12)
+    # density x bin volume sums to the total weight minus the particles holding a maximum (dropped, hgram.rs:253)
+    vol = float(cards["CDELT1"]) * float(cards["CDELT2"])
+    assert data.sum() * vol == pytest.approx(float(cards["TOTAL"]), rel=2 * 2 / n + 1e-9)
+    cards, data = parse_fits(tmp_path / "1_electron_px_energy.fits")
+    assert data.shape == (8,) and cards["OBJECT"] == "hgram/density/px"
+    # a missing input file is the reference's MissingFile error
+    bad = subprocess.run([str(ROOT / "oracle" / "opal_ref_driver"), str(tmp_path / "none.yaml")], capture_output=True, text=True)
+    assert bad.returncode == 1 and "Unable to open configuration file." in bad.stderr
+
+
+def test_rng_stream_matches_the_oracles_restatement(host, oracle):
+    """two independent statements of xoshiro256** / SplitMix64 seeding (driver loader and oracle) agree"""
+    a, b = np.zeros(64), np.zeros(64)
+    host.opal_drv_rng_stream(7, 64, a.ctypes.data)
+    oracle.cdll.opal_ref_rng_stream.argtypes = [C.c_uint64, C.c_int64, C.c_void_p]
+    oracle.cdll.opal_ref_rng_stream(7, 64, b.ctypes.data)
+    assert np.array_equal(a, b) and 0.0 <= a.min() and a.max() < 1.0
