@@ -101,6 +101,7 @@ struct opal_ctx {
     // exchange / mover buffers
     opal_migrant* d_movers = nullptr; int mover_seg_cap = 0;
     opal_migrant* d_overflow = nullptr;
+    int overflow_cap = 0;
     StripRec* d_cmovers = nullptr; int* d_cmcount = nullptr; int cell_mover_cap = 0;   // per-cell left/right mover strips (lean electrons)
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
     opal_migrant* d_in[2] = {nullptr, nullptr};
@@ -127,6 +128,10 @@ struct opal_ctx {
     int status = OPAL_OK;
     std::string err;
     double slack = 1.25; int pad = 64;
+    // adaptive re-layout (regrid): per charged species, steps since the last one, neighbourhood radius and slack boost
+    long long adv_calls[2] = {0, 0}, last_regrid[2] = {-1000000, -1000000};
+    int regrid_radius[2] = {0, 0};
+    double regrid_boost[2] = {1.0, 1.0};
 
     bool has_left() const { return g.left_bdy == OPAL_BDY_INTERNAL; }
     bool has_right() const { return g.right_bdy == OPAL_BDY_INTERNAL; }
@@ -168,7 +173,7 @@ StepParams sparams(opal_ctx* c, int species) {
     sp.flags = c->flags | (c->bx_zero ? OPAL_STEP_BX_ZERO : 0u); sp.species = species;
     sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
-    sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap;
+    sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap; sp.overflow_cap = c->overflow_cap;
     sp.cell_mover_cap = (species == OPAL_ELECTRON) ? c->cell_mover_cap : 0;
     return sp;
 }
@@ -204,16 +209,24 @@ bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand
 }
 
 bool ensure_movers(opal_ctx* c, long long n_particles) {
-    const double frac = env_double("OPAL_MOVER_FRACTION", n_particles <= 4000000 ? 1.0 : 0.05);
+    // small slabs: room for every particle crossing a cell each step (relativistic plasma at 0.95 CFL does), twice over,
+    // because the hashed segments fill unevenly; large slabs: the thermal crossing fraction
+    const double frac = env_double("OPAL_MOVER_FRACTION", n_particles <= 4000000 ? 2.0 : 0.05);
     long long seg_cap = (long long)std::ceil(2.0 * frac * (double)n_particles / OPAL_MOVER_SEGMENTS);
     if (seg_cap < 1024) seg_cap = 1024;
-    if (seg_cap <= c->mover_seg_cap) return true;
+    // parked movers (destination bucket full, e.g. a compression front): never more than the species holds; bounded at
+    // 2M records (256 MB) for the large slabs, whose per-step pile-up is a small fraction
+    long long ov_cap = std::max<long long>(seg_cap, std::min<long long>(n_particles, 1ll << 21));
+    if (seg_cap <= c->mover_seg_cap && ov_cap <= c->overflow_cap) return true;
+    seg_cap = std::max<long long>(seg_cap, c->mover_seg_cap);
+    ov_cap = std::max<long long>(ov_cap, c->overflow_cap);
     if (c->d_movers) cudaFree(c->d_movers);
     if (c->d_overflow) cudaFree(c->d_overflow);
     c->d_movers = nullptr; c->d_overflow = nullptr;
     CUB(cudaMalloc(&c->d_movers, (size_t)seg_cap * OPAL_MOVER_SEGMENTS * sizeof(opal_migrant)));
-    CUB(cudaMalloc(&c->d_overflow, (size_t)seg_cap * sizeof(opal_migrant)));
+    CUB(cudaMalloc(&c->d_overflow, (size_t)ov_cap * sizeof(opal_migrant)));
     c->mover_seg_cap = (int)seg_cap;
+    c->overflow_cap = (int)ov_cap;
     return true;
 }
 
@@ -291,7 +304,15 @@ bool fetch_status(opal_ctx* c) {
     if (e & ERR_CFL) return fail(c, OPAL_EASSERT_CFL, "push: assert!(dxi < 1.0) failed (electron.rs:313 / ion.rs:199 / photon.rs:164)");
     if (e & ERR_INDEX) return fail(c, OPAL_EASSERT_INDEX, "cell index out of range (yee.rs:501-502)");
     if (e & ERR_CHI) return fail(c, OPAL_ECHI_RANGE, "sample: chi beyond the tabulated range (photon_emission.rs:144)");
-    if (e & ERR_CAPACITY) return fail(c, OPAL_ECAPACITY, "mover/exchange/photon buffer overflow (raise OPAL_MOVER_FRACTION / OPAL_EXCHANGE_CAP)");
+    if (e & ERR_CAPACITY) {
+        std::string which;
+        if (e & ERR_CAP_MOVERS) which += " mover segments (raise OPAL_MOVER_FRACTION)";
+        if (e & ERR_CAP_PARKED) which += " parked-mover list";
+        if (e & ERR_CAP_OUTBOX) which += " neighbour outbox (raise OPAL_EXCHANGE_CAP)";
+        if (e & ERR_CAP_PHOTONS) which += " photon store";
+        if (which.empty()) which = " mover strip / photon append (raise OPAL_MOVER_FRACTION / OPAL_EXCHANGE_CAP)";
+        return fail(c, OPAL_ECAPACITY, "fixed-capacity buffer overflow:" + which);
+    }
     return true;
 }
 
@@ -306,6 +327,27 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
     std::vector<long long> demand(ncell);
     long long total = 0;
     for (int i = 0; i < ncell; i++) { demand[i] = cnt[i]; total += cnt[i]; }
+    // A density pile that MOVES (a compression front, an expanding edge) overflows a fresh set of cells every few steps.
+    // When re-layouts come in quick succession, size every bucket for the densest cell within a growing radius and add
+    // slack, so the next re-layout is only due after the pile has travelled that far.
+    if (c->adv_calls[sp] - c->last_regrid[sp] < 64) {
+        c->regrid_radius[sp] = std::min(std::max(2 * c->regrid_radius[sp], 2), 32);
+        c->regrid_boost[sp] = std::min(c->regrid_boost[sp] * 1.25, 3.0);
+    } else {
+        c->regrid_radius[sp] /= 2;
+        c->regrid_boost[sp] = std::max(1.0, c->regrid_boost[sp] / 1.25);
+    }
+    c->last_regrid[sp] = c->adv_calls[sp];
+    if (c->regrid_radius[sp] > 0 || c->regrid_boost[sp] > 1.0) {
+        const int R = c->regrid_radius[sp];
+        std::vector<long long> wide(ncell);
+        for (int i = 0; i < ncell; i++) {
+            long long m = 0;
+            for (int j = std::max(0, i - R); j <= std::min(ncell - 1, i + R); j++) m = std::max<long long>(m, cnt[j]);
+            wide[i] = (long long)std::ceil((double)m * c->regrid_boost[sp]);
+        }
+        demand.swap(wide);
+    }
     Buckets old = B;
     B = Buckets();
     if (!alloc_buckets(c, B, demand, old.full)) return false;
@@ -320,7 +362,7 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
     CUB(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
     StepParams sp_ = sparams(c, sp);
     sp_.route_left = sp_.route_right = 0;
-    c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, old.full, deposit_parked, c->d_overflow, c->d_tmp_int, c->mover_seg_cap, 0, nullptr,
+    c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, old.full, deposit_parked, c->d_overflow, c->d_tmp_int, c->overflow_cap, 0, nullptr,
                  nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
     (void)n_parked;
     CUB(cudaStreamSynchronize(c->stream));
@@ -331,7 +373,7 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
 bool handle_overflow(opal_ctx* c, int sp, bool deposit_parked) {
     int guard = 0;
     while (c->h_status->n_overflow > 0) {
-        if (c->h_status->n_overflow > c->mover_seg_cap) return fail(c, OPAL_ECAPACITY, "too many parked movers");
+        if (c->h_status->n_overflow > c->overflow_cap) return fail(c, OPAL_ECAPACITY, "too many parked movers");
         if (!regrid(c, sp, deposit_parked)) return false;
         if (++guard > 4) return fail(c, OPAL_ECAPACITY, "re-layout did not converge");
     }
@@ -400,6 +442,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     Buckets& B = c->bk[sp];
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
     if (!reset_status(c, true)) return false;
+    c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
     bool strips = false;
     double* ke_out = nullptr;

@@ -146,8 +146,9 @@ __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepPara
             const unsigned m_move = __ballot_sync(FULLMASK, move);
             // reserve mover slots early (one atomic per chunk that has movers, on one of
             // OPAL_MOVER_SEGMENTS counters) so its latency overlaps the stayers' deposit below
+            // (segment = hash(cell, chunk): a few cells holding most of the slab -- a compression front -- still spread over all segments)
             int mbase = 0;
-            const int seg = c & (OPAL_MOVER_SEGMENTS - 1);
+            const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)(k0 >> 5) * 0x85EBCA77u) >> 22);   // top 10 bits: OPAL_MOVER_SEGMENTS == 1024
             if (m_move) {
                 const int leader = __ffs(m_move) - 1;
                 if (lane == leader) mbase = atomicAdd(seg_count + seg, __popc(m_move));
@@ -208,7 +209,7 @@ __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepPara
         }
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
-    if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
+    if (cap_err) atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_MOVERS);
 }
 
 #ifdef OPAL_FAST
@@ -562,7 +563,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         if (dst && mine != 0.0) atomicAdd(dst, mine);
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
-    if (cap_err) atomicOr(&st->err, ERR_CAPACITY);
+    if (cap_err) atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_MOVERS);
     if (KE) {
         ske = warp_sum(ske) * (1.0e6 * OPAL_ME_MEV * OPAL_E);
         if (lane == 0 && ske != 0.0) atomicAdd(ke_out, ske);
@@ -609,7 +610,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                         m.cell = -1; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         out_l[o + i] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY);
+                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
                 }
             }
         }
@@ -627,7 +628,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                         m.cell = 0; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         out_r[o + i] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY);
+                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
                 }
             }
         }
@@ -652,12 +653,12 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                 } else {
                     // bucket full: park; the host re-lays the buckets out (count[c] keeps the demand)
                     int o = atomicAdd(&st->n_overflow, 1);
-                    if (o < sp.mover_cap) {
+                    if (o < sp.overflow_cap) {
                         opal_migrant m;
                         m.cell = c; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         overflow[o] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY);
+                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PARKED);
                 }
                 if (slot < cap) {
                     // R-face form of the mover's deposit in the frame of its new cell c (faces -3/2..+5/2):
@@ -722,7 +723,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
                 if (sp.route_left == 1) cell += b.ncell;                       // mod.rs:313-315 + 366-368
                 else if (sp.route_left == 2) {
                     int r = atomicAdd(&st->n_out[0], 1);
-                    if (r < sp.out_cap) { m.cell = cell; out_l[r] = m; } else atomicOr(&st->err, ERR_CAPACITY);
+                    if (r < sp.out_cap) { m.cell = cell; out_l[r] = m; } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
                     continue;
                 } else continue;                                               // open boundary: deleted by the splice
             } else if (cell >= b.ncell) {
@@ -730,7 +731,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
                 if (sp.route_right == 1) cell -= b.ncell;                      // mod.rs:291-293
                 else if (sp.route_right == 2) {
                     int r = atomicAdd(&st->n_out[1], 1);
-                    if (r < sp.out_cap) { m.cell = cell - b.ncell; out_r[r] = m; } else atomicOr(&st->err, ERR_CAPACITY);
+                    if (r < sp.out_cap) { m.cell = cell - b.ncell; out_r[r] = m; } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
                     continue;
                 } else continue;
             }
@@ -741,7 +742,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
                 // destination bucket full: park the record; the host re-lays the buckets out and
                 // re-runs this kernel on the parked records (count[c] keeps the demand)
                 int r = atomicAdd(&st->n_overflow, 1);
-                if (r < sp.mover_cap) { m.cell = cell; overflow[r] = m; } else atomicOr(&st->err, ERR_CAPACITY);
+                if (r < sp.overflow_cap) { m.cell = cell; overflow[r] = m; } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PARKED);
                 continue;
             }
             const long long s = b.start[c] + slot;
@@ -878,7 +879,7 @@ __global__ void k_photon_insert(PhotonDev dst, const opal_migrant* __restrict__ 
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const opal_migrant m = recs[i];
         const int o = atomicAdd(dst.n, 1);
-        if (o >= dst.cap) { atomicOr(&st->err, ERR_CAPACITY); continue; }
+        if (o >= dst.cap) { atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PHOTONS); continue; }
         dst.cell[o] = (int)(m.cell + cell_shift);
         dst.f[P_X][o] = m.x; dst.f[P_PREVX][o] = m.prev_x; dst.f[P_KX][o] = m.u[0]; dst.f[P_KY][o] = m.u[1]; dst.f[P_KZ][o] = m.u[2];
         dst.f[P_W][o] = m.weight; dst.f[P_CHI][o] = m.chi; dst.f[P_TAU][o] = m.tau; dst.f[P_Y][o] = m.y; dst.f[P_Z][o] = m.z;

@@ -54,7 +54,9 @@ struct StatusDev {
     int n_new_photons;
     int pad;
 };
-enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u };
+enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
+       // which fixed-capacity buffer overflowed (set together with ERR_CAPACITY)
+       ERR_CAP_MOVERS = 16u, ERR_CAP_PARKED = 32u, ERR_CAP_OUTBOX = 64u, ERR_CAP_PHOTONS = 128u };
 
 // compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout);
 // the destination (c-1 / c+1) is implied by the strip it sits in
@@ -68,6 +70,7 @@ struct StepParams {
     int species;             // opal_species
     int route_left, route_right;   // what happens to a leaver: 0 = delete (open boundary), 1 = wrap (self), 2 = outbox
     int mover_cap, out_cap;
+    int overflow_cap;        // records in the parked-mover list (destination bucket full)
     int cell_mover_cap;      // records per cell and direction in the mover strips (0: strips not in use)
 };
 

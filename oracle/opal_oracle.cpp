@@ -26,6 +26,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstdint>
 #include <cstring>
 #include <limits>
@@ -951,6 +952,7 @@ opal_status opal_ref_create(opal_ctx** out, int device, int64_t nx, double xmin,
                             int rank, int nranks, uint64_t seed, uint32_t flags) {
     (void)device;
     if (!out || nx < 1 || nranks < 1 || rank < 0 || rank >= nranks) return OPAL_EINVAL;
+    if (const char* e = std::getenv("OPAL_REF_THREADS")) { const int n = std::atoi(e); g_threads = n < 1 ? 1 : n; }   // callers without set_threads (the driver build)
     opal_ctx* g = new opal_ctx();
     g->rank = rank; g->nranks = nranks; g->dx = dx; g->dt = dt; g->flags = flags; g->size = nx;
     // yee.rs:278-292
