@@ -151,3 +151,25 @@ def test_hole_boring_deck_gpu_vs_oracle(tmp_path):
     ea, eb = _energies(a / "2_energy.dat"), _energies(b / "2_energy.dat")
     for k in ("em_field", "electrons", "ions"):
         assert abs(ea[k] - eb[k]) <= 1e-3 * abs(eb[k]), (k, ea[k], eb[k])
+
+
+def test_two_ranks_two_gpus(tmp_path):
+    """`--ranks 2`: one process per GPU (the reference: mpirun -n 2), x-slabs from GridDesign, NCCL ring in the library, host
+    collectives for the outputs.  Each rank seeds its loader with its rank id (main.rs:53), so the plasma differs from the
+    one-rank run in its random draws only: totals are exact, energies agree statistically."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    deck = TWO_STREAM.format(end=repr(200.5 * DT500))
+    one = _run(GPU_DRIVER, deck, tmp_path, "one")
+    two = _run(GPU_DRIVER, deck, tmp_path, "two", extra=("--ranks", "2"))
+    for idx in (0, 1, 2):
+        g1, g2 = np.loadtxt(one / f"{idx}_grid.dat"), np.loadtxt(two / f"{idx}_grid.dat")
+        assert g1.shape == g2.shape == (200, 11) and np.array_equal(g1[:, 0], g2[:, 0])      # rank 0 gathered both slabs, in order
+        c1, d1 = parse_fits(one / f"{idx}_electron_x-px.fits")
+        c2, d2 = parse_fits(two / f"{idx}_electron_x-px.fits")
+        assert d1.shape == d2.shape and float(c2["TOTAL"]) == pytest.approx(float(c1["TOTAL"]), rel=1e-12)   # no particle lost in migration
+        e1, e2 = _energies(one / f"{idx}_energy.dat"), _energies(two / f"{idx}_energy.dat")
+        assert abs(e2["electrons"] - e1["electrons"]) <= 1e-3 * e1["electrons"]
+    # the field energy grows from noise: same order of magnitude
+    assert 0.2 < _energies(two / "2_energy.dat")["em_field"] / _energies(one / "2_energy.dat")["em_field"] < 5.0
