@@ -113,7 +113,8 @@ struct opal_ctx {
     StatusDev* d_status = nullptr;   // followed by OPAL_MOVER_SEGMENTS ints
     StatusDev* h_status = nullptr;   // pinned
     double* d_energy = nullptr;      // 4 doubles + [4]: electron kinetic energy accumulated by the last fused push
-    bool ke_fused = false;           // d_energy[4] is the electrons' current total_kinetic_energy
+    bool ke_fused = false;
+    bool holes_open = false;         // lean electrons: the last fused step left holes in the buckets (count[] counts slots in use)           // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
     double* d_qed_tables = nullptr;
@@ -243,8 +244,9 @@ bool ensure_cell_movers(opal_ctx* c, long long n_particles) {
     if (c->d_cmcount) cudaFree(c->d_cmcount);
     c->d_cmovers = nullptr; c->d_cmcount = nullptr;
     CUB(cudaMalloc(&c->d_cmovers, (size_t)mc * 2 * c->g.nx * sizeof(StripRec)));
-    CUB(cudaMalloc(&c->d_cmcount, (size_t)2 * c->g.nx * sizeof(int)));
-    CUB(cudaMemset(c->d_cmcount, 0, (size_t)2 * c->g.nx * sizeof(int)));
+    // [2 nx strip counts][nx hole counts][nx x 2 mc hole slots]
+    CUB(cudaMalloc(&c->d_cmcount, (size_t)(3 + 2 * mc) * c->g.nx * sizeof(int)));
+    CUB(cudaMemset(c->d_cmcount, 0, (size_t)3 * c->g.nx * sizeof(int)));
     c->cell_mover_cap = (int)mc;
     return true;
 }
@@ -313,6 +315,17 @@ bool fetch_status(opal_ctx* c) {
         if (which.empty()) which = " mover strip / photon append (raise OPAL_MOVER_FRACTION / OPAL_EXCHANGE_CAP)";
         return fail(c, OPAL_ECAPACITY, "fixed-capacity buffer overflow:" + which);
     }
+    return true;
+}
+
+// The lean fused step kernels leave holes in the electron buckets (see OPAL_PUSH_HOLES); everything else reads
+// buckets whose first count[c] slots are live.
+bool ensure_compact(opal_ctx* c) {
+    if (!c->holes_open) return true;
+    c->holes_open = false;
+    if (!c->bk[OPAL_ELECTRON].allocated || !c->d_cmcount) return true;
+    c->k.compact_cells(c->stream, bdev(c, OPAL_ELECTRON), c->d_cmcount); c->launches++;
+    CUB(cudaMemsetAsync(c->d_cmcount + 2ll * c->g.nx, 0, (size_t)c->g.nx * sizeof(int), c->stream));
     return true;
 }
 
@@ -452,6 +465,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     }
     { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status, ke_out); c->launches++; }
     if (ke_out && strips) c->ke_fused = true;
+    if (strips && c->k.push_leaves_holes) c->holes_open = true;
     if (strips) { Timed tm(c, 1); c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1,
                  c->d_overflow, c->d_status); c->launches++; }
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
@@ -641,6 +655,7 @@ opal_status opal_set_ion(opal_ctx* c, double z_star, double a) {
 opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int64_t* cell, const double* x, const double* ux,
                                   const double* uy, const double* uz, const double* w, const double* tau) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON) c->holes_open = false;
     c->ke_fused = false;
     if (n < 0 || n > (1ll << 31) - 64 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
     const double dx = c->g.dx, dt = c->g.dt;
@@ -718,6 +733,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
 opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, double weight, const double u_th[3], const double drift[3],
                                     int two_stream, int64_t global_cell_offset, uint64_t seed) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON) c->holes_open = false;
     c->ke_fused = false;
     if ((species != OPAL_ELECTRON && species != OPAL_ION) || npc < 1 || !u_th || !drift) return OPAL_EINVAL;
     Buckets& B = c->bk[species];
@@ -737,6 +753,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
 
 opal_status opal_particles_count(opal_ctx* c, int species, int64_t* n) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
     if (!n) return OPAL_EINVAL;
     *n = 0;
     if (species == OPAL_PHOTON) {
@@ -761,6 +778,7 @@ opal_status opal_particles_download(opal_ctx* c, int species, int64_t cap, int64
                                     double* uy, double* uz, double* w, double* gamma, double* chi, double* tau, double* work,
                                     double* y, double* z, double* birth) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
     const double inf = std::numeric_limits<double>::infinity();
     if (species == OPAL_PHOTON) {
         int n = 0;
@@ -913,6 +931,7 @@ opal_status opal_migrants_take(opal_ctx* c, int species, int side, int64_t cap, 
 
 opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, const opal_migrant* in) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
     c->ke_fused = false;
     if (side != OPAL_LEFT && side != OPAL_RIGHT || n < 0 || species < 0 || species > 2) return OPAL_EINVAL;
     if (n == 0) return OPAL_OK;
@@ -1038,6 +1057,7 @@ static bool hgram_args_ok(int species, int ndim, const int* q) {
 
 opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, const int* lg, double* mn, double* mx, int64_t* n) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
     if (!hgram_args_ok(species, ndim, q) || !mn || !mx || !n) return OPAL_EINVAL;
     for (int d = 0; d < ndim; d++) { mn[d] = std::numeric_limits<double>::max(); mx[d] = -std::numeric_limits<double>::max(); }   // hgram.rs:189
     opal_status st = opal_particles_count(c, species, n);
@@ -1059,6 +1079,7 @@ opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, 
 opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
                            const int64_t* nbins, int weight_kind, int log_density_adjust, double* counts, double* total) {
     CHECK_CTX(c);
+    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
     if (!hgram_args_ok(species, ndim, q) || !gmin || !bin_sz || !nbins || !counts || !total) return OPAL_EINVAL;
     if (weight_kind != OPAL_W_WEIGHT && weight_kind != OPAL_W_ENERGY) return OPAL_EINVAL;
     long long nb[2] = {1, 1};
@@ -1093,6 +1114,7 @@ opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, dou
     BucketDev be, bi;
     PhotonDev pp;
     const bool fused_ke = c->ke_fused && c->bk[0].allocated;
+    if (!fused_ke && !ensure_compact(c)) return (opal_status)c->status;
     const bool he = c->bk[0].allocated && !fused_ke, hi = c->bk[1].allocated, hp = c->ph[0].cap > 0;
     if (he) be = bdev(c, 0);
     if (hi) bi = bdev(c, 1);

@@ -305,13 +305,70 @@ __constant__ signed char c_pre_k[18] = {0, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 2, 2, 3
 #ifndef OPAL_PUSH_MINBLK
 #define OPAL_PUSH_MINBLK 4
 #endif
+// OPAL_PUSH_HOLES (experimental, default off): a particle that stays in its cell is written back to the slot it was
+// read from; a particle that leaves marks its slot (x := OPAL_HOLE_MARK).  The push records the slot indices of all
+// holes of a cell (new and left over) in the cell's hole list; k_pull, which owns the destination bucket, drops the
+// arriving movers into the listed holes and appends the rest.  Holes that find no arrival simply stay (the push skips
+// marked slots), so count[c] counts SLOTS IN USE, live or hole, between steps; any consumer other than the step kernels
+// sees the buckets only after k_compact_cells has closed the holes (host: ensure_compact).
+// Measured at the bench size (1e9 electrons, 1e6 cells, B200): the push no longer rewrites w behind the first mover of a
+// cell (write traffic 39.8 -> 32 B/particle) and drops from 15.4 to 14.5 ms, but the arrivals now land in scattered
+// 8-byte slots whose 32-byte sectors have long left the L2: ~48 x 5 partial-sector read-modify-writes per cell make
+// k_pull 1.5 -> 4.0-4.5 ms.  Net loss (19.1-20.0 vs 17.0 ms per step), so the default stays the in-push shift; the way
+// to keep the push's gain is to consume the strips inside the NEXT push, while the cell's sectors stream through L2.
+#ifndef OPAL_PUSH_HOLES
+#define OPAL_PUSH_HOLES 0
+#endif
+#define OPAL_HOLE_MARK (__longlong_as_double(0x7ff8dead0000beefll))   // a quiet NaN: never a valid offset
+__device__ __forceinline__ bool is_hole(double x) { return x != x; }
 // BX0: B_x == 0 on the whole grid (the solver never updates it, yee.rs:839-848) => tau_x terms drop out.
 // KE:  also accumulate total_kinetic_energy (electron.rs:122-126: w u^2 mc^2 / (gamma + 1), mod.rs:227-240) of the
 //      pushed particles into *ke_out, so the energy diagnostic that follows a step costs no second pass over HBM.
+// shift the live particles of one lean bucket down over its holes (one warp); returns the live count
+__device__ __forceinline__ int compact_cell(const BucketDev& b, long long base, int n, int lane, unsigned lt_mask) {
+    __syncwarp();
+    int wr = 0;
+    for (int k0 = 0; k0 < n; k0 += 32) {
+        const int i = k0 + lane;
+        double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0, v4 = 0.0;
+        bool live = false;
+        if (i < n) {
+            const long long s = base + i;
+            v0 = b.f[F_X][s]; live = !is_hole(v0);
+            v1 = b.f[F_UX][s]; v2 = b.f[F_UY][s]; v3 = b.f[F_UZ][s]; v4 = b.f[F_W][s];
+        }
+        const unsigned m_live = __ballot_sync(FULLMASK, live);
+        __syncwarp();        // every lane has read its slot before any lane overwrites a lower one
+        const int pos = wr + __popc(m_live & lt_mask);
+        if (live && pos != i) {
+            const long long s = base + pos;
+            b.f[F_X][s] = v0; b.f[F_UX][s] = v1; b.f[F_UY][s] = v2; b.f[F_UZ][s] = v3; b.f[F_W][s] = v4;
+        }
+        wr += __popc(m_live);
+    }
+    __syncwarp();
+    return wr;
+}
+
+// closes the holes of every cell (host: ensure_compact, before anything but the step kernels reads the buckets)
+__global__ void __launch_bounds__(256) k_compact_cells(BucketDev b, const int* __restrict__ hcount) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < b.ncell; c += gridDim.x * 8) {
+        const int n = b.count[c];
+        if (n == 0) continue;
+        // cells without a recorded hole are skipped; k_pull keeps hcount current (holes left after the arrivals)
+        if (hcount[c] == 0) continue;
+        const int live = compact_cell(b, b.start[c], n, lane, lt_mask);
+        if (lane == 0) b.count[c] = live;
+    }
+}
+
 template <bool BX0, bool KE>
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StripRec* __restrict__ strips,
-                                                           int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out) {
+                                                           int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out,
+                                                           int* __restrict__ holes, int* __restrict__ hcount) {
     constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
     constexpr int CH = 32 * ILP;
     const int lane = threadIdx.x & 31;
@@ -328,10 +385,19 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     const int MC = sp.cell_mover_cap;
     for (int c = blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
         const int n = b.count[c];
-        if (n == 0) { if (lane < 2) scount[2 * c + lane] = 0; continue; }
+        if (n == 0) {
+            if (lane < 2) scount[2 * c + lane] = 0;
+#if OPAL_PUSH_HOLES
+            if (lane == 2) hcount[c] = 0;
+#endif
+            continue;
+        }
         const long long base = b.start[c];
         const int j = c + g.left;
         int mloc_l = 0, mloc_r = 0;   // left / right movers of this cell so far (warp-uniform): slots in its two strips
+#if OPAL_PUSH_HOLES
+        int n_holes = 0;              // holes of this cell so far (warp-uniform)
+#endif
         // the 18 field values every lane of this warp gathers from -> 18 per-cell gather coefficients (CellPre),
         // one copy per warp in shared memory
         __shared__ double s_raw[OPAL_PUSH_WPB][20];
@@ -394,6 +460,9 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             RFaces ro[ILP];
             int d[ILP];
             bool valid[ILP];
+#if OPAL_PUSH_HOLES
+            bool was_hole[ILP];
+#endif
 #if OPAL_PUSH_STAGES > 0
             cp_async_wait<NST - 2>();
 #pragma unroll
@@ -401,6 +470,10 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 valid[q] = k0 + q * 32 + lane < n;
                 const int e = q * 32 + lane;
                 x[q] = valid[q] ? ring[stage][0][e] : 0.0;
+#if OPAL_PUSH_HOLES
+                was_hole[q] = valid[q] && is_hole(x[q]);      // a hole no arrival has filled yet: skipped, re-listed below
+                if (was_hole[q]) { valid[q] = false; x[q] = 0.0; }
+#endif
                 u[q] = {valid[q] ? ring[stage][1][e] : 0.0, valid[q] ? ring[stage][2][e] : 0.0, valid[q] ? ring[stage][3][e] : 0.0};
                 W[q] = valid[q] ? ring[stage][4][e] : 0.0;
             }
@@ -424,6 +497,10 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             for (int q = 0; q < ILP; q++) {
                 x[q] = nx0[q]; u[q] = {nx1[q], nx2[q], nx3[q]}; W[q] = nx4[q];
                 valid[q] = k0 + q * 32 + lane < n;
+#if OPAL_PUSH_HOLES
+                was_hole[q] = valid[q] && is_hole(x[q]);
+                if (was_hole[q]) { valid[q] = false; x[q] = 0.0; u[q] = {0.0, 0.0, 0.0}; W[q] = 0.0; }
+#endif
             }
 #pragma unroll
             for (int q = 0; q < ILP; q++) {
@@ -503,10 +580,16 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             for (int q = 0; q < ILP; q++) {
                 const int i = k0 + q * 32 + lane;
                 if (valid[q] && d[q] == 0) {
+#if OPAL_PUSH_HOLES
+                    // stayers are written back to the slot they were read from: no shift, w is never rewritten
+                    const long long s = base + i;
+                    fx[s] = xn[q]; fux[s] = u[q].x; fuy[s] = u[q].y; fuz[s] = u[q].z;
+#else
                     const int pos = written + __popc(m_stay[q] & lt_mask);
                     const long long s = base + pos;
                     fx[s] = xn[q]; fux[s] = u[q].x; fuy[s] = u[q].y; fuz[s] = u[q].z;
                     if (pos != i) fw[s] = W[q];
+#endif
                     // ---- deposit of a stayer (yee.rs:584-609) ----
                     const RFaces rn = r_faces(xn[q]);
                     sjx0 += W[q] * (rn.a - ro[q].a); sjx1 += W[q] * (rn.b - ro[q].b); sjx2 += W[q] * (rn.c - ro[q].c);
@@ -519,8 +602,11 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                     const bool left = d[q] < 0;
                     const int r = left ? base_l + __popc(m_l[q] & lt_mask) : base_r + __popc(m_r[q] & lt_mask);
                     const double gam = gam2[q] * igam[q], px = x[q] - fl[q];
+#if OPAL_PUSH_HOLES
+                    fx[base + i] = OPAL_HOLE_MARK;     // the vacated slot
+#endif
                     if (r < MC) {
-                        StripRec rec = {xn[q], px, u[q].x, u[q].y, u[q].z, W[q], gam, 0.0};
+                        StripRec rec = {xn[q], px, u[q].x, u[q].y, u[q].z, W[q]};
                         strips[((long long)c * 2 + (left ? 0 : 1)) * MC + r] = rec;
                     } else {
                         const int rg = gbase + (left ? r - first_over_l : over_l + (r - first_over_r));
@@ -535,14 +621,35 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 }
                 written += __popc(m_stay[q]);
                 base_l += __popc(m_l[q]); base_r += __popc(m_r[q]);
+#if OPAL_PUSH_HOLES
+                {   // list every hole of this chunk: slots just vacated and slots still empty from earlier steps
+                    const bool hole = was_hole[q] || (valid[q] && d[q] != 0);
+                    const unsigned m_hole = __ballot_sync(FULLMASK, hole);
+                    if (hole) {
+                        const int k = n_holes + __popc(m_hole & lt_mask);
+                        if (k < 2 * MC) holes[(long long)c * (2 * MC) + k] = i;
+                    }
+                    n_holes += __popc(m_hole);
+                }
+#endif
             }
         }
+#if OPAL_PUSH_STAGES > 0
+        cp_async_wait<0>();
+#endif
+#if OPAL_PUSH_HOLES
+        if (n_holes > 2 * MC) {
+            // rare: more holes than the list holds.  Close them all now by shifting the live particles down.
+            const int live = compact_cell(b, base, n, lane, lt_mask);
+            if (lane == 0) b.count[c] = live;
+            n_holes = 0;
+        }
+        if (lane == 0) { scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC; hcount[c] = n_holes; }
+#else
         if (lane == 0) {
             b.count[c] = written;
             scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC;
         }
-#if OPAL_PUSH_STAGES > 0
-        cp_async_wait<0>();
 #endif
 
         // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
@@ -582,9 +689,8 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
                                                const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
                                                opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
-                                               StatusDev* __restrict__ st) {
+                                               StatusDev* __restrict__ st, const int* __restrict__ holes, int* __restrict__ hcount) {
     const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * 8;
     const int MC = sp.cell_mover_cap;
     const int nc = b.ncell;
@@ -607,7 +713,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                     const StripRec r = strips[(long long)0 * MC + i];
                     if (o + i < sp.out_cap) {
                         opal_migrant m;
-                        m.cell = -1; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.cell = -1; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         out_l[o + i] = m;
                     } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
@@ -625,7 +731,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                     const StripRec r = strips[((long long)c * 2 + 1) * MC + i];
                     if (o + i < sp.out_cap) {
                         opal_migrant m;
-                        m.cell = 0; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.cell = 0; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         out_r[o + i] = m;
                     } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
@@ -633,7 +739,14 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             }
         }
         const int n_in = n_from_l + n_from_r;
+#if OPAL_PUSH_HOLES
+        const int n_holes = hcount[c];         // listed by the push: slots of this bucket that are free
         if (n_in == 0) continue;
+#else
+        const int n_holes = 0;
+        (void)n_holes;
+        if (n_in == 0) continue;
+#endif
         const int cnt = b.count[c];
         const long long bstart = b.start[c];
         const int cap = (int)(b.start[c + 1] - bstart);
@@ -646,7 +759,12 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             if (i < n_in) {
                 const StripRec r = i < n_from_l ? strips[((long long)src_l * 2 + 1) * MC + i]
                                                 : strips[((long long)src_r * 2) * MC + (i - n_from_l)];
+#if OPAL_PUSH_HOLES
+                // the first n_holes arrivals drop into the listed holes, the rest are appended behind the slots in use
+                const int slot = i < n_holes ? holes[(long long)c * (2 * MC) + i] : cnt + (i - n_holes);
+#else
                 const int slot = cnt + i;
+#endif
                 if (slot < cap) {
                     const long long s = bstart + slot;
                     b.f[F_X][s] = r.x; b.f[F_UX][s] = r.ux; b.f[F_UY][s] = r.uy; b.f[F_UZ][s] = r.uz; b.f[F_W][s] = r.w;
@@ -655,7 +773,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                     int o = atomicAdd(&st->n_overflow, 1);
                     if (o < sp.overflow_cap) {
                         opal_migrant m;
-                        m.cell = c; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = r.gamma;
+                        m.cell = c; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
                         m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
                         overflow[o] = m;
                     } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PARKED);
@@ -674,14 +792,21 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                     const double f4 = from_l ? 0.0 : -ro.c;
                     acc[0] += r.w * f0; acc[1] += r.w * f1; acc[2] += r.w * f2; acc[3] += r.w * f3; acc[4] += r.w * f4;
                     const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
-                    const double tw = r.w / r.gamma, ty = tw * r.uy, tz = tw * r.uz;
+                    const double tw = r.w * rsqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0)))), ty = tw * r.uy, tz = tw * r.uz;
                     acc[5] += ty * w0; acc[6] += ty * w1; acc[7] += ty * w2;
                     acc[8] += tz * w0; acc[9] += tz * w1; acc[10] += tz * w2;
                     acc[11] += r.w * w3; acc[12] += r.w * w0; acc[13] += r.w * w1; acc[14] += r.w * w2;
                 }
             }
         }
+#if OPAL_PUSH_HOLES
+        if (lane == 0) {
+            if (n_in > n_holes) b.count[c] = cnt + (n_in - n_holes);
+            hcount[c] = n_in < n_holes ? n_holes - n_in : 0;       // holes still open (k_compact_cells skips cells without)
+        }
+#else
         if (lane == 0) b.count[c] = cnt + n_in;
+#endif
         const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
 #pragma unroll
         for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]) * (k < 5 ? kx : (k < 11 ? ky : kr));
@@ -696,7 +821,6 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
         }
         if (dst && mine != 0.0) atomicAdd(dst, mine);
     }
-    (void)lt_mask;
 }
 #endif  // OPAL_FAST
 
@@ -1532,7 +1656,7 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     if (sp.species == OPAL_ELECTRON && !full && dep && strips && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
         const int gr = (int)(blocks < 1 ? 1 : blocks);
-#define LAUNCHF(B0, K) k_push_lean_fast<B0, K><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out)
+#define LAUNCHF(B0, K) k_push_lean_fast<B0, K><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
         if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
         else { if (ke_out) LAUNCHF(false, true); else LAUNCHF(false, false); }
 #undef LAUNCHF
@@ -1555,7 +1679,18 @@ static void l_pull(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
                    const int* scount, opal_migrant* out_l, opal_migrant* out_r, opal_migrant* overflow, StatusDev* st) {
 #ifdef OPAL_FAST
     long long blocks = ((long long)b.ncell + 7) / 8;
-    k_pull<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(g, b, sp, strips, scount, out_l, out_r, overflow, st);
+    // the strip counters are followed by the per-cell hole counts and hole lists (host: ensure_cell_movers)
+    int* sc = const_cast<int*>(scount);
+    k_pull<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(g, b, sp, strips, scount, out_l, out_r, overflow, st, sc + 3ll * b.ncell, sc + 2ll * b.ncell);
+#endif
+}
+
+// close the holes the lean step kernels leave in the buckets (count[] := live particles)
+static void l_compact_cells(cudaStream_t s, const BucketDev& b, const int* scount) {
+#ifdef OPAL_FAST
+    long long blocks = ((long long)b.ncell + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_compact_cells<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(b, scount + 2ll * b.ncell);
 #endif
 }
 
@@ -1683,7 +1818,12 @@ KernelTable table() {
     t.push = l_push; t.pull = l_pull; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
-    t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets;
+    t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells;
+#if defined(OPAL_FAST) && OPAL_PUSH_HOLES
+    t.push_leaves_holes = true;
+#else
+    t.push_leaves_holes = false;
+#endif
     return t;
 }
 

@@ -60,7 +60,7 @@ enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
 
 // compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout);
 // the destination (c-1 / c+1) is implied by the strip it sits in
-struct StripRec { double x, prev_x, ux, uy, uz, w, gamma, pad; };   // 64 bytes
+struct StripRec { double x, prev_x, ux, uy, uz, w; };   // 48 bytes (gamma is recomputed from u where a consumer needs it)
 
 // internal StepParams.flags bit (above the public OPAL_FLAG_* bits): B_x is zero on the whole grid
 #define OPAL_STEP_BX_ZERO (1u << 31)
@@ -111,6 +111,9 @@ struct KernelTable {
                        const double* r2, const double* r3, int classical, double* out3, StatusDev* st);
     void (*fields_at)(cudaStream_t, const GridDev&, int n, const long long* cell, const double* xi, double* out6, StatusDev* st);
     void (*copy_buckets)(cudaStream_t, const BucketDev& src, const BucketDev& dst, bool full);
+    // lean electrons: close the holes the fused step kernels leave (strip_count: the push's counter block)
+    void (*compact_cells)(cudaStream_t, const BucketDev&, const int* strip_count);
+    bool push_leaves_holes;     // the lean strip kernel was built with OPAL_PUSH_HOLES
 };
 
 namespace fast { KernelTable table(); }
