@@ -567,7 +567,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             // latency); only the excess beyond MC is appended to the shared segmented buffer.
             int base_l = mloc_l, base_r = mloc_r;
             int gbase = 0;
-            const int seg = c & (OPAL_MOVER_SEGMENTS - 1);
+            const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)(k0 / CH) * 0x85EBCA77u) >> 22);   // hashed like k_push: a dense cell spreads over all segments
             const int first_over_l = mloc_l > MC ? mloc_l : MC, first_over_r = mloc_r > MC ? mloc_r : MC;
             const int over_l = mloc_l + n_l > first_over_l ? mloc_l + n_l - first_over_l : 0;
             const int over_r = mloc_r + n_r > first_over_r ? mloc_r + n_r - first_over_r : 0;

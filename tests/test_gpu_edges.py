@@ -1,0 +1,136 @@
+"""Edge cases and error behaviour of the CUDA path against the oracle (the reference's assert!/panic sites surface as
+sticky opal_status codes on both sides), and size-independent invariants at the full BASELINE bench size."""
+import numpy as np
+import pytest
+
+from opal_b200.abi import (BDY_ABSORBING, BDY_LASER, ELECTRON, FLAG_LEAN_STATE, ION, PHOTON, OpalError, Slab)
+from opal_b200.constants import ELECTRON_CHARGE, SPEED_OF_LIGHT
+import pic_cases as pc
+
+pytestmark = pytest.mark.gpu
+EASSERT_CFL, EASSERT_INDEX, ECHI_RANGE = 5, 6, 7
+
+
+def _one(nx, cell, x, ux, w=1.0):
+    n = len(cell)
+    return dict(cell=np.asarray(cell, dtype=np.int64), x=np.asarray(x, float), ux=np.asarray(ux, float), uy=np.zeros(n), uz=np.zeros(n),
+                weight=np.full(n, w))
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_LEAN_STATE])
+def test_cfl_assert_is_a_sticky_status_on_both_sides(gpu, oracle, flags):
+    """assert!(dxi < 1.0) (electron.rs:313): dt = 1.5 dx/c and a relativistic electron"""
+    nx, dx = 32, 500.0
+    dt = 1.5 * dx / SPEED_OF_LIGHT
+    for lib, fl in ((gpu, flags), (oracle, 0)):
+        s = Slab(lib, nx, 0.0, dx, dt, flags=fl)
+        pc.upload(s, ELECTRON, _one(nx, [5, 9], [0.5, 0.25], [50.0, 0.001]))
+        with pytest.raises(OpalError) as e:
+            s.run_steps(1)
+        assert e.value.status == EASSERT_CFL
+        with pytest.raises(OpalError) as e2:          # sticky: the context stays failed, like the reference's abort
+            s.run_steps(1)
+        assert e2.value.status == EASSERT_CFL
+
+
+def test_index_assert_and_chi_range(gpu, oracle):
+    nx, dx = 32, 1.0e-8
+    for lib in (gpu, oracle):
+        s = Slab(lib, nx, 0.0, dx)
+        with pytest.raises(OpalError) as e:          # yee.rs:501-502
+            s.fields_at([nx], [0.5])
+        assert e.value.status == EASSERT_INDEX
+    # chi beyond the tabulated range: unimplemented!() at photon_emission.rs:143-144
+    for lib in (gpu, oracle):
+        with pytest.raises(OpalError) as e:
+            lib.sample(150.0, 1.0e5, 0.5, 0.5, 0.5)
+        assert e.value.status == ECHI_RANGE
+
+
+def test_empty_and_minimal_populations(gpu, oracle):
+    nx, dx = 8, 500.0                                 # YeeGrid::min_size (yee.rs:782-784)
+    a, b = Slab(gpu, nx, 0.0, dx), Slab(oracle, nx, 0.0, dx)
+    empty = _one(nx, [], [], [])
+    for s in (a, b):
+        pc.upload(s, ELECTRON, empty)
+        s.run_steps(3)
+        assert s.count(ELECTRON) == 0 and s.count(ION) == 0 and s.count(PHOTON) == 0
+        assert s.energy() == (0.0, 0.0, 0.0, 0.0)
+        assert s.last_leavers(ELECTRON) == (0, 0)
+    # one particle circling the minimal periodic grid: wraps every ~8 steps
+    one = _one(nx, [7], [0.9], [30.0], w=2.0e3)
+    for s in (a, b):
+        pc.upload(s, ELECTRON, one)
+    for _ in range(4):
+        a.run_steps(5)
+        b.run_steps(5)
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "prev_x", "ux", "uy", "uz", "gamma"))
+        pc.compare_fields(a.fields(), b.fields())
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_LEAN_STATE])
+def test_everything_in_one_cell(gpu, oracle, flags):
+    """ragged extreme: 6000 particles in ONE cell of 64 (one warp walks 188 chunks; hot enough to spill its mover strips)"""
+    nx, dx = 64, 500.0
+    a, b = Slab(gpu, nx, 0.0, dx, flags=flags), Slab(oracle, nx, 0.0, dx)
+    p = pc.thermal_particles(nx, 6000, dx, 0.5, seed=13, cells=np.array([31]))
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for chunk in (1, 1, 6):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
+        pc.compare_fields(a.fields(), b.fields())
+    assert a.count(ELECTRON) == 6000
+
+
+def test_open_domain_drains_completely(gpu, oracle):
+    """every particle leaves through the open edges (mod.rs:372-373): counts go to zero on both sides in step"""
+    nx, dx = 48, 1.0e-8
+    a = Slab(gpu, nx, 0.0, dx, None, BDY_LASER, BDY_ABSORBING)
+    b = Slab(oracle, nx, 0.0, dx, None, BDY_LASER, BDY_ABSORBING)
+    rng = np.random.default_rng(3)
+    n = 400
+    p = dict(cell=np.sort(rng.integers(0, nx, n)), x=rng.random(n), ux=np.where(rng.random(n) < 0.5, -40.0, 40.0), uy=np.zeros(n), uz=np.zeros(n),
+             weight=1.0 + 1e-6 * np.arange(n))
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for _ in range(60):
+        for s in (a, b):
+            pc.step_by_calls(s, 0.0, species=(ELECTRON,))
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        assert a.count(ELECTRON) == b.count(ELECTRON)
+    assert a.count(ELECTRON) == 0
+
+
+def test_full_bench_size_invariants(gpu):
+    """BASELINE config 4 at full size (1e9 electrons, 1e6 cells, lean layout) through size-independent properties:
+    the population is conserved exactly on the periodic ring, the deposited charge sums to the total charge (the four
+    spline weights sum to one, yee.rs:606-609), total energy is conserved to the leapfrog's accuracy, and the current is
+    the thermal noise it should be (zero mean)."""
+    import torch
+    free, _ = torch.cuda.mem_get_info()
+    if free < 100 * 2 ** 30:
+        pytest.skip("needs ~80 GB of free HBM")
+    nx, npc, dx, u_th = 1_000_000, 1000, 500.0, 0.03128
+    w = 20.0 * dx / npc
+    s = Slab(gpu, nx, 0.0, dx, flags=FLAG_LEAN_STATE, seed=12345)
+    s.generate(ELECTRON, npc, w, u_th=(u_th,) * 3)
+    assert s.count(ELECTRON) == nx * npc
+    e0 = None
+    for k in range(3):
+        s.run_steps(4)
+        e = s.energy()
+        f = s.fields()[s.left_size: s.left_size + nx]
+        rho, jx = f[:, 1], f[:, 2]
+        total_charge = rho.sum() * dx
+        assert abs(total_charge - ELECTRON_CHARGE * w * nx * npc) <= 1e-9 * abs(ELECTRON_CHARGE * w * nx * npc)
+        assert abs(jx.mean()) < 5.0 * jx.std() / np.sqrt(nx)
+        tot = e[0] + e[1]
+        if e0 is None:
+            e0 = tot
+        assert abs(tot - e0) <= 1e-6 * e0, (k, tot, e0)
+    assert s.count(ELECTRON) == nx * npc
+    assert s.last_leavers(ELECTRON)[0] >= 0
+    s.close()
