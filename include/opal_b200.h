@@ -220,6 +220,10 @@ opal_status OPAL_FN(launch_count)(opal_ctx*, int64_t* n);
    field update} since timing was enabled.                                                      */
 opal_status OPAL_FN(timing)(opal_ctx*, int enable);
 opal_status OPAL_FN(kernel_times)(opal_ctx*, double ms3[3], int64_t launches3[3]);
+/* Steps of opal_run_steps that ran as replayed CUDA graphs ("burst mode": launch-bound decks with deposition on,
+   emission off, no remote neighbour, timing off; two steps per graph, status read back once per 128 steps, a
+   device-side halt flag freezes the batch where the host must re-lay buckets out).  OPAL_BURST=0 disables it.   */
+opal_status OPAL_FN(burst_steps)(opal_ctx*, int64_t* n);
 /* device-generated synthetic plasma (BASELINE configs 4/5): npc particles in every cell,
    x uniform in [0,1), u = drift[k]*sign + u_th[k]*N(0,1) from Philox4x32-10 keyed by
    (seed, global particle index) so any slab count yields the same global particle set;

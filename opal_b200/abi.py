@@ -68,6 +68,7 @@ SIGNATURES = {
     "launch_count": [_vp, _pi64],
     "timing": [_vp, _int],
     "kernel_times": [_vp, _vp, _vp],
+    "burst_steps": [_vp, _pi64],
     "particles_generate": [_vp, _int, _i64, _f64, _vp, _vp, _int, _i64, _u64],
     "qed_rate": [_i64, _vp, _vp, _vp],
     "qed_sample": [_i64, _vp, _vp, _vp, _vp, _vp, _int, _vp],
@@ -321,6 +322,11 @@ class Slab:
     def launch_count(self):
         n = C.c_int64()
         self._ck(self.abi.launch_count(self._h, C.byref(n)), "launch_count")
+        return n.value
+
+    def burst_steps(self):
+        n = C.c_int64(0)
+        self._ck(self.abi.burst_steps(self._h, C.byref(n)), "burst_steps")
         return n.value
 
     def timing(self, enable=True):

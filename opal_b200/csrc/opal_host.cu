@@ -114,6 +114,8 @@ struct opal_ctx {
     StatusDev* h_status = nullptr;   // pinned
     double* d_energy = nullptr;      // 4 doubles + [4]: electron kinetic energy accumulated by the last fused push
     bool ke_fused = false;
+    double* d_laser = nullptr; long long laser_cap = 0;   // burst mode: per-step laser amplitudes on the device
+    int64_t burst_steps = 0;         // steps executed through replayed CUDA graphs (instrumentation)
     bool holes_open = false;         // lean electrons: the last fused step left holes in the buckets (count[] counts slots in use)           // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
@@ -556,6 +558,98 @@ void do_field(opal_ctx* c) {
     c->g = nxt;
 }
 
+
+// ---- burst mode: the fused step as a replayed CUDA graph ---------------------------------------------------------
+// Small decks (two_stream.yaml: 1e5 particles) spend their time in launch latency and in the per-step status
+// read-back, not in the kernels.  Two consecutive steps (the E/B ping-pong has period two) are captured once into a
+// CUDA graph and replayed; the status block is read back once per batch instead of once per species and step.  What
+// the host would have reacted to -- a parked mover (bucket full) or an assert -- raises a halt flag on the device
+// instead, and every later kernel of the batch returns at once, so the host finds the state exactly as it was when
+// the condition arose, completes that step the ordinary way (re-layout, remaining species, field update) and resumes.
+void swap_fields(opal_ctx* c) {
+    double** cur[6] = {&c->g.ex, &c->g.ey, &c->g.ez, &c->g.bx, &c->g.by, &c->g.bz};
+    for (int k = 0; k < 6; k++) std::swap(*cur[k], c->eb_alt[k]);
+}
+
+void enqueue_species(opal_ctx* c, int sp) {     // advance_charged without the host in the loop (fused deposit, local slab)
+    Buckets& B = c->bk[sp];
+    if (!B.allocated) return;
+    c->adv_calls[sp]++;
+    StepParams p = sparams(c, sp);
+    c->k.burst_mark(c->stream, c->d_status, 0, sp);
+    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status, nullptr);
+    if (strips) c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1, c->d_overflow, c->d_status);
+    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                 reinterpret_cast<int*>(c->d_overflow), c->d_status);
+    c->k.burst_mark(c->stream, c->d_status, 1, sp);
+    if (strips && c->k.push_leaves_holes) c->holes_open = true;
+}
+
+int enqueue_step(opal_ctx* c) {                 // main.rs:238-267 with deposition on, emission off; returns the launch count
+    const long long l0 = c->launches;
+    c->k.clear(c->stream, c->g);
+    enqueue_species(c, OPAL_ELECTRON);
+    enqueue_species(c, OPAL_ION);
+    c->k.sync_bc(c->stream, c->g, nullptr, 0.0, 0.0, nullptr);
+    do_field(c);
+    c->k.burst_mark(c->stream, c->d_status, 2, 0);
+    int n = 4;                                   // clear, sync_bc, field, end mark
+    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) n += 4 + ((sp == OPAL_ELECTRON && !c->bk[sp].full && c->cell_mover_cap > 0 && !(c->flags & OPAL_FLAG_STRICT_FP)) ? 1 : 0);
+    (void)l0;
+    return n;
+}
+
+// Runs up to n (even) steps from laser_y/z[0..n) as graph replays.  *done = steps completed; *halted tells whether the
+// step after them stopped half-way (c->h_status then holds the counters and halt_species of that moment).
+bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64_t* done, bool* halted) {
+    *done = 0; *halted = false;
+    if (c->laser_cap < 2 * n) {
+        if (c->d_laser) cudaFree(c->d_laser);
+        c->d_laser = nullptr; c->laser_cap = 0;
+        CUB(cudaMalloc(&c->d_laser, (size_t)(2 * n) * sizeof(double)));
+        c->laser_cap = 2 * n;
+    }
+    std::vector<double> lh((size_t)(2 * n), 0.0);
+    for (int64_t k = 0; k < n; k++) { lh[2 * k] = ly ? ly[k] : 0.0; lh[2 * k + 1] = lz ? lz[k] : 0.0; }
+    CUB(cudaMemcpyAsync(c->d_laser, lh.data(), lh.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    CUB(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    c->g.halt = &c->d_status->halt; c->g.step = &c->d_status->step; c->g.laser_arr = c->d_laser;
+    auto leave = [&]() { c->g.halt = nullptr; c->g.step = nullptr; c->g.laser_arr = nullptr; };
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int per_step = 0;
+    cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
+    if (e == cudaSuccess) {
+        per_step = enqueue_step(c);
+        enqueue_step(c);                         // the second half of the ping-pong: c->g is back where it started
+        e = cudaStreamEndCapture(c->stream, &graph);
+    }
+    if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+    if (e != cudaSuccess) { if (graph) cudaGraphDestroy(graph); leave(); return fail(c, OPAL_ECUDA, std::string("burst graph: ") + cudaGetErrorString(e)); }
+    bool ok = true;
+    int64_t s = 0;
+    while (s < n && ok) {
+        const int64_t batch = std::min<int64_t>(n - s, 128);
+        for (int64_t i = 0; i < batch; i += 2) {
+            if (cudaGraphLaunch(exec, c->stream) != cudaSuccess) { ok = fail(c, OPAL_ECUDA, "cudaGraphLaunch failed"); break; }
+        }
+        if (!ok) break;
+        c->launches += batch * per_step;
+        if (cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+            cudaStreamSynchronize(c->stream) != cudaSuccess) { ok = fail(c, OPAL_ECUDA, "burst status read-back failed"); break; }
+        *done = c->h_status->step;
+        if (c->h_status->halt) { *halted = true; break; }
+        s += batch;
+    }
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+    leave();
+    c->burst_steps += *done;
+    if (ok && (*done & 1)) swap_fields(c);       // an odd number of steps ran: the fields sit in the other buffer set
+    return ok;
+}
+
 }  // namespace
 
 // =============================== C ABI ======================================================
@@ -627,7 +721,7 @@ opal_status opal_destroy(opal_ctx* c) {
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
     void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_cmovers, c->d_cmcount, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
-                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables};
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser};
     for (void* p : frees) if (p) cudaFree(p);
     if (c->h_status) cudaFreeHost(c->h_status);
     if (c->h_energy) cudaFreeHost(c->h_energy);
@@ -1026,7 +1120,32 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     const bool fused = current_deposition && !photon_emission;
     double t = t0;
     c->ke_fused = false;
-    for (int64_t s = 0; s < nsteps; s++) {   // main.rs:238-267
+    int64_t s0 = 0;
+    // launch-bound decks: replay the fused step as a CUDA graph (all but the last one or two steps, which also sum the
+    // kinetic energy and report the leaver counts)
+    const bool burst_ok = fused && !remote(c) && !c->timing && c->ph[0].cap == 0 && env_ll("OPAL_BURST", 1) != 0 &&
+                          (long long)c->bk[0].n_hint + c->bk[1].n_hint <= env_ll("OPAL_BURST_MAX_PARTICLES", 20000000);
+    while (burst_ok && nsteps - s0 >= 6 && c->status == OPAL_OK) {
+        const int64_t n = ((nsteps - s0 - 1) / 2) * 2;
+        int64_t done = 0;
+        bool halted = false;
+        if (!run_burst(c, n, laser_y ? laser_y + s0 : nullptr, laser_z ? laser_z + s0 : nullptr, &done, &halted)) break;
+        s0 += done;
+        t += (double)done * c->g.dt;
+        if (!halted) break;
+        // step s0 stopped half-way: finish it the ordinary way, then resume
+        const unsigned err = c->h_status->err;
+        const int hsp = c->h_status->halt_species;
+        if (err) { fetch_status(c); break; }                      // an assert: sticky status, as in the ordinary path
+        c->last_gone[hsp][0] = c->h_status->gone[0]; c->last_gone[hsp][1] = c->h_status->gone[1];
+        if (!handle_overflow(c, hsp, true)) break;
+        if (hsp == OPAL_ELECTRON && !advance_charged(c, OPAL_ION, fused, true)) break;
+        if (!do_sync(c, laser_y ? laser_y[s0] : 0.0, laser_z ? laser_z[s0] : 0.0)) break;
+        do_field(c);
+        s0++;
+        t += c->g.dt;
+    }
+    for (int64_t s = s0; s < nsteps && c->status == OPAL_OK; s++) {   // main.rs:238-267
         if (current_deposition) { c->k.clear(c->stream, c->g); c->launches++; }
         // the last step of the call also sums the electrons' kinetic energy (lean strip kernel): opal_energy then needs no particle pass
         if (!advance_charged(c, OPAL_ELECTRON, fused, true, s == nsteps - 1 && !photon_emission)) break;
@@ -1176,6 +1295,12 @@ opal_status opal_kernel_times(opal_ctx* c, double ms3[3], int64_t launches3[3]) 
         }
         ms3[k] = total; launches3[k] = (int64_t)c->ev_used[k];
     }
+    return OPAL_OK;
+}
+
+opal_status opal_burst_steps(opal_ctx* c, int64_t* n) {
+    if (!c || !n) return OPAL_EINVAL;
+    *n = c->burst_steps;
     return OPAL_OK;
 }
 

@@ -86,6 +86,7 @@ __device__ __forceinline__ void deposit_atomic(const GridDev& g, int idx, double
 template <int SP, bool FULL, bool DEP>
 __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                  int* __restrict__ seg_count, StatusDev* __restrict__ st) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     __shared__ double s_ln_h[41];
     if (FULL && SP == OPAL_ELECTRON) {
         if (threadIdx.x < 41) s_ln_h[threadIdx.x] = c_ln_h[threadIdx.x];
@@ -369,6 +370,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                                                            int* __restrict__ seg_count, StripRec* __restrict__ strips,
                                                            int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out,
                                                            int* __restrict__ holes, int* __restrict__ hcount) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
     constexpr int CH = 32 * ILP;
     const int lane = threadIdx.x & 31;
@@ -690,6 +692,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                                                const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
                                                opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
                                                StatusDev* __restrict__ st, const int* __restrict__ holes, int* __restrict__ hcount) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     const int lane = threadIdx.x & 31;
     const int warps_total = gridDim.x * 8;
     const int MC = sp.cell_mover_cap;
@@ -835,6 +838,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
                                                   const int* __restrict__ seg_count, int nseg, int seg_cap, long long cell_shift,
                                                   opal_migrant* __restrict__ out_l, opal_migrant* __restrict__ out_r,
                                                   opal_migrant* __restrict__ overflow, StatusDev* __restrict__ st) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     const double q = species_charge(SP, b.z_star);
     for (int seg = blockIdx.x; seg < nseg; seg += gridDim.x) {
         int n = seg_count[seg];
@@ -1353,6 +1357,7 @@ __device__ __forceinline__ double cell_x(const GridDev& g, int c) { return g.xmi
 // one block.  halo_recv: [2][8][11] cells received from the left / right neighbour (remote case).
 __global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __restrict__ halo_recv, double laser_y, double laser_z,
                                                   const double* __restrict__ laser_dev) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     __shared__ double s_send[2][OPAL_HALO_CELLS][10];   // copies of my first / last 8 cells (yee.rs:353-354)
     const int G = OPAL_GHOST_SIZE;
     double* arr[10] = {g.rho, g.jx, g.jy, g.jz, g.ex, g.ey, g.ez, g.bx, g.by, g.bz};
@@ -1379,6 +1384,7 @@ __global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __rest
     __syncthreads();
     if (g.left_bdy == OPAL_BDY_LASER && tid == 0) {       // yee.rs:456-462
         if (laser_dev) { laser_y = laser_dev[0]; laser_z = laser_dev[1]; }
+        if (g.laser_arr) { const int k = *(volatile const int*)g.step; laser_y = g.laser_arr[2 * k]; laser_z = g.laser_arr[2 * k + 1]; }
         const int start = g.left - 2;
         const double r = OPAL_C * g.dt / g.dx;
         g.ey[start] += 2.0 * r * laser_y;
@@ -1416,6 +1422,7 @@ constexpr int FT = 256;   // field tile
 // one-cell halo it needs (identical arithmetic to the owning block) and writes its tile to the
 // other buffer of the E/B ping-pong, so no block ever reads a value another block has updated.
 __global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     __shared__ double s_ey[FT + 3], s_ez[FT + 3], s_by[FT + 2], s_bz[FT + 2];
     const int t0 = blockIdx.x * FT;
     const int tid = threadIdx.x;
@@ -1478,6 +1485,7 @@ __global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
 
 __global__ void k_clear(GridDev g) {   // yee.rs:543-549
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.len; i += gridDim.x * blockDim.x) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
         g.rho[i] = 0.0; g.jx[i] = 0.0; g.jy[i] = 0.0; g.jz[i] = 0.0;
     }
 }
@@ -1747,6 +1755,22 @@ static void l_emit(cudaStream_t s, const GridDev& g, const BucketDev& e, const P
     k_emit<<<grid, BLOCK, smem, s>>>(g, e, ph, sp, tables, t, min_energy, max_angle, max_fl, seed, call_index, st);
 }
 
+// burst-mode bookkeeping (one block): what == 0 zero the per-advance counters and the mover segment counters,
+// 1 raise halt when the advance of `species` parked movers or tripped an assert, 2 count the completed step
+__global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, int species) {
+    if (*(volatile int*)&st->halt) return;
+    if (what == 0) {
+        int* seg = reinterpret_cast<int*>(st + 1);
+        for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) seg[i] = 0;
+        if (threadIdx.x == 0) { st->n_movers = 0; st->n_overflow = 0; st->n_out[0] = st->n_out[1] = 0; st->gone[0] = st->gone[1] = 0; st->n_new_photons = 0; }
+    } else if (what == 1) {
+        if (threadIdx.x == 0 && (st->n_overflow > 0 || st->err)) { st->halt_species = species; __threadfence(); st->halt = 1; }
+    } else if (threadIdx.x == 0) {
+        st->step = st->step + 1;
+    }
+}
+static void l_burst_mark(cudaStream_t s, StatusDev* st, int what, int species) { k_burst_mark<<<1, what == 0 ? 1024 : 32, 0, s>>>(st, what, species); }
+
 static void l_sync_bc(cudaStream_t s, const GridDev& g, const double* halo_recv, double ly, double lz, const double* laser_dev) {
     k_sync_bc<<<1, 256, 0, s>>>(g, halo_recv, ly, lz, laser_dev);
 }
@@ -1818,7 +1842,7 @@ KernelTable table() {
     t.push = l_push; t.pull = l_pull; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
-    t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells;
+    t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
 #if defined(OPAL_FAST) && OPAL_PUSH_HOLES
     t.push_leaves_holes = true;
 #else

@@ -24,6 +24,12 @@ struct GridDev {
     double xmin, dx, dt;
     double *rho, *jx, *jy, *jz;     // current set (deposit target / field kernel source)
     double *ex, *ey, *ez, *bx, *by, *bz;
+    // graph-replayed bursts of steps (host: run_burst): every step kernel returns at once when *halt is set (a bucket
+    // overflowed or an assert fired in an earlier kernel of the burst); the laser amplitudes of step *step are
+    // laser_arr[2 * *step .. +1].  All three are null outside a burst.
+    const int* halt;
+    const int* step;
+    const double* laser_arr;
 };
 
 // Cell-major gapped buckets: cell c owns slots [start[c], start[c+1]) of which the first
@@ -53,6 +59,11 @@ struct StatusDev {
     unsigned err;        // bit 0: CFL assert, 1: index assert, 2: chi range, 3: buffer capacity
     int n_new_photons;
     int pad;
+    // burst mode (see GridDev::halt)
+    int halt;            // set by k_burst_check: the host has to intervene before the next kernel may run
+    int step;            // steps of the burst completed so far
+    int halt_species;    // the species whose advance raised the halt
+    int pad2;
 };
 enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
        // which fixed-capacity buffer overflowed (set together with ERR_CAPACITY)
@@ -114,6 +125,8 @@ struct KernelTable {
     // lean electrons: close the holes the fused step kernels leave (strip_count: the push's counter block)
     void (*compact_cells)(cudaStream_t, const BucketDev&, const int* strip_count);
     bool push_leaves_holes;     // the lean strip kernel was built with OPAL_PUSH_HOLES
+    // burst mode bookkeeping kernels: 0 begin (zero the per-advance counters), 1 check (raise halt on overflow / error), 2 end (step++)
+    void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species);
 };
 
 namespace fast { KernelTable table(); }

@@ -1323,6 +1323,7 @@ opal_status opal_ref_comm_init(opal_ctx*, const void*) { return OPAL_ENCCL; }
 opal_status opal_ref_stream(opal_ctx*, void** s) { if (s) *s = nullptr; return OPAL_OK; }
 opal_status opal_ref_launch_count(opal_ctx*, int64_t* n) { if (n) *n = 0; return OPAL_OK; }
 opal_status opal_ref_timing(opal_ctx*, int) { return OPAL_OK; }
+opal_status opal_ref_burst_steps(opal_ctx*, int64_t* n) { if (n) *n = 0; return OPAL_OK; }
 opal_status opal_ref_kernel_times(opal_ctx*, double* ms, int64_t* n) { for (int i = 0; i < 3; i++) { ms[i] = 0.0; n[i] = 0; } return OPAL_OK; }
 opal_status opal_ref_particles_generate(opal_ctx*, int, int64_t, double, const double*, const double*, int, int64_t, uint64_t) {
     return OPAL_EINVAL;   // the oracle is fed the arrays the GPU generator produced (download -> upload)

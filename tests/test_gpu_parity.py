@@ -307,3 +307,41 @@ def test_two_gpu_nccl_ring_matches_single_oracle_slab():
                           "--master-port", "29531", str(script)], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("MGPU OK") == 5, out.stdout[-3000:]
+
+
+@pytest.mark.parametrize("flags", [0, FLAG_LEAN_STATE])
+def test_graph_replayed_bursts_equal_the_step_by_step_path(gpu, oracle, monkeypatch, flags):
+    """opal_run_steps replays launch-bound decks as CUDA graphs (burst mode).  Same kernels, same order: the result equals
+    the ordinary path's to deposit-atomics round-off -- including when a bucket overflows inside a burst (the device-side
+    halt, the host's re-layout and the resumed burst) and with a laser whose amplitude changes every step."""
+    nx, dx = 160, 2.0e-8
+    laser = lambda t: 2.0e12 * math.sin(2.0e15 * t)
+    p = pc.thermal_particles(nx, 40, dx, 0.3, seed=21, ne=4.0e26, cells=np.arange(40, 120))
+    monkeypatch.setenv("OPAL_BUCKET_SLACK", "1.0")      # tight buckets: the expanding slab forces re-layouts
+    monkeypatch.setenv("OPAL_BUCKET_PAD", "8")
+    runs = {}
+    for burst in ("1", "0"):
+        monkeypatch.setenv("OPAL_BURST", burst)
+        a = Slab(gpu, nx, 0.0, dx, None, BDY_LASER, BDY_ABSORBING, flags=flags)
+        pc.upload(a, ELECTRON, p)
+        t = 0.0
+        for n in (41, 7, 64):
+            ts = t + a.dt * np.arange(n)
+            a.run_steps(n, t, laser_y=[laser(v) for v in ts], laser_z=[0.5 * laser(v) for v in ts])
+            t += n * a.dt
+        runs[burst] = (a.download(ELECTRON), a.fields(), a.energy(), a.burst_steps(), a.last_leavers(ELECTRON))
+    assert runs["1"][3] >= 90 and runs["0"][3] == 0          # the burst path really ran (41+7+64 steps, minus remainders and halts)
+    pc.compare_particles(runs["1"][0], runs["0"][0], fields=("x", "ux", "uy", "uz"), tol=1e-11)
+    pc.compare_fields(runs["1"][1], runs["0"][1], tol=1e-11)
+    assert runs["1"][4] == runs["0"][4]
+    for k in range(2):
+        assert abs(runs["1"][2][k] - runs["0"][2][k]) <= 1e-11 * abs(runs["0"][2][k])
+    # and both agree with the oracle stepping the same deck
+    b = Slab(oracle, nx, 0.0, dx, None, BDY_LASER, BDY_ABSORBING)
+    pc.upload(b, ELECTRON, p)
+    t = 0.0
+    for n in (41, 7, 64):
+        ts = t + b.dt * np.arange(n)
+        b.run_steps(n, t, laser_y=[laser(v) for v in ts], laser_z=[0.5 * laser(v) for v in ts])
+        t += n * b.dt
+    pc.compare_particles(runs["1"][0], b.download(ELECTRON), fields=("x", "ux", "uy", "uz"), tol=1e-8)
