@@ -130,7 +130,7 @@ struct opal_ctx {
     size_t ev_used[3] = {0, 0, 0};
     int status = OPAL_OK;
     std::string err;
-    double slack = 1.25; int pad = 64;
+    double slack = 1.25; int pad = 64; bool slack_from_env = false;
     // adaptive re-layout (regrid): per charged species, steps since the last one, neighbourhood radius and slack boost
     long long adv_calls[2] = {0, 0}, last_regrid[2] = {-1000000, -1000000};
     int regrid_radius[2] = {0, 0};
@@ -189,15 +189,22 @@ void free_buckets(Buckets& B) {
 }
 
 // capacity policy: demand * slack + pad, rounded up to a multiple of 32 slots
-long long bucket_cap(opal_ctx* c, long long demand) {
-    long long cap = (long long)std::ceil((double)demand * c->slack) + c->pad;
+long long bucket_cap(opal_ctx* c, long long demand, bool roomy) {
+    // small populations (memory is no concern): twice the demand, so the density fluctuations of e.g. a saturated
+    // two-stream instability do not force a re-layout (a host round trip) every few steps
+    const double slack = roomy ? std::max(c->slack, 2.0) : c->slack;
+    const long long pad = roomy ? std::max(c->pad, 128) : c->pad;
+    long long cap = (long long)std::ceil((double)demand * slack) + pad;
     return (cap + 31) / 32 * 32;
 }
 
 bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand, bool full) {
     const int ncell = c->g.nx;
     B.h_start.assign(ncell + 1, 0);
-    for (int i = 0; i < ncell; i++) B.h_start[i + 1] = B.h_start[i] + bucket_cap(c, demand[i]);
+    long long total = 0;
+    for (int i = 0; i < ncell; i++) total += demand[i];
+    const bool roomy = !c->slack_from_env && total <= 4000000 && (long long)ncell <= 4000000;
+    for (int i = 0; i < ncell; i++) B.h_start[i + 1] = B.h_start[i] + bucket_cap(c, demand[i], roomy);
     B.slots = B.h_start[ncell];
     B.full = full;
     CUB(cudaMalloc(&B.d_start, (size_t)(ncell + 1) * sizeof(long long)));
@@ -667,6 +674,7 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     c->full = !(flags & OPAL_FLAG_LEAN_STATE);
     c->k = (flags & OPAL_FLAG_STRICT_FP) ? strict::table() : fast::table();
     c->slack = env_double("OPAL_BUCKET_SLACK", 1.25);
+    c->slack_from_env = getenv("OPAL_BUCKET_SLACK") != nullptr || getenv("OPAL_BUCKET_PAD") != nullptr;
     c->pad = (int)env_ll("OPAL_BUCKET_PAD", 64);
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));

@@ -2,10 +2,11 @@
 // libopal_b200.so entry point (include/opal_b200.h).  The reference's driver is Rust; no Rust toolchain exists in
 // this image, so the host side is C++ (INTEGRATION.md shows the Rust `extern "C"` block for the same calls).
 //
-//   opal_b200_driver input.yaml [--ranks N] [--device D] [--lean] [--outputs K] [--quiet]
+//   opal_b200_driver input.yaml [--ranks N] [--device D] [--lean|--full] [--outputs K] [--quiet]
 //
 // --ranks N    one process per GPU (the reference: mpirun -n N), x-slabs from GridDesign, NCCL ring inside the library
-// --lean       keep only (x, u, w) per particle (QED off, deposition on, no r/work/chi outputs): the 80 B/particle-step layout
+// --lean/--full  keep only (x, u, w) per particle -- the 80 B/particle-step layout; automatic when QED is off, deposition on and
+//              no r/work/chi output is requested -- or insist on the reference's whole per-particle state
 // --outputs K  stop after output K (for tests; default: run to `end`)
 #include <chrono>
 #include <cmath>
@@ -42,7 +43,7 @@ template <class F> bool optional_read(F f) {      // `.ok()` / `.unwrap_or()` of
 struct Options {
     std::string input;
     int ranks = 1, device = -1;
-    bool lean = false, quiet = false;
+    bool lean = false, full = false, quiet = false;
     long outputs = -1;
 };
 
@@ -96,7 +97,21 @@ int run(const Options& opt, Ranks& ranks) {
     const double my_xmin = xmin + design.offset[(size_t)id];
 
     // ---- the slab context (YeeGrid::build, yee.rs:272-319) ----
-    const uint32_t flags = opt.lean ? OPAL_FLAG_LEAN_STATE : 0u;
+    // The lean (x, u, w) layout -- the fused fast kernel -- is valid when nothing observable needs the rest of the
+    // particle state: QED off, deposition on, and no r / work / chi distribution requested.  It is chosen automatically
+    // then (--full keeps the reference's whole per-particle state, --lean insists).
+    bool lean_ok = !photon_emission && !photon_absorption && current_deposition;
+    for (const char* sec : {"electrons", "ions"}) {
+        std::vector<std::string> outs;
+        optional_read([&] { outs = input.read_strings(sec, "output"); });
+        for (const std::string& o : outs) {
+            const OutputSpec spec = OutputSpec::parse(o);
+            for (int q : spec.quantity) if (q == OPAL_Q_R || q == OPAL_Q_WORK || q == OPAL_Q_CHI) lean_ok = false;
+        }
+    }
+    if (opt.lean && !lean_ok) throw std::runtime_error("--lean: this deck needs the full particle state (QED on, deposition off, or r/work/chi outputs)");
+    const bool lean = opt.lean || (lean_ok && !opt.full);
+    const uint32_t flags = lean ? OPAL_FLAG_LEAN_STATE : 0u;
     opal_ctx* ctx = nullptr;
     const int device = opt.device >= 0 ? opt.device + id : id;
     ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, flags), nullptr, "opal_create");
@@ -218,6 +233,7 @@ int main(int argc, char** argv) {
         else if (s == "--device" && a + 1 < argc) opt.device = std::atoi(argv[++a]);
         else if (s == "--outputs" && a + 1 < argc) opt.outputs = std::atol(argv[++a]);
         else if (s == "--lean") opt.lean = true;
+        else if (s == "--full") opt.full = true;
         else if (s == "--quiet") opt.quiet = true;
         else if (!s.empty() && s[0] != '-' && opt.input.empty()) opt.input = s;
         else { std::fprintf(stderr, "unknown argument %s\n", s.c_str()); return 2; }

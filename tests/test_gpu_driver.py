@@ -130,11 +130,11 @@ def _compare_dirs(a, b, indices, fits, rel):
 def test_two_stream_deck_gpu_vs_oracle(tmp_path):
     subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
     deck = TWO_STREAM.format(end=repr(200.5 * DT500))
-    a = _run(GPU_DRIVER, deck, tmp_path, "gpu")
+    a = _run(GPU_DRIVER, deck, tmp_path, "gpu", extra=("--full",))       # the reference's whole per-particle state
     b = _run(REF_DRIVER, deck, tmp_path, "ref")
     _compare_dirs(a, b, (0, 1, 2), ("electron_x-px", "electron_px", "electron_energy"), rel=2e-6)
-    # the lean (x, u, w) layout runs the fused fast kernel: same outputs
-    c = _run(GPU_DRIVER, deck, tmp_path, "lean", extra=("--lean",))
+    # default for this deck (QED off, deposition on, no r/work/chi output): the lean (x, u, w) layout and the fused fast kernel
+    c = _run(GPU_DRIVER, deck, tmp_path, "lean")
     _compare_dirs(c, b, (0, 1, 2), ("electron_x-px", "electron_px", "electron_energy"), rel=2e-6)
 
 
@@ -143,10 +143,12 @@ def test_hole_boring_deck_gpu_vs_oracle(tmp_path):
     subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
     dt = 0.95 * 1.0e-8 / 2.997925e8
     deck = HOLE_BORING.format(end=repr(-3.0e-6 / 2.997925e8 + 240.5 * dt))
-    a = _run(GPU_DRIVER, deck, tmp_path, "gpu")
+    a = _run(GPU_DRIVER, deck, tmp_path, "gpu", extra=("--full",))
     b = _run(REF_DRIVER, deck, tmp_path, "ref")
     fits = ("electron_x-px", "electron_x-p_perp", "electron_py-pz", "carbon_x-px", "carbon_energy")
     _compare_dirs(a, b, (0, 1), fits, rel=1e-5)
+    lean = _run(GPU_DRIVER, deck, tmp_path, "lean")                      # automatic: lean electrons (fast kernel) + lean ions
+    _compare_dirs(lean, b, (0, 1), fits, rel=1e-5)
     # after the pulse has hit the plasma round-off grows exponentially: conservation-level agreement
     ea, eb = _energies(a / "2_energy.dat"), _energies(b / "2_energy.dat")
     for k in ("em_field", "electrons", "ions"):
