@@ -317,8 +317,16 @@ __constant__ signed char c_pre_k[18] = {0, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 2, 2, 3
 // 8-byte slots whose 32-byte sectors have long left the L2: ~48 x 5 partial-sector read-modify-writes per cell make
 // k_pull 1.5 -> 4.0-4.5 ms.  Net loss (19.1-20.0 vs 17.0 ms per step), so the default stays the in-push shift; the way
 // to keep the push's gain is to consume the strips inside the NEXT push, while the cell's sectors stream through L2.
+// OPAL_PUSH_HOLES == 2 (experimental): in-place stayers as above, but the push closes its own holes before it leaves
+// the cell ("tail fill" from a shared-memory hole list, while the sectors are still in L2): count[] stays the live count
+// and k_pull and every other consumer are untouched.  Measured: DRAM writes drop as intended, but the four dependent
+// round trips of the fill at the end of every cell cost the push more than the 8 B/particle save (16.0 vs 15.4-15.6 ms),
+// step 17.5 vs 17.0-17.1 ms.  Also a net loss; kept selectable for the record.
 #ifndef OPAL_PUSH_HOLES
 #define OPAL_PUSH_HOLES 0
+#endif
+#ifndef OPAL_HOLE_LIST
+#define OPAL_HOLE_LIST 256             // slot indices per warp (shared memory); a cell with more movers falls back to the shift
 #endif
 #define OPAL_HOLE_MARK (__longlong_as_double(0x7ff8dead0000beefll))   // a quiet NaN: never a valid offset
 __device__ __forceinline__ bool is_hole(double x) { return x != x; }
@@ -389,7 +397,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         const int n = b.count[c];
         if (n == 0) {
             if (lane < 2) scount[2 * c + lane] = 0;
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
             if (lane == 2) hcount[c] = 0;
 #endif
             continue;
@@ -399,6 +407,10 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
         int mloc_l = 0, mloc_r = 0;   // left / right movers of this cell so far (warp-uniform): slots in its two strips
 #if OPAL_PUSH_HOLES
         int n_holes = 0;              // holes of this cell so far (warp-uniform)
+#endif
+#if OPAL_PUSH_HOLES == 2
+        __shared__ int s_holes[OPAL_PUSH_WPB][OPAL_HOLE_LIST];
+        int* const hole_list = s_holes[threadIdx.x >> 5];
 #endif
         // the 18 field values every lane of this warp gathers from -> 18 per-cell gather coefficients (CellPre),
         // one copy per warp in shared memory
@@ -462,7 +474,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             RFaces ro[ILP];
             int d[ILP];
             bool valid[ILP];
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
             bool was_hole[ILP];
 #endif
 #if OPAL_PUSH_STAGES > 0
@@ -472,7 +484,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 valid[q] = k0 + q * 32 + lane < n;
                 const int e = q * 32 + lane;
                 x[q] = valid[q] ? ring[stage][0][e] : 0.0;
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
                 was_hole[q] = valid[q] && is_hole(x[q]);      // a hole no arrival has filled yet: skipped, re-listed below
                 if (was_hole[q]) { valid[q] = false; x[q] = 0.0; }
 #endif
@@ -499,7 +511,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             for (int q = 0; q < ILP; q++) {
                 x[q] = nx0[q]; u[q] = {nx1[q], nx2[q], nx3[q]}; W[q] = nx4[q];
                 valid[q] = k0 + q * 32 + lane < n;
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
                 was_hole[q] = valid[q] && is_hole(x[q]);
                 if (was_hole[q]) { valid[q] = false; x[q] = 0.0; u[q] = {0.0, 0.0, 0.0}; W[q] = 0.0; }
 #endif
@@ -623,7 +635,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 }
                 written += __popc(m_stay[q]);
                 base_l += __popc(m_l[q]); base_r += __popc(m_r[q]);
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
                 {   // list every hole of this chunk: slots just vacated and slots still empty from earlier steps
                     const bool hole = was_hole[q] || (valid[q] && d[q] != 0);
                     const unsigned m_hole = __ballot_sync(FULLMASK, hole);
@@ -633,13 +645,22 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                     }
                     n_holes += __popc(m_hole);
                 }
+#elif OPAL_PUSH_HOLES == 2
+                {   // the slots this chunk vacated, kept in the warp's shared-memory list for the tail fill below
+                    const unsigned m_hole = m_l[q] | m_r[q];
+                    if ((m_hole >> lane) & 1u) {
+                        const int k = n_holes + __popc(m_hole & lt_mask);
+                        if (k < OPAL_HOLE_LIST) hole_list[k] = i;
+                    }
+                    n_holes += __popc(m_hole);
+                }
 #endif
             }
         }
 #if OPAL_PUSH_STAGES > 0
         cp_async_wait<0>();
 #endif
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
         if (n_holes > 2 * MC) {
             // rare: more holes than the list holds.  Close them all now by shifting the live particles down.
             const int live = compact_cell(b, base, n, lane, lt_mask);
@@ -647,6 +668,42 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
             n_holes = 0;
         }
         if (lane == 0) { scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC; hcount[c] = n_holes; }
+#elif OPAL_PUSH_HOLES == 2
+        // Tail fill: the bucket shrinks by n_holes slots; the live particles of the cut-off tail [n_new, n) move into the
+        // holes below n_new (exactly as many of one as of the other).  The sectors involved were written by this warp
+        // microseconds ago, so the scattered 8-byte moves merge in L2 instead of costing DRAM read-modify-writes.
+        if (n_holes > OPAL_HOLE_LIST) {
+            const int live = compact_cell(b, base, n, lane, lt_mask);      // rare: list too short, shift instead
+            if (lane == 0) b.count[c] = live;
+        } else if (n_holes > 0) {
+            const int n_new = n - n_holes;
+            __syncwarp();                                     // hole_list and this cell's stores are visible warp-wide
+            int n_low = 0;
+            for (int k0 = 0; k0 < n_holes; k0 += 32) {        // keep the holes below n_new, in place
+                const int k = k0 + lane;
+                const int hs = k < n_holes ? hole_list[k] : 0x7fffffff;
+                const unsigned m_low = __ballot_sync(FULLMASK, hs < n_new);
+                __syncwarp();
+                if (hs < n_new) hole_list[n_low + __popc(m_low & lt_mask)] = hs;
+                n_low += __popc(m_low);
+            }
+            __syncwarp();
+            int taken = 0;
+            for (int t0 = n_new; t0 < n && taken < n_low; t0 += 32) {
+                const int t = t0 + lane;
+                double v0 = 0.0;
+                bool live = false;
+                if (t < n) { v0 = __ldcg(fx + base + t); live = !is_hole(v0); }
+                const unsigned m_live = __ballot_sync(FULLMASK, live);
+                if (live) {
+                    const long long from = base + t, to = base + hole_list[taken + __popc(m_live & lt_mask)];
+                    fx[to] = v0; fux[to] = __ldcg(fux + from); fuy[to] = __ldcg(fuy + from); fuz[to] = __ldcg(fuz + from); fw[to] = __ldcg(fw + from);
+                }
+                taken += __popc(m_live);
+            }
+            if (lane == 0) b.count[c] = n_new;
+        }
+        if (lane == 0) { scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC; }
 #else
         if (lane == 0) {
             b.count[c] = written;
@@ -742,7 +799,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             }
         }
         const int n_in = n_from_l + n_from_r;
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
         const int n_holes = hcount[c];         // listed by the push: slots of this bucket that are free
         if (n_in == 0) continue;
 #else
@@ -762,7 +819,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             if (i < n_in) {
                 const StripRec r = i < n_from_l ? strips[((long long)src_l * 2 + 1) * MC + i]
                                                 : strips[((long long)src_r * 2) * MC + (i - n_from_l)];
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
                 // the first n_holes arrivals drop into the listed holes, the rest are appended behind the slots in use
                 const int slot = i < n_holes ? holes[(long long)c * (2 * MC) + i] : cnt + (i - n_holes);
 #else
@@ -802,7 +859,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                 }
             }
         }
-#if OPAL_PUSH_HOLES
+#if OPAL_PUSH_HOLES == 1
         if (lane == 0) {
             if (n_in > n_holes) b.count[c] = cnt + (n_in - n_holes);
             hcount[c] = n_in < n_holes ? n_holes - n_in : 0;       // holes still open (k_compact_cells skips cells without)
@@ -1843,7 +1900,7 @@ KernelTable table() {
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
     t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
-#if defined(OPAL_FAST) && OPAL_PUSH_HOLES
+#if defined(OPAL_FAST) && OPAL_PUSH_HOLES == 1
     t.push_leaves_holes = true;
 #else
     t.push_leaves_holes = false;
