@@ -177,7 +177,7 @@ StepParams sparams(opal_ctx* c, int species) {
     sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap; sp.overflow_cap = c->overflow_cap;
-    sp.cell_mover_cap = (species == OPAL_ELECTRON) ? c->cell_mover_cap : 0;
+    sp.cell_mover_cap = (species == OPAL_ELECTRON || species == OPAL_ION) ? c->cell_mover_cap : 0;   // the strips serve one species at a time
     return sp;
 }
 
@@ -802,7 +802,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = n;
     if (!ensure_movers(c, n)) return (opal_status)c->status;
-    if (species == OPAL_ELECTRON && !ensure_cell_movers(c, n)) return (opal_status)c->status;
+    if (!ensure_cell_movers(c, n)) return (opal_status)c->status;
     // host-side bucketing into the slot layout (stable: keeps the caller's order inside a cell)
     const int nf = c->full ? NF_FULL : NF_LEAN;
     std::vector<std::vector<double>> hf(nf, std::vector<double>((size_t)B.slots, 0.0));
@@ -845,7 +845,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = npc * (long long)c->g.nx;
     if (!ensure_movers(c, B.n_hint)) return (opal_status)c->status;
-    if (species == OPAL_ELECTRON && !ensure_cell_movers(c, B.n_hint)) return (opal_status)c->status;
+    if (!ensure_cell_movers(c, B.n_hint)) return (opal_status)c->status;
     c->k.generate(c->stream, bdev(c, species), species, npc, weight, u_th, drift, two_stream, global_cell_offset, seed, c->full, c->g.dx, c->g.dt);
     c->launches++;
     CU(cudaStreamSynchronize(c->stream));

@@ -373,7 +373,9 @@ __global__ void __launch_bounds__(256) k_compact_cells(BucketDev b, const int* _
     }
 }
 
-template <bool BX0, bool KE>
+// SP: OPAL_ELECTRON -> Vay push (electron.rs:268-330); OPAL_ION -> Boris push (ion.rs:168-214) in the same reciprocal
+// arithmetic, alpha and the deposited charge from Z* and A (ion.rs:170-172).
+template <bool BX0, bool KE, int SP>
 __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
                                                            int* __restrict__ seg_count, StripRec* __restrict__ strips,
                                                            int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out,
@@ -384,7 +386,8 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * OPAL_PUSH_WPB;
-    const double alpha = OPAL_QE * g.dt / (2.0 * OPAL_ME * OPAL_C);
+    const double qsp = SP == OPAL_ELECTRON ? OPAL_QE : b.z_star * OPAL_E;
+    const double alpha = SP == OPAL_ELECTRON ? OPAL_QE * g.dt / (2.0 * OPAL_ME * OPAL_C) : qsp * g.dt / (2.0 * (b.mass_number * OPAL_MP) * OPAL_C);
     const double ac = alpha * OPAL_C;
     const double kdt = OPAL_C * g.dt / g.dx;
     bool cfl = false, cap_err = false;
@@ -534,26 +537,41 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
                 tv.x = BX0 ? 0.0 : P.tx;
                 tv.y = fma(x2, P.dty2, fma(xm2, P.dty0, P.ty1));
                 tv.z = fma(x2, P.dtz2, fma(xm2, P.dtz0, P.tz1));
-                // ---- Vay push (electron.rs:268-330) ----
-                // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma
-                const double ig = fast_rsqrt(fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0))));
-                const V3 uxt = BX0 ? V3{u[q].y * tv.z - u[q].z * tv.y, -(u[q].x * tv.z), u[q].x * tv.y} : cross(u[q], tv);
-                const V3 ue = u[q] + aE;
-                const V3 u_prime = {fma(ig, uxt.x, ue.x) + aE.x, fma(ig, uxt.y, ue.y) + aE.y, fma(ig, uxt.z, ue.z) + aE.z};
-                const double gp2 = fma(u_prime.x, u_prime.x, fma(u_prime.y, u_prime.y, fma(u_prime.z, u_prime.z, 1.0)));
-                const double u_star = BX0 ? fma(u_prime.y, tv.y, u_prime.z * tv.z) : dot(u_prime, tv);
-                const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
-                const double hs = 0.5 * (gp2 - tau2);
-                gam2[q] = hs + fast_sqrt(fma(hs, hs, fma(u_star, u_star, tau2)));
                 double gam;
-                fast_rsqrt_sqrt(gam2[q], igam[q], gam);
-                // u = s (u' + (u'.t) t + u' x t), t = tau/gamma, s = 1/(1+t^2)   ==   (gamma^2 u' + (u'.tau) tau + gamma u' x tau) / (gamma^2 + tau^2)
-                const double inv = fast_rcp(gam2[q] + tau2);
-                const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
-                V3 w = {fma(gam, pxt.x, gam2[q] * u_prime.x), fma(gam, pxt.y, gam2[q] * u_prime.y), fma(gam, pxt.z, gam2[q] * u_prime.z)};
-                if (!BX0) w.x = fma(u_star, tv.x, w.x);
-                w.y = fma(u_star, tv.y, w.y); w.z = fma(u_star, tv.z, w.z);
-                u[q] = inv * w;
+                if (SP == OPAL_ELECTRON) {
+                    // ---- Vay push (electron.rs:268-330) ----
+                    // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma
+                    const double ig = fast_rsqrt(fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0))));
+                    const V3 uxt = BX0 ? V3{u[q].y * tv.z - u[q].z * tv.y, -(u[q].x * tv.z), u[q].x * tv.y} : cross(u[q], tv);
+                    const V3 ue = u[q] + aE;
+                    const V3 u_prime = {fma(ig, uxt.x, ue.x) + aE.x, fma(ig, uxt.y, ue.y) + aE.y, fma(ig, uxt.z, ue.z) + aE.z};
+                    const double gp2 = fma(u_prime.x, u_prime.x, fma(u_prime.y, u_prime.y, fma(u_prime.z, u_prime.z, 1.0)));
+                    const double u_star = BX0 ? fma(u_prime.y, tv.y, u_prime.z * tv.z) : dot(u_prime, tv);
+                    const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
+                    const double hs = 0.5 * (gp2 - tau2);
+                    gam2[q] = hs + fast_sqrt(fma(hs, hs, fma(u_star, u_star, tau2)));
+                    fast_rsqrt_sqrt(gam2[q], igam[q], gam);
+                    // u = s (u' + (u'.t) t + u' x t), t = tau/gamma, s = 1/(1+t^2)   ==   (gamma^2 u' + (u'.tau) tau + gamma u' x tau) / (gamma^2 + tau^2)
+                    const double inv = fast_rcp(gam2[q] + tau2);
+                    const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
+                    V3 w = {fma(gam, pxt.x, gam2[q] * u_prime.x), fma(gam, pxt.y, gam2[q] * u_prime.y), fma(gam, pxt.z, gam2[q] * u_prime.z)};
+                    if (!BX0) w.x = fma(u_star, tv.x, w.x);
+                    w.y = fma(u_star, tv.y, w.y); w.z = fma(u_star, tv.z, w.z);
+                    u[q] = inv * w;
+                } else {
+                    // ---- Boris push (ion.rs:168-214): u- = u + alpha E; u' = u- + (u- x tau)/gamma-;
+                    //      u+ = u- + (u' x tau) 2 gamma- / (gamma-^2 + tau^2); u = u+ + alpha E   (tau = alpha c B) ----
+                    const V3 um = u[q] + aE;
+                    const double ig = fast_rsqrt(fma(um.x, um.x, fma(um.y, um.y, fma(um.z, um.z, 1.0))));
+                    const V3 mxt = BX0 ? V3{um.y * tv.z - um.z * tv.y, -(um.x * tv.z), um.x * tv.y} : cross(um, tv);
+                    const V3 u_prime = {fma(ig, mxt.x, um.x), fma(ig, mxt.y, um.y), fma(ig, mxt.z, um.z)};
+                    const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
+                    const double s2 = (2.0 * ig) * fast_rcp(fma(tau2 * ig, ig, 1.0));
+                    const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
+                    u[q] = {fma(s2, pxt.x, um.x) + aE.x, fma(s2, pxt.y, um.y) + aE.y, fma(s2, pxt.z, um.z) + aE.z};
+                    gam2[q] = fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0)));
+                    fast_rsqrt_sqrt(gam2[q], igam[q], gam);
+                }
                 const double dxi = (kdt * igam[q]) * u[q].x;
                 if (valid[q] && !(dxi < 1.0)) cfl = true;
                 xn[q] = x[q] + dxi;
@@ -712,7 +730,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 #endif
 
         // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
-        const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
+        const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
         double v13[13] = {kx * sjx0, kx * sjx1, kx * sjx2, ky * sjy0, ky * sjy1, ky * sjy2, ky * sjz0, ky * sjz1, ky * sjz2,
                           kr * sr0, kr * sr1, kr * sr2, kr * sr3};
 #pragma unroll
@@ -743,7 +761,7 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 // boundary (mod.rs:290-373): periodic self-neighbour => the strips of the opposite edge; remote
 // neighbour => the edge strips are copied to the outbox here and arrive through the inbox path.
 #ifndef OPAL_PULL_MINBLK
-#define OPAL_PULL_MINBLK 3
+#define OPAL_PULL_MINBLK 4
 #endif
 __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
                                                const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
@@ -867,7 +885,8 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
 #else
         if (lane == 0) b.count[c] = cnt + n_in;
 #endif
-        const double kx = OPAL_QE / g.dt, kr = OPAL_QE / g.dx, ky = OPAL_QE * OPAL_C / g.dx;
+        const double qsp = sp.species == OPAL_ION ? b.z_star * OPAL_E : OPAL_QE;
+        const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
 #pragma unroll
         for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]) * (k < 5 ? kx : (k < 11 ? ky : kr));
         double mine = 0.0;
@@ -1718,13 +1737,16 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
-    if (sp.species == OPAL_ELECTRON && !full && dep && strips && sp.cell_mover_cap > 0) {
+    if ((sp.species == OPAL_ELECTRON || sp.species == OPAL_ION) && !full && dep && strips && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
         const int gr = (int)(blocks < 1 ? 1 : blocks);
-#define LAUNCHF(B0, K) k_push_lean_fast<B0, K><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
-        if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
+#define LAUNCHF(B0, K) k_push_lean_fast<B0, K, OPAL_ELECTRON><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
+#define LAUNCHI(B0) k_push_lean_fast<B0, false, OPAL_ION><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, nullptr, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
+        if (sp.species == OPAL_ION) { if (sp.flags & OPAL_STEP_BX_ZERO) LAUNCHI(true); else LAUNCHI(false); }
+        else if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
         else { if (ke_out) LAUNCHF(false, true); else LAUNCHF(false, false); }
 #undef LAUNCHF
+#undef LAUNCHI
         return true;
     }
 #endif

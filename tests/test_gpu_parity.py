@@ -345,3 +345,37 @@ def test_graph_replayed_bursts_equal_the_step_by_step_path(gpu, oracle, monkeypa
         b.run_steps(n, t, laser_y=[laser(v) for v in ts], laser_z=[0.5 * laser(v) for v in ts])
         t += n * b.dt
     pc.compare_particles(runs["1"][0], b.download(ELECTRON), fields=("x", "ux", "uy", "uz"), tol=1e-8)
+
+
+@pytest.mark.parametrize("bx", [0.0, 3.0e-7])
+def test_lean_ions_fast_boris_kernel(gpu, oracle, bx):
+    """Lean electrons AND lean ions through the fused fast kernels (Vay / Boris in reciprocal arithmetic, per-cell gather
+    coefficients, mover strips) against the oracle's literal ion.rs:168-214 / electron.rs:268-330: C6+ ions hot enough to
+    cross cells, seed fields on every component (bx != 0 selects the general rotation)."""
+    nx, dx = 128, 500.0
+    a = Slab(gpu, nx, 0.0, dx, flags=FLAG_LEAN_STATE)
+    b = Slab(oracle, nx, 0.0, dx)
+    pe = pc.thermal_particles(nx, 60, dx, 0.2, seed=51)
+    pi = pc.thermal_particles(nx, 40, dx, 0.15, seed=52, ne=20.0 / 6.0)
+    f = b.fields()
+    k = np.arange(f.shape[0])
+    f[:, pc.FIELD_NAMES.index("Bx")] = bx
+    f[:, pc.FIELD_NAMES.index("By")] = 2.0e-7 * np.cos(0.07 * k)
+    f[:, pc.FIELD_NAMES.index("Bz")] = -1.5e-7 * np.sin(0.05 * k)
+    f[:, pc.FIELD_NAMES.index("Ey")] = 40.0 * np.sin(0.09 * k)
+    f[:, pc.FIELD_NAMES.index("Ez")] = 25.0 * np.cos(0.04 * k)
+    f[:, pc.FIELD_NAMES.index("Ex")] = 10.0 * np.sin(0.11 * k)
+    for s_ in (a, b):
+        s_.set_fields(f)
+        s_.set_ion(6.0, 12.0)
+        pc.upload(s_, ELECTRON, pe)
+        pc.upload(s_, ION, pi)
+    for chunk in (1, 4, 25):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        for sp in (ELECTRON, ION):
+            pc.compare_particles(a.download(sp), b.download(sp), fields=("x", "ux", "uy", "uz"))
+            assert a.last_leavers(sp) == b.last_leavers(sp)
+        pc.compare_fields(a.fields(), b.fields())
+        _same_energies(a, b)
+    assert a.count(ION) == nx * 40 and a.count(ELECTRON) == nx * 60
