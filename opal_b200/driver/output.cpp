@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <charconv>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -15,13 +16,12 @@ namespace opal_driver {
 // ---- Rust float formatting -------------------------------------------------------------------
 namespace {
 
-// shortest decimal digits that round-trip: digits (no dot) and the decimal exponent of the first digit
+// shortest decimal digits that round-trip (std::to_chars, the same Ryu-style shortest representation Rust prints):
+// digits (no dot) and the decimal exponent of the first digit
 void shortest_digits(double v, std::string* digits, int* exp10) {
-    char buf[40];
-    for (int p = 1; p <= 17; p++) {
-        std::snprintf(buf, sizeof buf, "%.*e", p - 1, v);
-        if (std::strtod(buf, nullptr) == v || p == 17) break;
-    }
+    char buf[64];
+    const auto r = std::to_chars(buf, buf + sizeof buf, v, std::chars_format::scientific);
+    *r.ptr = 0;
     const char* e = std::strchr(buf, 'e');
     *exp10 = std::atoi(e + 1);
     digits->clear();
