@@ -368,7 +368,14 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
             for (int j = std::max(0, i - R); j <= std::min(ncell - 1, i + R); j++) m = std::max<long long>(m, cnt[j]);
             wide[i] = (long long)std::ceil((double)m * c->regrid_boost[sp]);
         }
-        demand.swap(wide);
+        // the old and the new buckets coexist during the copy: widen only when that fits comfortably
+        long long wide_slots = 0;
+        for (int i = 0; i < ncell; i++) wide_slots += bucket_cap(c, wide[i], false);
+        size_t free_b = 0, total_b = 0;
+        cudaMemGetInfo(&free_b, &total_b);
+        const double need = (double)wide_slots * (B.full ? NF_FULL : NF_LEAN) * sizeof(double);
+        if (need < 0.8 * (double)free_b) demand.swap(wide);
+        else { c->regrid_radius[sp] = 0; c->regrid_boost[sp] = 1.0; }
     }
     Buckets old = B;
     B = Buckets();
