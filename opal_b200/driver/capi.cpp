@@ -4,6 +4,7 @@
 #include <string>
 
 #include "config.h"
+#include "grid_design.h"
 #include "loader.h"
 #include "output.h"
 
@@ -105,6 +106,48 @@ int opal_drv_write_fits(const char* path, int dim, const long* bins, const doubl
 void opal_drv_rng_stream(unsigned long long seed, long n, double* out) {
     Xoshiro256StarStar r(seed);
     for (long i = 0; i < n; i++) out[i] = r.gen_f64();
+}
+
+// GridDesign::{unbalanced, balanced} with ne(x) given as an expression of x; writes numtasks cell counts and offsets
+int opal_drv_grid_design(int balanced, int numtasks, long size, double xmin, double dx, long min_subsize, const char* ne_expr, long* nx_out,
+                         double* offset_out) {
+    try {
+        GridDesign d;
+        if (balanced) {
+            Context ctx;
+            const Expr e = Expr::parse(ne_expr);
+            const char* names[1] = {"x"};
+            d = GridDesign::balanced(numtasks, (size_t)size, xmin, dx, (size_t)min_subsize, [&](double x) { return e.eval(ctx, names, &x, 1); });
+        } else {
+            d = GridDesign::unbalanced(numtasks, (size_t)size, xmin, dx, (size_t)min_subsize);
+        }
+        for (int i = 0; i < numtasks; i++) { nx_out[i] = (long)d.nx[(size_t)i]; offset_out[i] = d.offset[(size_t)i]; }
+        return 0;
+    } catch (...) {
+        return 1;
+    }
+}
+
+// Population::new on `ncells` cells from the deck's section (ne/ni field name given); returns the particle count, fills up to cap entries
+long opal_drv_load(const char* yaml, const char* section, const char* density_field, long npc, long ncells, double slab_xmin, double dx,
+                   unsigned long long seed, int with_tau, long cap, long long* cell, double* x, double* ux, double* uy, double* uz, double* w, double* tau) {
+    try {
+        Config c = Config::from_string(yaml);
+        c.with_context("constants");
+        Xoshiro256StarStar rng(seed);
+        const ParticleArrays p = load_population((size_t)npc, c.func(section, density_field, "x"), c.func3(section, "ux", "x", "urand", "nrand"),
+                                                 c.func3(section, "uy", "x", "urand", "nrand"), c.func3(section, "uz", "x", "urand", "nrand"),
+                                                 ncells, slab_xmin, dx, rng, with_tau != 0);
+        const long n = (long)p.size();
+        for (long i = 0; i < n && i < cap; i++) {
+            cell[i] = p.cell[(size_t)i]; x[i] = p.x[(size_t)i]; ux[i] = p.ux[(size_t)i]; uy[i] = p.uy[(size_t)i]; uz[i] = p.uz[(size_t)i];
+            w[i] = p.weight[(size_t)i];
+            if (with_tau) tau[i] = p.tau[(size_t)i];
+        }
+        return n;
+    } catch (...) {
+        return -1;
+    }
 }
 
 }  // extern "C"

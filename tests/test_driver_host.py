@@ -279,3 +279,64 @@ def test_rng_stream_matches_the_oracles_restatement(host, oracle):
     oracle.cdll.opal_ref_rng_stream.argtypes = [C.c_uint64, C.c_int64, C.c_void_p]
     oracle.cdll.opal_ref_rng_stream(7, 64, b.ctypes.data)
     assert np.array_equal(a, b) and 0.0 <= a.min() and a.max() < 1.0
+
+
+def test_yaml_subset_features(host):
+    y = ("# a comment line\r\n---\r\ncontrol:   # trailing comment\r\n  dx: 2.5   # metres\r\n  label: \"x:px # not a comment\"\r\n"
+         "  outs: [x,\r\n         px:py,   # inside a flow sequence\r\n         \"energy:(log;energy)\"]\r\n"
+         "  lit: |\r\n    1 +\r\n    2\r\n  fold: >-\r\n    3 *\r\n    4\r\n  hex: 0x10\r\n  neg: -7\r\n  sci: 1e3\r\n  yes: true\r\n...\r\n")
+    assert read(host, y, "control", "dx")[1] == 2.5
+    assert read(host, y, "control", "label", kind=3)[2] == "x:px # not a comment"
+    assert read(host, y, "control", "outs", kind=3)[2].split("\n") == ["x", "px:py", "energy:(log;energy)"]
+    assert read(host, y, "control", "lit")[1] == 3.0                 # "1 +\n2\n" evaluates as an expression
+    assert read(host, y, "control", "fold")[1] == 12.0
+    assert read(host, y, "control", "hex", kind=1)[1] == 16.0 and read(host, y, "control", "neg")[1] == -7.0
+    assert read(host, y, "control", "neg", kind=1)[0] == 4           # usize::try_from(-7) fails (setup.rs:312-318)
+    assert read(host, y, "control", "sci")[1] == 1000.0 and read(host, y, "control", "sci", kind=1)[0] == 4   # "1e3" is a Real, not an Integer
+    assert read(host, y, "control", "yes", kind=2)[1] == 1.0
+    assert read(host, "not yaml at all", "control", "dx")[0] == 1    # MissingFile, as setup.rs:96-99 maps load errors
+
+
+def test_cpp_grid_design_equals_the_python_mirror(host):
+    from opal_b200.slabs import GridDesign
+    host.opal_drv_grid_design.argtypes = [C.c_int, C.c_int, C.c_long, C.c_double, C.c_double, C.c_long, C.c_char_p, C.c_void_p, C.c_void_p]
+    cases = [(False, 4, 1003, "1"), (False, 8, 20, "1"), (True, 3, 600, "1 + 0*x"), (True, 4, 2000, "step(x, 0, 2.5e-6) + 0.01"),
+             (True, 2, 64, "exp(-x*x*1.0e10)"), (True, 1, 40, "1")]
+    for balanced, np_, size, ne in cases:
+        nx, off = (C.c_long * np_)(), (C.c_double * np_)()
+        expr = ne.replace("step(x, 0, 2.5e-6)", "max(0, min(1, floor(1 + x*1.0e9) * floor(1 + (2.5e-6 - x)*1.0e9)))")   # meval has no step(); opal adds it in Config
+        xmin, dx = -1.0e-6, 5.0e-9
+        assert host.opal_drv_grid_design(int(balanced), np_, size, xmin, dx, 8, expr.encode(), nx, off) == 0
+        import math
+        env = {"x": 0.0, "exp": math.exp, "floor": math.floor, "max": max, "min": min}
+        f = lambda x: eval(expr, {"__builtins__": {}}, dict(env, x=x))
+        want = GridDesign.balanced(np_, size, xmin, dx, f) if balanced else GridDesign.unbalanced(np_, size, xmin, dx)
+        assert list(nx) == list(want.nx), (balanced, np_, size, ne)
+        assert list(off) == [float(v) for v in want.offset]
+
+
+def test_loader_draw_order_and_moments(host):
+    """Population::new (mod.rs:172-203): npc particles in every cell whose density is positive, weight = ne dx / npc,
+    u from the deck's expressions of (x, urand, nrand); statistics of the draws."""
+    host.opal_drv_load.restype = C.c_long
+    host.opal_drv_load.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_long, C.c_long, C.c_double, C.c_double, C.c_ulonglong, C.c_int, C.c_long] + [C.c_void_p] * 7
+    y = ("electrons:\n ne: 3.0 * step(x, 1000, 4000)\n ux: 0.5 * nrand\n uy: urand\n uz: x / 1000\n")
+    cap = 200000
+    cell = np.zeros(cap, dtype=np.int64)
+    x, ux, uy, uz, w, tau = (np.zeros(cap) for _ in range(6))
+    n = host.opal_drv_load(y.encode(), b"electrons", b"ne", 400, 100, 0.0, 100.0, 5, 1, cap, *(a.ctypes.data for a in (cell, x, ux, uy, uz, w, tau)))
+    # cell centres 50, 150, ...: density positive where 1000 <= centre < 4000 -> cells 10..39
+    assert n == 30 * 400
+    cell, x, ux, uy, uz, w, tau = (a[:n] for a in (cell, x, ux, uy, uz, w, tau))
+    assert np.array_equal(np.unique(cell), np.arange(10, 40)) and np.all(np.bincount(cell)[10:40] == 400)
+    assert np.all(w == 3.0 * 100.0 / 400) and np.all((x >= 0) & (x < 1))
+    assert np.allclose(uz, (cell + x) * 100.0 / 1000, rtol=1e-14)                 # real_x = xmin + (c + x) dx
+    assert abs(ux.mean()) < 4 * 0.5 / np.sqrt(n) and abs(ux.std() / 0.5 - 1) < 0.03
+    assert abs(uy.mean() - 0.5) < 4 / np.sqrt(12 * n) and uy.min() >= 0 and uy.max() < 1
+    assert abs(tau.mean() - 1.0) < 0.05 and tau.min() > 0                          # Exp1 optical depths
+    # same seed -> same stream; the rank id seeds it (main.rs:53)
+    keep = (np.zeros(cap, dtype=np.int64),) + tuple(np.zeros(cap) for _ in range(6))
+    n2 = host.opal_drv_load(y.encode(), b"electrons", b"ne", 400, 100, 0.0, 100.0, 5, 1, cap, *(a.ctypes.data for a in keep))
+    assert n2 == n and np.array_equal(keep[2][:n], ux) and np.array_equal(keep[6][:n], tau)
+    n3 = host.opal_drv_load(y.encode(), b"electrons", b"ne", 400, 100, 0.0, 100.0, 6, 1, cap, *(a.ctypes.data for a in keep))
+    assert n3 == n and not np.array_equal(keep[2][:n], ux)
