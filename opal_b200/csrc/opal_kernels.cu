@@ -760,6 +760,17 @@ __global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_l
 // registers: one shuffle reduction + <= 15 atomics per cell.  Edge cells route through the slab
 // boundary (mod.rs:290-373): periodic self-neighbour => the strips of the opposite edge; remote
 // neighbour => the edge strips are copied to the outbox here and arrive through the inbox path.
+#ifndef OPAL_PULL_SUB
+#define OPAL_PULL_SUB 16
+#endif
+#if OPAL_PUSH_HOLES == 1 && OPAL_PULL_SUB != 32
+#error "OPAL_PUSH_HOLES=1 needs OPAL_PULL_SUB=32"
+#endif
+template <int W> __device__ __forceinline__ double group_sum(double v, unsigned mask) {
+#pragma unroll
+    for (int o = W / 2; o; o >>= 1) v += __shfl_xor_sync(mask, v, o, W);
+    return v;
+}
 #ifndef OPAL_PULL_MINBLK
 #define OPAL_PULL_MINBLK 4
 #endif
@@ -768,11 +779,16 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
                                                opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
                                                StatusDev* __restrict__ st, const int* __restrict__ holes, int* __restrict__ hcount) {
     if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
-    const int lane = threadIdx.x & 31;
-    const int warps_total = gridDim.x * 8;
+    // OPAL_PULL_SUB lanes serve one cell (32: a warp per cell; 16: two cells per warp -- twice the cells in flight per SM
+    // for a kernel that waits on memory: ~48 arrivals per cell are three 16-lane trips instead of two 32-lane ones)
+    constexpr int SUB = OPAL_PULL_SUB;
+    constexpr int CPW = 32 / SUB;                                   // cells per warp
+    const int lane = threadIdx.x & (SUB - 1);                      // lane within the cell's group
+    const unsigned gmask = SUB == 32 ? FULLMASK : (((1u << SUB) - 1u) << ((threadIdx.x & 31) & ~(SUB - 1)));
+    const int groups_total = gridDim.x * 8 * CPW;
     const int MC = sp.cell_mover_cap;
     const int nc = b.ncell;
-    for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < nc; c += warps_total) {
+    for (int c = (blockIdx.x * 8 + (threadIdx.x >> 5)) * CPW + ((threadIdx.x & 31) / SUB); c < nc; c += groups_total) {
         // source strips: right-movers of the left neighbour cell, left-movers of the right neighbour cell
         int src_l = c - 1, src_r = c + 1;
         if (src_l < 0) src_l = sp.route_left == 1 ? nc - 1 : -1;
@@ -786,8 +802,8 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             if (sp.route_left == 2 && n) {
                 int o = 0;
                 if (lane == 0) o = atomicAdd(&st->n_out[0], n);
-                o = __shfl_sync(FULLMASK, o, 0);
-                for (int i = lane; i < n; i += 32) {
+                o = __shfl_sync(gmask, o, 0, SUB);
+                for (int i = lane; i < n; i += SUB) {
                     const StripRec r = strips[(long long)0 * MC + i];
                     if (o + i < sp.out_cap) {
                         opal_migrant m;
@@ -804,8 +820,8 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
             if (sp.route_right == 2 && n) {
                 int o = 0;
                 if (lane == 0) o = atomicAdd(&st->n_out[1], n);
-                o = __shfl_sync(FULLMASK, o, 0);
-                for (int i = lane; i < n; i += 32) {
+                o = __shfl_sync(gmask, o, 0, SUB);
+                for (int i = lane; i < n; i += SUB) {
                     const StripRec r = strips[((long long)c * 2 + 1) * MC + i];
                     if (o + i < sp.out_cap) {
                         opal_migrant m;
@@ -832,7 +848,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
         double acc[15];
 #pragma unroll
         for (int k = 0; k < 15; k++) acc[k] = 0.0;
-        for (int i0 = 0; i0 < n_in; i0 += 32) {
+        for (int i0 = 0; i0 < n_in; i0 += SUB) {
             const int i = i0 + lane;
             if (i < n_in) {
                 const StripRec r = i < n_from_l ? strips[((long long)src_l * 2 + 1) * MC + i]
@@ -888,7 +904,7 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
         const double qsp = sp.species == OPAL_ION ? b.z_star * OPAL_E : OPAL_QE;
         const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
 #pragma unroll
-        for (int k = 0; k < 15; k++) acc[k] = warp_sum(acc[k]) * (k < 5 ? kx : (k < 11 ? ky : kr));
+        for (int k = 0; k < 15; k++) acc[k] = group_sum<SUB>(acc[k], gmask) * (k < 5 ? kx : (k < 11 ? ky : kr));
         double mine = 0.0;
         double* dst = nullptr;
 #pragma unroll
@@ -1765,7 +1781,7 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
 static void l_pull(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, const StripRec* strips,
                    const int* scount, opal_migrant* out_l, opal_migrant* out_r, opal_migrant* overflow, StatusDev* st) {
 #ifdef OPAL_FAST
-    long long blocks = ((long long)b.ncell + 7) / 8;
+    long long blocks = ((long long)b.ncell + 8 * (32 / OPAL_PULL_SUB) - 1) / (8 * (32 / OPAL_PULL_SUB));
     // the strip counters are followed by the per-cell hole counts and hole lists (host: ensure_cell_movers)
     int* sc = const_cast<int*>(scount);
     k_pull<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(g, b, sp, strips, scount, out_l, out_r, overflow, st, sc + 3ll * b.ncell, sc + 2ll * b.ncell);
