@@ -905,16 +905,13 @@ __global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, Bucke
         const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
 #pragma unroll
         for (int k = 0; k < 15; k++) acc[k] = group_sum<SUB>(acc[k], gmask) * (k < 5 ? kx : (k < 11 ? ky : kr));
-        double mine = 0.0;
-        double* dst = nullptr;
 #pragma unroll
         for (int k = 0; k < 15; k++) {
-            if (lane == k) {
-                mine = acc[k];
-                dst = k < 5 ? g.jx + idx - 2 + k : (k < 8 ? g.jy + idx - 1 + (k - 5) : (k < 11 ? g.jz + idx - 1 + (k - 8) : g.rho + idx - 2 + (k - 11)));
+            if (lane == (k % SUB) && acc[k] != 0.0) {
+                double* const dst = k < 5 ? g.jx + idx - 2 + k : (k < 8 ? g.jy + idx - 1 + (k - 5) : (k < 11 ? g.jz + idx - 1 + (k - 8) : g.rho + idx - 2 + (k - 11)));
+                atomicAdd(dst, acc[k]);
             }
         }
-        if (dst && mine != 0.0) atomicAdd(dst, mine);
     }
 }
 #endif  // OPAL_FAST
