@@ -238,6 +238,16 @@ opal_status OPAL_FN(qed_rate)(int64_t n, const double* chi, const double* gamma,
 /* photon_emission::sample (:129) -> out[3n] = (omega/mc^2, theta, phi) */
 opal_status OPAL_FN(qed_sample)(int64_t n, const double* chi, const double* gamma, const double* r1,
                                 const double* r2, const double* r3, int classical, double* out3);
+/* airy_ai_for_positive (qed/special_functions/airy.rs:19): ai[i] = Ai(x[i]); defined[i] = 0 where the
+   reference returns None (x < 0, x >= 50 or NaN), and ai[i] = 0 there */
+opal_status OPAL_FN(qed_airy)(int64_t n, const double* x, double* ai, int* defined);
+/* photon_absorption::scaled_cross_section (qed/photon_absorption.rs:17) and
+   stimulated_emission::scaled_cross_section (qed/stimulated_emission.rs:17) for n photon/electron pairs:
+   k4, p4 = four-momenta / mc, 4 doubles per pair; defined[i] bit 0: absorption is Some, bit 1: stimulated
+   emission is Some (the sigma of a None is written as 0) */
+opal_status OPAL_FN(qed_pair_cross_sections)(int64_t n, const double* k4, const double* p4,
+                                             const double* chi_gamma, const double* chi_e,
+                                             double* sigma_abs, double* sigma_st, int* defined);
 /* YeeGrid::fields_at (yee.rs:499) for n (cell, xi) pairs -> out[6n] = E[3],B[3] */
 opal_status OPAL_FN(fields_at)(opal_ctx*, int64_t n, const int64_t* cell, const double* xi, double* out6);
 

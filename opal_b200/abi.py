@@ -72,6 +72,8 @@ SIGNATURES = {
     "particles_generate": [_vp, _int, _i64, _f64, _vp, _vp, _int, _i64, _u64],
     "qed_rate": [_i64, _vp, _vp, _vp],
     "qed_sample": [_i64, _vp, _vp, _vp, _vp, _vp, _int, _vp],
+    "qed_airy": [_i64, _vp, _vp, _vp],
+    "qed_pair_cross_sections": [_i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "fields_at": [_vp, _i64, _vp, _vp, _vp],
 }
 
@@ -123,6 +125,26 @@ class OpalABI:
         if st:
             raise OpalError(st, "qed_sample")
         return out
+
+    def airy(self, x):
+        """(Ai(x), defined) -- airy_ai_for_positive (airy.rs:19); defined is False where the reference gives None"""
+        x = _f64arr(np.atleast_1d(x))
+        ai, ok = np.empty_like(x), np.empty(x.size, dtype=np.int32)
+        st = self.qed_airy(x.size, _ptr(x), _ptr(ai), _ptr(ok))
+        if st:
+            raise OpalError(st, "qed_airy")
+        return ai, ok.astype(bool)
+
+    def pair_cross_sections(self, k4, p4, chi_gamma, chi_e):
+        """(sigma_abs, sigma_st, abs_defined, st_defined) for n pairs (photon_absorption.rs:17, stimulated_emission.rs:17)"""
+        k4, p4 = _f64arr(np.atleast_2d(k4)), _f64arr(np.atleast_2d(p4))
+        n = k4.shape[0]
+        chi_gamma, chi_e = (_f64arr(np.broadcast_to(np.atleast_1d(v), (n,))) for v in (chi_gamma, chi_e))
+        sa, ss, ok = np.empty(n), np.empty(n), np.empty(n, dtype=np.int32)
+        st = self.qed_pair_cross_sections(n, _ptr(k4), _ptr(p4), _ptr(chi_gamma), _ptr(chi_e), _ptr(sa), _ptr(ss), _ptr(ok))
+        if st:
+            raise OpalError(st, "qed_pair_cross_sections")
+        return sa, ss, (ok & 1).astype(bool), (ok & 2).astype(bool)
 
 
 # opal_quantity (particle/mod.rs:455-470) and their units (mod.rs:475-486)

@@ -415,6 +415,55 @@ void qed_sample(double chi, double gamma, double rand1, double rand2, double ran
     out[0] = gamma * u / (1.0 + u); out[1] = std::acos(ct); out[2] = 2.0 * PI * rand3;
 }
 
+// ---- Airy Ai for x >= 0 (qed/special_functions/airy.rs:19-69, Series::evaluate_up_to mod.rs:29-35) -----
+// Pinned by the reference's known answers Ai(0), Ai(2), Ai(17), Ai(20) at 1e-12 and None beyond 50 (airy.rs:77-112).
+#include "airy_tables.h"
+constexpr double CLASSICAL_ELECTRON_RADIUS = 2.817940e-15;   // constants.rs:28
+constexpr double AIRY_SCALE = 0.262183997088323;             // the 15-digit literal of airy.rs:40
+inline double powi(double a, int b) {     // f64::powi = llvm.powi = compiler-rt's __powidf2: square-and-multiply from the low bit
+    double r = 1.0;
+    for (;;) { if (b & 1) r *= a; b /= 2; if (b == 0) break; a *= a; }
+    return r;
+}
+template <int N>
+double airy_quadrature(double x, const double (&node)[N], const double (&weight)[N]) {   // airy.rs:39-45
+    double s = 2.0 * std::pow(x, 1.5) / 3.0;
+    double a = AIRY_SCALE * std::pow(s, -1.0 / 6.0) * std::exp(-s);
+    double integral = 0.0;
+    for (int i = 0; i < N; i++) integral += weight[i] * std::pow(2.0 + node[i] / s, -1.0 / 6.0);
+    return a * integral;
+}
+bool airy_ai_for_positive(double x, double* ai) {
+    if (x < 0.0) return false;
+    if (x < 1.0) {
+        double sum = 0.0;
+        for (int i = 0; i < AIRY_SERIES_TERMS; i++) sum += AIRY_SERIES_A[i] * powi(x, AIRY_SERIES_N[i]);
+        *ai = sum;
+    } else if (x < 2.0) *ai = airy_quadrature(x, AIRY_GL40_X, AIRY_GL40_W);
+    else if (x < 10.0) *ai = airy_quadrature(x, AIRY_GL16_X, AIRY_GL16_W);
+    else if (x < 50.0) *ai = airy_quadrature(x, AIRY_GL4_X, AIRY_GL4_W);
+    else return false;       // Ai(50) < 4.5e-104: None
+    return true;             // (a NaN argument falls through every comparison to None, as in the reference)
+}
+
+// ---- one-photon absorption and stimulated emission (qed/photon_absorption.rs:17-35, stimulated_emission.rs:17-37) ----
+// k, p: four-momenta / mc of the photon and the electron.  sign = +1 absorption, -1 stimulated emission.
+bool pair_cross_section(int sign, const double k[4], const double p[4], double chi_gamma, double chi_e, double* sigma) {
+    if (sign < 0 && (chi_gamma >= chi_e || k[0] >= p[0])) return false;     // stimulated_emission.rs:19
+    if (chi_e <= 0.0 || chi_gamma <= 0.0) return false;
+    double den = chi_e * (sign > 0 ? chi_e + chi_gamma : chi_e - chi_gamma);
+    double g = 0.5 + 0.25 * (chi_gamma * chi_gamma) / den;
+    double z = std::pow(chi_gamma / den, 2.0 / 3.0);
+    double k_p = k[0] * p[0] - k[1] * p[1] - k[2] * p[2] - k[3] * p[3];
+    double zbar = 2.0 * z * chi_e * k_p / chi_gamma;
+    double zbar_z = 2.0 * p[0] * k_p / k[0];
+    double ai;
+    if (!airy_ai_for_positive(zbar, &ai)) return false;
+    double r = 2.0 * PI * CLASSICAL_ELECTRON_RADIUS;
+    *sigma = (r * r) * chi_e * z * (4.0 * g * zbar_z - 1.0) * ai / (ALPHA_FINE * chi_gamma * k[0] * p[0]);
+    return true;
+}
+
 // ---- particle structs: reference layouts (electron.rs:14-27, ion.rs:14-26, photon.rs:16-32) ---
 struct Electron {
     int64_t cell; double prev_x, x, y, z, weight, gamma; Vec3 u; double chi, tau, work; bool flag;
@@ -1341,6 +1390,19 @@ opal_status opal_ref_qed_sample(int64_t n, const double* chi, const double* gamm
     }
     bool bad = g_chi_range_error; g_chi_range_error = false;
     return bad ? OPAL_ECHI_RANGE : OPAL_OK;
+}
+opal_status opal_ref_qed_airy(int64_t n, const double* x, double* ai, int* defined) {
+    for (int64_t i = 0; i < n; i++) { ai[i] = 0.0; defined[i] = airy_ai_for_positive(x[i], ai + i) ? 1 : 0; }
+    return OPAL_OK;
+}
+opal_status opal_ref_qed_pair_cross_sections(int64_t n, const double* k4, const double* p4, const double* chi_gamma, const double* chi_e,
+                                             double* sigma_abs, double* sigma_st, int* defined) {
+    for (int64_t i = 0; i < n; i++) {
+        sigma_abs[i] = sigma_st[i] = 0.0;
+        defined[i] = (pair_cross_section(+1, k4 + 4 * i, p4 + 4 * i, chi_gamma[i], chi_e[i], sigma_abs + i) ? 1 : 0)
+                   | (pair_cross_section(-1, k4 + 4 * i, p4 + 4 * i, chi_gamma[i], chi_e[i], sigma_st + i) ? 2 : 0);
+    }
+    return OPAL_OK;
 }
 opal_status opal_ref_fields_at(opal_ctx* g, int64_t n, const int64_t* cell, const double* xi, double* out6) {
     CHECK_CTX(g);

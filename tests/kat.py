@@ -144,3 +144,37 @@ def rate_kats(abi):
     got = abi.rate(chi, np.full_like(chi, 1000.0))
     want = np.array([v for _, v in RATE_KATS])
     return got, want
+
+
+# qed/special_functions/airy.rs:77-112: Ai at 0, 2, 17, 20 to 1e-12 relative; Ai(200) is None
+AIRY_KATS = ((0.0, 0.3550280538878172), (2.0, 0.03492413042327438), (17.0, 7.05019729838861e-22), (20.0, 1.69167286867e-27))
+
+
+def airy_kats(abi):
+    x = np.array([v for v, _ in AIRY_KATS] + [200.0, -1.0, 50.0, float("nan")])
+    ai, ok = abi.airy(x)
+    rel = [abs(ai[i] - t) / t for i, (_, t) in enumerate(AIRY_KATS)]
+    return rel, ok
+
+
+def pair_cases(seed=7, n=4000):
+    """photon / electron pairs spanning the branches of the two cross sections: both chi orderings, k0 above and below
+    gamma, zero chi, and zbar in each of the Airy function's five ranges"""
+    rng = np.random.default_rng(seed)
+    gamma = 10.0 ** rng.uniform(0.5, 4.0, n)
+    u = np.sqrt(gamma ** 2 - 1.0)
+    ct = rng.uniform(-1.0, 1.0, n)
+    ph = rng.uniform(0.0, 2.0 * np.pi, n)
+    st = np.sqrt(1.0 - ct ** 2)
+    p4 = np.stack([gamma, u * ct, u * st * np.cos(ph), u * st * np.sin(ph)], axis=1)
+    k0 = gamma * 10.0 ** rng.uniform(-6.0, 0.3, n)
+    # nearly collinear with the electron (k.p small, zbar in the series range) or at a wide angle (zbar large)
+    dth = 10.0 ** rng.uniform(-5.0, 0.5, n)
+    ct2 = np.cos(np.arccos(ct) + dth)
+    st2 = np.sqrt(np.maximum(0.0, 1.0 - ct2 ** 2))
+    k4 = np.stack([k0, k0 * ct2, k0 * st2 * np.cos(ph), k0 * st2 * np.sin(ph)], axis=1)
+    chi_e = 10.0 ** rng.uniform(-3.0, 1.0, n)
+    chi_g = chi_e * 10.0 ** rng.uniform(-4.0, 0.5, n)
+    chi_e[:8] = 0.0
+    chi_g[8:16] = 0.0
+    return k4, p4, chi_g, chi_e

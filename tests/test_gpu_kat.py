@@ -65,3 +65,25 @@ def test_sample_matches_oracle(gpu, oracle):
         assert np.max(rel[:, 0]) < 1.0e-5
         assert np.max(np.abs(a[:, 1] - b[:, 1])) < 1.0e-5 * np.max(np.abs(b[:, 1]))
         assert np.max(rel[:, 2]) < 1.0e-14
+
+
+def test_airy_kats(gpu, oracle):                 # qed/special_functions/airy.rs:77-112
+    rel, ok = kat.airy_kats(gpu)
+    assert max(rel) < 1.0e-12, rel
+    assert list(ok) == [True, True, True, True, False, False, False, False]
+    x = np.concatenate([np.linspace(0.0, 2.0, 4001), np.linspace(2.0, 49.99, 6000), [-0.5, 50.0, 1e300]])
+    a, oka = gpu.airy(x)
+    b, okb = oracle.airy(x)
+    assert (oka == okb).all()
+    assert np.max(np.abs(a[oka] - b[oka]) / b[oka]) < 1.0e-13
+
+
+def test_pair_cross_sections_match_oracle(gpu, oracle):
+    k4, p4, cg, ce = kat.pair_cases(n=20000)
+    ga, gs, goa, gos = gpu.pair_cross_sections(k4, p4, cg, ce)
+    ra, rs, roa, ros = oracle.pair_cross_sections(k4, p4, cg, ce)
+    assert (goa == roa).all() and (gos == ros).all()
+    assert roa.sum() > 2000 and ros.sum() > 2000
+    for a, b, ok in ((ga, ra, roa), (gs, rs, ros)):
+        assert (a[~ok] == 0.0).all()
+        assert np.max(np.abs(a[ok] - b[ok]) / np.abs(b[ok])) < 1.0e-12

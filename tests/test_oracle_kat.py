@@ -97,3 +97,45 @@ def test_vec3_rotation(oracle_cdll):             # vec3.rs:160-169: two pi/2 rot
     oracle_cdll.opal_ref_vec3_rotate_around(v, zaxis, math.pi / 2.0, o1)       # x -> y
     oracle_cdll.opal_ref_vec3_rotate_around(o1, xaxis, math.pi / 2.0, o2)      # y -> z
     assert abs(o2[0]) < 1.0e-10 and abs(o2[1]) < 1.0e-10 and abs(o2[2] - 1.0) < 1.0e-10
+
+
+def test_airy_kats(oracle):                      # qed/special_functions/airy.rs:77-112
+    rel, ok = kat.airy_kats(oracle)
+    assert max(rel) < 1.0e-12, rel
+    assert list(ok) == [True, True, True, True, False, False, False, False]      # None: x = 200, x < 0, x >= 50, NaN
+
+
+def test_airy_against_an_independent_evaluation(oracle):
+    """the restated algorithm (series below 1, 40/16/4-node Gauss-Laguerre above) against scipy's Ai over [0, 50)"""
+    from scipy.special import airy
+    x = np.concatenate([np.linspace(0.0, 2.0, 801), np.linspace(2.0, 49.99, 1500)])
+    ai, ok = oracle.airy(x)
+    assert ok.all()
+    assert np.max(np.abs(ai - airy(x)[0]) / airy(x)[0]) < 2.0e-12
+
+
+def test_pair_cross_sections_branches(oracle):
+    """photon_absorption.rs:17-35 / stimulated_emission.rs:17-37 against a direct numpy statement of the formulas"""
+    from scipy.special import airy
+    k4, p4, cg, ce = kat.pair_cases()
+    sa, ss, oka, oks = oracle.pair_cross_sections(k4, p4, cg, ce)
+    # same association as the reference: k.p cancels to ~1e-8 of k0 p0 for these pairs and Ai amplifies what is left
+    kp = k4[:, 0] * p4[:, 0] - k4[:, 1] * p4[:, 1] - k4[:, 2] * p4[:, 2] - k4[:, 3] * p4[:, 3]
+    r2 = (2.0 * np.pi * 2.817940e-15) ** 2
+    seen = set()
+    for sign, sig, ok in ((+1, sa, oka), (-1, ss, oks)):
+        with np.errstate(all="ignore"):
+            den = ce * (ce + sign * cg)
+            z = np.abs(cg / den) ** (2.0 / 3.0)
+            zbar = 2.0 * z * ce * kp / cg
+            expect_ok = (ce > 0) & (cg > 0) & (zbar >= 0) & (zbar < 50.0)
+            if sign < 0:
+                expect_ok &= (cg < ce) & (k4[:, 0] < p4[:, 0])
+            g = 0.5 + 0.25 * cg ** 2 / den
+            val = r2 * ce * z * (4.0 * g * (2.0 * p4[:, 0] * kp / k4[:, 0]) - 1.0) * airy(zbar)[0] / (7.29735257e-3 * cg * k4[:, 0] * p4[:, 0])
+        assert (ok == expect_ok).all()
+        assert (sig[~ok] == 0.0).all()
+        assert np.max(np.abs(sig[ok] - val[ok]) / np.abs(val[ok])) < 1.0e-11
+        seen |= set(np.digitize(zbar[ok], [1.0, 2.0, 10.0]))
+        assert ok.sum() > 500 and (~ok).sum() > 100
+    assert seen == {0, 1, 2, 3}                   # every range of the Airy evaluation was exercised

@@ -10,6 +10,6 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 for v in "$@"; do
   tag=${v%%:*}; flags=${v#*:}
   ( $NVCC $ARCH -ccbin /usr/bin/g++ -std=c++17 -O3 -lineinfo -Xcompiler -fPIC -DOPAL_KNS=fast -DOPAL_FAST=1 --fmad=true $flags -c $C/opal_kernels.cu -o build/kf_$tag.o &&
-    $NVCC $ARCH -ccbin /usr/bin/g++ -shared -o build/libopal_$tag.so build/kf_$tag.o $C/kernels_strict.o $C/hgram.o $C/host.o -cudart static -ldl && echo built $tag ) &
+    $NVCC $ARCH -ccbin /usr/bin/g++ -shared -o build/libopal_$tag.so build/kf_$tag.o $C/kernels_strict.o $C/hgram.o $C/absorb.o $C/host.o -cudart static -ldl && echo built $tag ) &
 done
 wait
