@@ -45,7 +45,8 @@ typedef enum {
     OPAL_EASSERT_CFL = 5,   /* assert!(dxi < 1.0): electron.rs:313, ion.rs:199, photon.rs:164      */
     OPAL_EASSERT_INDEX = 6, /* index asserts: yee.rs:501-502, yee.rs:578-579                        */
     OPAL_ECHI_RANGE = 7,    /* unimplemented!() for chi beyond the table: photon_emission.rs:144   */
-    OPAL_ECAPACITY = 8      /* a fixed-capacity exchange buffer overflowed                         */
+    OPAL_ECAPACITY = 8,     /* a fixed-capacity exchange buffer overflowed                         */
+    OPAL_EASSERT_PROB = 9   /* assert!(partial_prob >= 0.0): photon.rs:325, photon.rs:336          */
 } opal_status;
 
 /* grid/mod.rs:22-28 */
@@ -63,6 +64,7 @@ enum {
     OPAL_FLAG_NO_RADIATION_REACTION = 1u << 0,
     OPAL_FLAG_NO_BEAMING            = 1u << 1,
     OPAL_FLAG_IMMOBILE_PHOTONS      = 1u << 2,
+    OPAL_FLAG_NO_STIMULATED_EMISSION = 1u << 3,
     /* Charged species keep only (x, u, weight) per particle; prev_x, gamma and velocity are
        recomputed in registers by the fused push+deposit kernel and work/chi/tau/y/z (which are
        unobservable with QED and such outputs off) are not maintained.  Only opal_run_steps()
@@ -90,7 +92,7 @@ typedef struct {
     double chi, tau, work;
     double y, z;
     double birth_time;   /* photons only                                                       */
-    double pad[2];
+    double pad[2];       /* ions: gamma_m1 in pad[0]; photons: tau_abs, tau_st (photon.rs:28-29)  */
 } opal_migrant;          /* 128 bytes */
 
 /* ---- lifetime ------------------------------------------------------------------------- */
@@ -154,6 +156,18 @@ opal_status OPAL_FN(migrants_give)(opal_ctx*, int species, int side, int64_t n, 
    NULL pointer == None for the three optional filters.                                         */
 opal_status OPAL_FN(emit_radiation)(opal_ctx*, double t, const double* min_energy_mev,
                                     const double* max_angle, const double* max_formation_length);
+
+/* absorb (particle/interactions.rs:145) incl. Photon::interacts_with (photon.rs:312) and
+   Electron::kick (electron.rs:256): every photon walks the electrons of its cell, spending its two optical
+   depths; an absorbed photon is deleted and its momentum given to the electron, a stimulated emission
+   adds a copy of the photon (weight of the electron) and takes its momentum from the electron.
+   NULL == None for the two optional limits.  Call it where main.rs:246 does: after both advances.
+   Reference behaviour kept: the electrons of the slab's LAST occupied cell never interact
+   (interactions.rs:216-222 needs a following electron to close the range).                    */
+opal_status OPAL_FN(absorb)(opal_ctx*, double t, const double* max_displacement, const double* stop_time);
+/* Photon::tau_abs / tau_st (photon.rs:28-29) in the order particles_download(OPAL_PHOTON) uses;
+   set != 0 writes them (n must equal the photon count), set == 0 reads them                     */
+opal_status OPAL_FN(photon_pair_depths)(opal_ctx*, int set, int64_t n, double* tau_abs, double* tau_st);
 
 opal_status OPAL_FN(clear)(opal_ctx*);                 /* Grid::clear    yee.rs:543 */
 opal_status OPAL_FN(deposit)(opal_ctx*, int species);  /* Grid::deposit  yee.rs:551 */

@@ -11,14 +11,15 @@ from __future__ import annotations
 import ctypes as C
 import numpy as np
 
-OK, EINVAL, ECUDA, ENCCL, ENOMEM, EASSERT_CFL, EASSERT_INDEX, ECHI_RANGE, ECAPACITY = range(9)
-STATUS_NAMES = ["OK", "EINVAL", "ECUDA", "ENCCL", "ENOMEM", "EASSERT_CFL", "EASSERT_INDEX", "ECHI_RANGE", "ECAPACITY"]
+OK, EINVAL, ECUDA, ENCCL, ENOMEM, EASSERT_CFL, EASSERT_INDEX, ECHI_RANGE, ECAPACITY, EASSERT_PROB = range(10)
+STATUS_NAMES = ["OK", "EINVAL", "ECUDA", "ENCCL", "ENOMEM", "EASSERT_CFL", "EASSERT_INDEX", "ECHI_RANGE", "ECAPACITY", "EASSERT_PROB"]
 BDY_INTERNAL, BDY_LASER, BDY_ABSORBING, BDY_CONDUCTING = range(4)
 ELECTRON, ION, PHOTON = range(3)
 LEFT, RIGHT = 0, 1
 FLAG_NO_RADIATION_REACTION = 1 << 0
 FLAG_NO_BEAMING = 1 << 1
 FLAG_IMMOBILE_PHOTONS = 1 << 2
+FLAG_NO_STIMULATED_EMISSION = 1 << 3
 FLAG_LEAN_STATE = 1 << 8
 FLAG_STRICT_FP = 1 << 9
 GHOST_SIZE, LASER_BDY_SIZE, ABSORBING_BDY_SIZE, CONDUCTING_BDY_SIZE = 4, 4, 200, 4
@@ -51,6 +52,8 @@ SIGNATURES = {
     "migrants_take": [_vp, _int, _int, _i64, _pi64, _vp],
     "migrants_give": [_vp, _int, _int, _i64, _vp],
     "emit_radiation": [_vp, _f64, _pf64, _pf64, _pf64],
+    "absorb": [_vp, _f64, _pf64, _pf64],
+    "photon_pair_depths": [_vp, _int, _i64, _vp, _vp],
     "clear": [_vp],
     "deposit": [_vp, _int],
     "halo_take": [_vp, _int, _vp],
@@ -260,6 +263,23 @@ class Slab:
             return None if v is None else C.byref(C.c_double(v))
         self._ck(self.abi.emit_radiation(self._h, t, opt(min_energy_mev), opt(max_angle), opt(max_formation_length)),
                  "emit_radiation")
+
+    def absorb(self, t, max_displacement=None, stop_time=None):
+        """absorb (particle/interactions.rs:145)"""
+        def opt(v):
+            return None if v is None else C.byref(C.c_double(v))
+        self._ck(self.abi.absorb(self._h, t, opt(max_displacement), opt(stop_time)), "absorb")
+
+    def photon_pair_depths(self):
+        """(tau_abs, tau_st) of the photons, in download order (photon.rs:28-29)"""
+        n = self.count(PHOTON)
+        a, b = np.empty(n), np.empty(n)
+        self._ck(self.abi.photon_pair_depths(self._h, 0, n, _ptr(a), _ptr(b)), "photon_pair_depths")
+        return a, b
+
+    def set_photon_pair_depths(self, tau_abs, tau_st):
+        a, b = _f64arr(tau_abs).copy(), _f64arr(tau_st).copy()
+        self._ck(self.abi.photon_pair_depths(self._h, 1, a.size, _ptr(a), _ptr(b)), "photon_pair_depths")
 
     def clear(self):
         self._ck(self.abi.clear(self._h), "clear")

@@ -2,8 +2,10 @@
 // qed/photon_absorption.rs, qed/stimulated_emission.rs, qed/special_functions/airy.rs).
 //
 // Compiled with --fmad=false (see opal_absorb.cuh).
+#include <algorithm>
 #include <cstdint>
 
+#include "opal_device.cuh"
 #include "opal_absorb.cuh"
 #include "opal_b200.h"
 
@@ -105,3 +107,188 @@ opal_status opal_qed_pair_cross_sections(int64_t n, const double* k4, const doub
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// absorb (particle/interactions.rs:145-340)
+//
+// The reference walks, photon by photon, the electrons of the photon's cell in store order, spending the photon's two
+// optical depths pair by pair and stopping at the first event.  Here one WARP takes one photon: the 32 lanes evaluate
+// the two cross sections of 32 electrons of the cell bucket at once (that is where the time goes: up to 40 pow() per
+// Airy function), then every lane replays the sequential optical-depth bookkeeping over those 32 partial probabilities
+// in store order -- the same subtractions in the same order as the reference, so the event, the electron it happens at
+// and the depths left over are those of the sequential loop.  Events are recorded per photon (no atomics); the kicks,
+// the copies made by stimulated emission and the deletion of absorbed photons follow in separate passes, as the
+// reference applies them after the pair loop (interactions.rs:291-330).
+// =====================================================================================================================
+namespace opal {
+namespace pairs {
+
+constexpr unsigned FULLMASK = 0xffffffffu;
+constexpr double PHOTON_E_ECRIT_CUTOFF = 1.0e-8;     // interactions.rs:146
+constexpr unsigned ABSORB_STREAM = 8u;               // Philox streams 8..11: apart from emit_radiation's 0..3
+
+struct AbsorbArgs {
+    double t, max_displacement, stop_time;           // NaN == None
+    unsigned long long seed;
+    unsigned call_index;
+    int no_stimulated;
+};
+
+__global__ void k_last_occupied(BucketDev e, int* __restrict__ last) {
+    int best = -1;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < e.ncell; c += gridDim.x * blockDim.x)
+        if (e.count[c] > 0) best = c;
+    if (best >= 0) atomicMax(last, best);
+}
+
+// kind[i]: 0 nothing, 1 absorbed, 2 stimulated emission; slot[i]: bucket slot of the electron it happened at
+__global__ void __launch_bounds__(128) k_absorb_scan(GridDev g, BucketDev e, PhotonDev ph, AbsorbArgs a, const int* __restrict__ last_occupied,
+                                                      int* __restrict__ kind, long long* __restrict__ slot, StatusDev* __restrict__ st) {
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int n = *ph.n;
+    const int last = *last_occupied;
+    const double cdt_dx = OPAL_C * g.dt / g.dx;
+    bool bad = false;
+    for (int i = warp; i < n; i += nwarps) {
+        if (lane == 0) { kind[i] = 0; slot[i] = -1; }
+        const double kx = ph.f[P_KX][i], ky = ph.f[P_KY][i], kz = ph.f[P_KZ][i];
+        const double k0 = sqrt(kx * kx + ky * ky + kz * kz);
+        const double chi_g = ph.f[P_CHI][i];
+        if (chi_g * OPAL_ME_MEV / (k0 * OPAL_ME_MEV) < PHOTON_E_ECRIT_CUTOFF) continue;
+        if (!isnan(a.stop_time) && a.t - ph.f[P_BIRTH][i] > a.stop_time) continue;
+        if (!isnan(a.max_displacement) && hypot(ph.f[P_Y][i], ph.f[P_Z][i]) > a.max_displacement) continue;
+        const int c = ph.cell[i];
+        if (c < 0 || c >= e.ncell || c == last) continue;      // (the last occupied cell: see the header of opal_absorb)
+        const int ne = e.count[c];
+        if (ne == 0) continue;
+        const long long base = e.start[c];
+        const double k4[4] = {k0, kx, ky, kz};
+        double tau_abs = ph.f[P_TAU_ABS][i], tau_st = ph.f[P_TAU_ST][i];
+        int what = 0;
+        long long where = -1;
+        for (int j0 = 0; j0 < ne && what == 0; j0 += 32) {
+            double pa = 0.0, ps = 0.0;
+            if (j0 + lane < ne) {
+                const long long s = base + j0 + lane;
+                const double p4[4] = {e.f[F_GAMMA][s], e.f[F_UX][s], e.f[F_UY][s], e.f[F_UZ][s]};
+                const double chi_e = e.f[F_CHI][s], w = e.f[F_W][s];
+                double sigma;
+                if (pair_cross_section<+1>(k4, p4, chi_g, chi_e, &sigma)) { pa = w * cdt_dx * sigma; if (!(pa >= 0.0)) bad = true; }
+                if (!a.no_stimulated && pair_cross_section<-1>(k4, p4, chi_g, chi_e, &sigma)) { ps = w * cdt_dx * sigma; if (!(ps >= 0.0)) bad = true; }
+            }
+            const int m = min(32, ne - j0);
+            for (int l = 0; l < m; l++) {                        // Photon::interacts_with (photon.rs:312-362), in store order
+                const double prob_abs = __shfl_sync(FULLMASK, pa, l), prob_st = __shfl_sync(FULLMASK, ps, l);
+                tau_abs -= prob_abs;                             // a None cross section subtracts nothing: prob == 0
+                tau_st -= prob_st;
+                if (tau_abs < 0.0 && tau_st < 0.0) {
+                    double r, r_abs, r_st, unused;
+                    philox_uniform2(a.seed, (uint64_t)i, a.call_index, ABSORB_STREAM, r, r_abs);
+                    philox_uniform2(a.seed, (uint64_t)i, a.call_index, ABSORB_STREAM + 1u, r_st, unused);
+                    if (r < prob_abs / (prob_abs + prob_st)) what = 1;
+                    else { tau_abs = -log1p(-r_abs); tau_st = -log1p(-r_st); what = 2; }
+                } else if (tau_abs < 0.0) {
+                    what = 1;
+                } else if (tau_st < 0.0) {
+                    double r_st, unused;
+                    philox_uniform2(a.seed, (uint64_t)i, a.call_index, ABSORB_STREAM + 1u, r_st, unused);
+                    tau_st = -log1p(-r_st);
+                    what = 2;
+                }
+                if (what) { where = base + j0 + l; break; }
+            }
+        }
+        if (lane == 0) {
+            ph.f[P_TAU_ABS][i] = tau_abs; ph.f[P_TAU_ST][i] = tau_st;
+            kind[i] = what; slot[i] = where;
+        }
+    }
+    if (bad) atomicOr(&st->err, ERR_PROB);
+}
+
+// Electron::kick (electron.rs:256-262) for every event, and the copy a stimulated emission adds (interactions.rs:305-310)
+__global__ void k_absorb_apply(BucketDev e, PhotonDev ph, AbsorbArgs a, int n0, const int* __restrict__ kind, const long long* __restrict__ slot,
+                               StatusDev* __restrict__ st) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n0; i += gridDim.x * blockDim.x) {
+        const int what = kind[i];
+        if (what == 0) continue;
+        const long long s = slot[i];
+        const double k[3] = {ph.f[P_KX][i] * OPAL_ME_MEV, ph.f[P_KY][i] * OPAL_ME_MEV, ph.f[P_KZ][i] * OPAL_ME_MEV};     // Photon::momentum
+        const double we = e.f[F_W][s];
+        // absorbed: kick(k, photon weight); stimulated: kick(-k, electron weight)
+        const double scale = what == 1 ? ph.f[P_W][i] / we : we / we;
+        const double sgn = what == 1 ? 1.0 : -1.0;
+        atomicAdd(&e.f[F_UX][s], scale * (sgn * k[0]) / OPAL_ME_MEV);
+        atomicAdd(&e.f[F_UY][s], scale * (sgn * k[1]) / OPAL_ME_MEV);
+        atomicAdd(&e.f[F_UZ][s], scale * (sgn * k[2]) / OPAL_ME_MEV);
+        if (what == 2) {
+            const int o = atomicAdd(ph.n, 1);
+            if (o >= ph.cap) { atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PHOTONS); continue; }
+            double r0, r1, r2, r3;
+            philox_uniform2(a.seed, (uint64_t)i, a.call_index, ABSORB_STREAM + 2u, r0, r1);
+            philox_uniform2(a.seed, (uint64_t)i, a.call_index, ABSORB_STREAM + 3u, r2, r3);
+            ph.cell[o] = ph.cell[i];
+            for (int f = 0; f < NF_PHOTON; f++) ph.f[f][o] = ph.f[f][i];
+            ph.f[P_W][o] = we;                                   // photon.with_weight(e.weight())
+            ph.f[P_TAU][o] = -log1p(-r0);                        // with_optical_depths: tau[0] (tau[1] is never read on this path)
+            (void)r1;
+            ph.f[P_TAU_ABS][o] = -log1p(-r2); ph.f[P_TAU_ST][o] = -log1p(-r3);
+            ph.f[P_BIRTH][o] = a.t;                              // at_time(t)
+        }
+    }
+}
+
+__global__ void k_absorb_gamma(BucketDev e, int n0, const int* __restrict__ kind, const long long* __restrict__ slot) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n0; i += gridDim.x * blockDim.x) {
+        if (kind[i] == 0) continue;
+        const long long s = slot[i];
+        const double ux = e.f[F_UX][s], uy = e.f[F_UY][s], uz = e.f[F_UZ][s];
+        e.f[F_GAMMA][s] = sqrt(1.0 + (ux * ux + uy * uy + uz * uz));
+    }
+}
+
+// the photon store without the absorbed ones (interactions.rs:291-301); copies appended by k_absorb_apply sit at >= n0
+__global__ void k_absorb_compact(PhotonDev src, PhotonDev dst, int n0, const int* __restrict__ kind) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n = min(*src.n, src.cap);
+    const int n_round = (n + 31) & ~31;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        const bool keep = i < n && (i >= n0 || kind[i] != 1);
+        const unsigned mk = __ballot_sync(FULLMASK, keep);
+        if (!mk) continue;
+        int base = 0;
+        const int leader = __ffs(mk) - 1;
+        if (lane == leader) base = atomicAdd(dst.n, __popc(mk));
+        base = __shfl_sync(FULLMASK, base, leader);
+        if (keep) {
+            const int o = base + __popc(mk & lt_mask);
+            dst.cell[o] = src.cell[i];
+            for (int f = 0; f < NF_PHOTON; f++) dst.f[f][o] = src.f[f][i];
+        }
+    }
+}
+
+}  // namespace pairs
+
+// host side of opal_absorb (opal_host.cu owns the context): 5 launches on `stream`
+int absorb_launch(cudaStream_t stream, const GridDev& g, const BucketDev& e, const PhotonDev& src, const PhotonDev& dst, int n0, double t,
+                  double max_displacement, double stop_time, unsigned long long seed, unsigned call_index, int no_stimulated, int* d_last,
+                  int* d_kind, long long* d_slot, StatusDev* d_status) {
+    using namespace pairs;
+    const AbsorbArgs a = {t, max_displacement, stop_time, seed, call_index, no_stimulated};
+    cudaMemsetAsync(d_last, 0xFF, sizeof(int), stream);
+    cudaMemsetAsync(dst.n, 0, sizeof(int), stream);
+    k_last_occupied<<<148, 256, 0, stream>>>(e, d_last);
+    const int warps_per_block = 4;
+    const int blocks = std::min((n0 + warps_per_block - 1) / warps_per_block, 148 * 16);
+    k_absorb_scan<<<blocks, warps_per_block * 32, 0, stream>>>(g, e, src, a, d_last, d_kind, d_slot, d_status);
+    const int gr = std::min((n0 + 255) / 256, 148 * 8);
+    k_absorb_apply<<<gr, 256, 0, stream>>>(e, src, a, n0, d_kind, d_slot, d_status);
+    k_absorb_gamma<<<gr, 256, 0, stream>>>(e, n0, d_kind, d_slot);
+    k_absorb_compact<<<std::min((2 * n0 + 255) / 256, 148 * 8), 256, 0, stream>>>(src, dst, n0, d_kind);
+    return 5;
+}
+
+}  // namespace opal

@@ -73,6 +73,11 @@ struct Photons {
 
 }  // namespace
 
+namespace opal {   // opal_absorb.cu
+int absorb_launch(cudaStream_t stream, const GridDev& g, const BucketDev& e, const PhotonDev& src, const PhotonDev& dst, int n0, double t,
+                  double max_displacement, double stop_time, unsigned long long seed, unsigned call_index, int no_stimulated, int* d_last,
+                  int* d_kind, long long* d_slot, StatusDev* d_status);
+}
 namespace opal {   // opal_hgram.cu
 void hgram_minmax_charged(cudaStream_t, const GridDev&, const BucketDev&, int species, bool full, int ndim, const int* q, const int* lg,
                           unsigned long long* d_mm, double* d_out4);
@@ -101,6 +106,8 @@ struct opal_ctx {
     // exchange / mover buffers
     opal_migrant* d_movers = nullptr; int mover_seg_cap = 0;
     opal_migrant* d_overflow = nullptr;
+    // absorb: per-photon event records (opal_absorb.cu)
+    int* d_absorb_kind = nullptr; long long* d_absorb_slot = nullptr; int* d_absorb_last = nullptr; int absorb_cap = 0; long long absorb_calls = 0;
     int overflow_cap = 0;
     StripRec* d_cmovers = nullptr; int* d_cmcount = nullptr; int cell_mover_cap = 0;   // per-cell left/right mover strips (lean electrons)
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
@@ -315,6 +322,7 @@ bool fetch_status(opal_ctx* c) {
     if (e & ERR_CFL) return fail(c, OPAL_EASSERT_CFL, "push: assert!(dxi < 1.0) failed (electron.rs:313 / ion.rs:199 / photon.rs:164)");
     if (e & ERR_INDEX) return fail(c, OPAL_EASSERT_INDEX, "cell index out of range (yee.rs:501-502)");
     if (e & ERR_CHI) return fail(c, OPAL_ECHI_RANGE, "sample: chi beyond the tabulated range (photon_emission.rs:144)");
+    if (e & ERR_PROB) return fail(c, OPAL_EASSERT_PROB, "absorb: assert!(partial_prob >= 0.0) failed (photon.rs:325 / photon.rs:336)");
     if (e & ERR_CAPACITY) {
         std::string which;
         if (e & ERR_CAP_MOVERS) which += " mover segments (raise OPAL_MOVER_FRACTION)";
@@ -544,6 +552,31 @@ bool do_emit(opal_ctx* c, double t, double min_e, double max_a, double max_fl) {
     return fetch_status(c);
 }
 
+// absorb (interactions.rs:145): see opal_absorb.cu
+bool do_absorb(opal_ctx* c, double t, double max_displacement, double stop_time) {
+    Buckets& E = c->bk[OPAL_ELECTRON];
+    if (!E.allocated || c->ph[0].cap == 0) return true;
+    if (!E.full) return fail(c, OPAL_EINVAL, "absorb needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)");
+    int nph = 0;
+    if (!photon_count(c, &nph)) return false;
+    if (nph == 0) return true;
+    // every photon can stimulate at most one copy of itself per call
+    if (!ensure_photons(c, 2ll * nph)) return false;
+    if (c->absorb_cap < nph) {
+        if (c->d_absorb_kind) { cudaFree(c->d_absorb_kind); cudaFree(c->d_absorb_slot); }
+        c->absorb_cap = std::max(2 * nph, 1 << 12);
+        CUB(cudaMalloc(&c->d_absorb_kind, (size_t)c->absorb_cap * sizeof(int)));
+        CUB(cudaMalloc(&c->d_absorb_slot, (size_t)c->absorb_cap * sizeof(long long)));
+    }
+    if (!c->d_absorb_last) CUB(cudaMalloc(&c->d_absorb_last, sizeof(int)));
+    const int src = c->ph_cur, dst = 1 - src;
+    c->launches += absorb_launch(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, src), pdev(c, dst), nph, t, max_displacement, stop_time, c->seed,
+                                 (unsigned)c->absorb_calls++, (c->flags & OPAL_FLAG_NO_STIMULATED_EMISSION) ? 1 : 0, c->d_absorb_last,
+                                 c->d_absorb_kind, c->d_absorb_slot, c->d_status);
+    c->ph_cur = dst;
+    return fetch_status(c);
+}
+
 bool do_sync(opal_ctx* c, double ly, double lz) {
     const double* halo = nullptr;
     if (remote(c)) {
@@ -730,6 +763,9 @@ opal_status opal_destroy(opal_ctx* c) {
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (int k = 0; k < 3; k++) for (auto& p : c->ev[k]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (int s = 0; s < 2; s++) free_buckets(c->bk[s]);
+    if (c->d_absorb_kind) cudaFree(c->d_absorb_kind);
+    if (c->d_absorb_slot) cudaFree(c->d_absorb_slot);
+    if (c->d_absorb_last) cudaFree(c->d_absorb_last);
     for (int w = 0; w < 2; w++) {
         if (c->ph[w].d_n) cudaFree(c->ph[w].d_n);
         if (c->ph[w].d_cell) cudaFree(c->ph[w].d_cell);
@@ -782,6 +818,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
             hf[P_X][i] = x[i]; hf[P_PREVX][i] = x[i] - C_LIGHT * ux[i] * dt / (k0 * dx);
             hf[P_KX][i] = ux[i]; hf[P_KY][i] = uy[i]; hf[P_KZ][i] = uz[i]; hf[P_W][i] = w[i];
             hf[P_TAU][i] = tau ? tau[i] : inf; hf[P_BIRTH][i] = -inf;
+            hf[P_TAU_ABS][i] = hf[P_TAU_ST][i] = hf[P_TAU][i];            // with_optical_depth (photon.rs:118-124)
         }
         const int nn = (int)n;
         CU(cudaMemcpyAsync(P.d_n, &nn, sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -1068,6 +1105,44 @@ opal_status opal_emit_radiation(opal_ctx* c, double t, const double* min_energy_
     const double nan = std::numeric_limits<double>::quiet_NaN();
     do_emit(c, t, min_energy_mev ? *min_energy_mev : nan, max_angle ? *max_angle : nan, max_fl ? *max_fl : nan);
     return (opal_status)c->status;
+}
+
+opal_status opal_absorb(opal_ctx* c, double t, const double* max_displacement, const double* stop_time) {
+    CHECK_CTX(c);
+    c->ke_fused = false;
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    do_absorb(c, t, max_displacement ? *max_displacement : nan, stop_time ? *stop_time : nan);
+    return (opal_status)c->status;
+}
+
+opal_status opal_photon_pair_depths(opal_ctx* c, int set, int64_t n, double* tau_abs, double* tau_st) {
+    CHECK_CTX(c);
+    int nph = 0;
+    if (!photon_count(c, &nph)) return (opal_status)c->status;
+    if (n != nph || (n > 0 && (!tau_abs || !tau_st))) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    Photons& P = c->ph[c->ph_cur];
+    std::vector<int> hc((size_t)n), order((size_t)n);
+    std::vector<double> a((size_t)n), b((size_t)n);
+    CU(cudaMemcpyAsync(hc.data(), P.d_cell, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (!set) {
+        CU(cudaMemcpyAsync(a.data(), P.d_f[P_TAU_ABS], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaMemcpyAsync(b.data(), P.d_f[P_TAU_ST], (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    for (int64_t i = 0; i < n; i++) order[(size_t)i] = (int)i;
+    std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return hc[(size_t)x] < hc[(size_t)y]; });      // the download order
+    for (int64_t o = 0; o < n; o++) {
+        const size_t i = (size_t)order[(size_t)o];
+        if (set) { a[i] = tau_abs[o]; b[i] = tau_st[o]; }
+        else { tau_abs[o] = a[i]; tau_st[o] = b[i]; }
+    }
+    if (set) {
+        CU(cudaMemcpyAsync(P.d_f[P_TAU_ABS], a.data(), (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(P.d_f[P_TAU_ST], b.data(), (size_t)n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    return OPAL_OK;
 }
 
 opal_status opal_clear(opal_ctx* c) {

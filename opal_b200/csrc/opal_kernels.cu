@@ -1037,12 +1037,12 @@ __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, P
         bool keep = false;
         PhState p;
         long long cell = 0;
-        double tau = 0.0, birth = 0.0;
+        double tau = 0.0, birth = 0.0, tau_abs = 0.0, tau_st = 0.0;
         if (i < n) {
             cell = src.cell[i];
             p.x = src.f[P_X][i]; p.prev_x = src.f[P_PREVX][i]; p.k = {src.f[P_KX][i], src.f[P_KY][i], src.f[P_KZ][i]};
             p.w = src.f[P_W][i]; p.chi = src.f[P_CHI][i]; p.y = src.f[P_Y][i]; p.z = src.f[P_Z][i];
-            tau = src.f[P_TAU][i]; birth = src.f[P_BIRTH][i];
+            tau = src.f[P_TAU][i]; birth = src.f[P_BIRTH][i]; tau_abs = src.f[P_TAU_ABS][i]; tau_st = src.f[P_TAU_ST][i];
             if (cell < 0 || cell >= g.nx) { bad_index = true; }
             else {
                 CellFields cf;
@@ -1064,7 +1064,7 @@ __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, P
                         m.cell = side == 0 ? cell : cell - g.nx;
                         m.x = p.x; m.prev_x = p.prev_x; m.u[0] = p.k.x; m.u[1] = p.k.y; m.u[2] = p.k.z; m.weight = p.w;
                         m.gamma = sqrt(dot(p.k, p.k)); m.chi = p.chi; m.tau = tau; m.work = 0.0; m.y = p.y; m.z = p.z;
-                        m.birth_time = birth; m.pad[0] = 0.0; m.pad[1] = 0.0;
+                        m.birth_time = birth; m.pad[0] = tau_abs; m.pad[1] = tau_st;
                         (side == 0 ? out_l : out_r)[r] = m;
                     } else atomicOr(&st->err, ERR_CAPACITY);
                 }
@@ -1082,7 +1082,7 @@ __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, P
             dst.cell[o] = (int)cell;
             dst.f[P_X][o] = p.x; dst.f[P_PREVX][o] = p.prev_x; dst.f[P_KX][o] = p.k.x; dst.f[P_KY][o] = p.k.y; dst.f[P_KZ][o] = p.k.z;
             dst.f[P_W][o] = p.w; dst.f[P_CHI][o] = p.chi; dst.f[P_TAU][o] = tau; dst.f[P_Y][o] = p.y; dst.f[P_Z][o] = p.z;
-            dst.f[P_BIRTH][o] = birth;
+            dst.f[P_BIRTH][o] = birth; dst.f[P_TAU_ABS][o] = tau_abs; dst.f[P_TAU_ST][o] = tau_st;
         }
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
@@ -1100,7 +1100,7 @@ __global__ void k_photon_insert(PhotonDev dst, const opal_migrant* __restrict__ 
         dst.cell[o] = (int)(m.cell + cell_shift);
         dst.f[P_X][o] = m.x; dst.f[P_PREVX][o] = m.prev_x; dst.f[P_KX][o] = m.u[0]; dst.f[P_KY][o] = m.u[1]; dst.f[P_KZ][o] = m.u[2];
         dst.f[P_W][o] = m.weight; dst.f[P_CHI][o] = m.chi; dst.f[P_TAU][o] = m.tau; dst.f[P_Y][o] = m.y; dst.f[P_Z][o] = m.z;
-        dst.f[P_BIRTH][o] = m.birth_time;
+        dst.f[P_BIRTH][o] = m.birth_time; dst.f[P_TAU_ABS][o] = m.pad[0]; dst.f[P_TAU_ST][o] = m.pad[1];
     }
 }
 
@@ -1337,10 +1337,11 @@ __global__ void __launch_bounds__(BLOCK) k_emit(GridDev g, BucketDev b, PhotonDe
                 const long long s = base + i;
                 double tau = b.f[F_TAU][s];
                 if (tau < 0.0) {                                                       // electron.rs:209
-                    double r_tau, r1, r2, r3, r4, r5;
+                    double r_tau, r1, r2, r3, r4, r5, r6, r7;
                     philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 0u, r_tau, r1);
                     philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 1u, r2, r3);
                     philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 2u, r4, r5);
+                    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 3u, r6, r7);
                     b.f[F_TAU][s] = -log1p(-r_tau);                                    // Exp1 by inversion
                     double chi = b.f[F_CHI][s], gamma = b.f[F_GAMMA][s];
                     V3 u = {b.f[F_UX][s], b.f[F_UY][s], b.f[F_UZ][s]};
@@ -1378,7 +1379,7 @@ __global__ void __launch_bounds__(BLOCK) k_emit(GridDev g, BucketDev b, PhotonDe
                             m.cell = c; m.x = b.f[F_X][s]; m.prev_x = CUDART_NAN;      // Photon::create with dx = dt = 0
                             m.u[0] = k.x; m.u[1] = k.y; m.u[2] = k.z; m.weight = b.f[F_W][s];
                             m.gamma = sqrt(dot(k, k)); m.chi = 0.0; m.tau = -log1p(-r4); m.work = 0.0; m.y = 0.0; m.z = 0.0;
-                            m.birth_time = t; m.pad[0] = 0.0; m.pad[1] = 0.0; (void)r5;
+                            m.birth_time = t; m.pad[0] = -log1p(-r5); m.pad[1] = -log1p(-r6); (void)r7;   // tau_abs, tau_st (photon.rs:130-131)
                         }
                     }
                 }
@@ -1395,7 +1396,7 @@ __global__ void __launch_bounds__(BLOCK) k_emit(GridDev g, BucketDev b, PhotonDe
                         ph.cell[o] = (int)m.cell;
                         ph.f[P_X][o] = m.x; ph.f[P_PREVX][o] = m.prev_x; ph.f[P_KX][o] = m.u[0]; ph.f[P_KY][o] = m.u[1]; ph.f[P_KZ][o] = m.u[2];
                         ph.f[P_W][o] = m.weight; ph.f[P_CHI][o] = 0.0; ph.f[P_TAU][o] = m.tau; ph.f[P_Y][o] = 0.0; ph.f[P_Z][o] = 0.0;
-                        ph.f[P_BIRTH][o] = m.birth_time;
+                        ph.f[P_BIRTH][o] = m.birth_time; ph.f[P_TAU_ABS][o] = m.pad[0]; ph.f[P_TAU_ST][o] = m.pad[1];
                     } else atomicOr(&st->err, ERR_CAPACITY);
                 }
             }

@@ -14,7 +14,9 @@ namespace opal {
 // allocated; the rest only for full-state contexts.
 enum { F_X = 0, F_UX, F_UY, F_UZ, F_W, NF_LEAN, F_PREVX = NF_LEAN, F_GAMMA, F_CHI, F_TAU, F_WORK, F_Y, F_Z, NF_FULL };
 // flat photon store
-enum { P_X = 0, P_PREVX, P_KX, P_KY, P_KZ, P_W, P_CHI, P_TAU, P_Y, P_Z, P_BIRTH, NF_PHOTON };
+enum { P_X = 0, P_PREVX, P_KX, P_KY, P_KZ, P_W, P_CHI, P_TAU, P_Y, P_Z, P_BIRTH,
+       P_TAU_ABS, P_TAU_ST,      // optical depths against one-photon absorption / stimulated emission (photon.rs:28-29)
+       NF_PHOTON };
 
 // device-side view of the Yee grid: SoA over `len` cells (ghost/boundary zones included).
 struct GridDev {
@@ -67,7 +69,8 @@ struct StatusDev {
 };
 enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
        // which fixed-capacity buffer overflowed (set together with ERR_CAPACITY)
-       ERR_CAP_MOVERS = 16u, ERR_CAP_PARKED = 32u, ERR_CAP_OUTBOX = 64u, ERR_CAP_PHOTONS = 128u };
+       ERR_CAP_MOVERS = 16u, ERR_CAP_PARKED = 32u, ERR_CAP_OUTBOX = 64u, ERR_CAP_PHOTONS = 128u,
+       ERR_PROB = 256u };     // assert!(partial_prob >= 0.0) (photon.rs:325)
 
 // compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout);
 // the destination (c-1 / c+1) is implied by the strip it sits in

@@ -623,13 +623,13 @@ inline opal_migrant to_wire(const Photon& p) {
     opal_migrant m; std::memset(&m, 0, sizeof(m));
     m.cell = p.cell; m.x = p.x; m.prev_x = p.prev_x; m.u[0] = p.k.x; m.u[1] = p.k.y; m.u[2] = p.k.z;
     m.weight = p.weight; m.gamma = std::sqrt(norm_sqr(p.k)); m.chi = p.chi; m.y = p.y; m.z = p.z; m.birth_time = p.birth_time;
-    m.tau = p.tau[0];
+    m.tau = p.tau[0]; m.pad[0] = p.tau_abs; m.pad[1] = p.tau_st;
     return m;
 }
 inline void from_wire(const opal_migrant& m, Photon& p) {
     p = photon_create(m.cell, m.x, Vec3{m.u[0], m.u[1], m.u[2]}, m.weight, 1.0, 0.0);
     p.prev_x = m.prev_x; p.chi = m.chi; p.y = m.y; p.z = m.z; p.birth_time = m.birth_time;
-    p.tau[0] = p.tau[1] = p.tau_abs = p.tau_st = m.tau;
+    p.tau[0] = p.tau[1] = m.tau; p.tau_abs = m.pad[0]; p.tau_st = m.pad[1];
 }
 
 // ---- Population<T> (particle/mod.rs:141-376) ----------------------------------------------
@@ -960,6 +960,108 @@ void emit_radiation(opal_ctx* g, double t, const double* min_energy, const doubl
     g->photons.store.insert(g->photons.store.end(), emitted.begin(), emitted.end());
 }
 
+// Photon::interacts_with (photon.rs:312-362): 0 nothing, 1 absorbed, 2 stimulated emission; sets *bad where the
+// reference's assert!(partial_prob >= 0.0) would panic
+int interacts_with(Photon& ph, const Electron& e, double dt, double dx, Xoshiro& rng, bool no_stimulated, bool* bad) {
+    const double k[4] = {std::sqrt(norm_sqr(ph.k)), ph.k.x, ph.k.y, ph.k.z};
+    const double p[4] = {e.gamma, e.u.x, e.u.y, e.u.z};
+    double prob_abs = 0.0, prob_st = 0.0, sigma;
+    if (pair_cross_section(+1, k, p, ph.chi, e.chi, &sigma)) {
+        double partial = e.weight * (SPEED_OF_LIGHT * dt / dx) * sigma;
+        if (!(partial >= 0.0)) *bad = true;
+        ph.tau_abs -= partial;
+        prob_abs = partial;
+    }
+    if (!no_stimulated && pair_cross_section(-1, k, p, ph.chi, e.chi, &sigma)) {
+        double partial = e.weight * (SPEED_OF_LIGHT * dt / dx) * sigma;
+        if (!(partial >= 0.0)) *bad = true;
+        ph.tau_st -= partial;
+        prob_st = partial;
+    }
+    if (ph.tau_abs < 0.0 && ph.tau_st < 0.0) {
+        double r = rng.gen();
+        if (r < prob_abs / (prob_abs + prob_st)) return 1;
+        ph.tau_abs = rng.exp1(); ph.tau_st = rng.exp1();
+        return 2;
+    } else if (ph.tau_abs < 0.0) {
+        return 1;
+    } else if (ph.tau_st < 0.0) {
+        ph.tau_st = rng.exp1();
+        return 2;
+    }
+    return 0;
+}
+
+// particle/interactions.rs:145-340 as the reference runs it on ONE rayon thread: chunks of max(nph / 4, 1) photons,
+// chunk i on a clone of the rng advanced by i jumps.  Both stores are sorted by cell here (the advances that precede
+// absorb in main.rs:239-247 leave them so).  Reference behaviour kept as is: the electron range of a photon's cell
+// needs a FOLLOWING electron of another cell to close it (:216-222), so the last occupied cell of the store never
+// interacts.
+void absorb(opal_ctx* g, double t, const double* max_displacement, const double* stop_time) {
+    const double PHOTON_E_ECRIT_CUTOFF = 1.0e-8;
+    finalize(g, g->electrons); finalize(g, g->photons);
+    std::vector<Electron>& es = g->electrons.store;
+    std::vector<Photon>& ps = g->photons.store;
+    if (es.empty() || ps.empty()) return;
+    const size_t nph = ps.size();
+    const size_t chunk_len = std::max<size_t>(nph / 4, 1);
+    const bool no_stim = (g->flags & OPAL_FLAG_NO_STIMULATED_EMISSION) != 0;
+    std::vector<std::pair<size_t, Photon>> absorbed, emitted;
+    bool bad = false;
+    for (size_t c0 = 0, ci = 0; c0 < nph; c0 += chunk_len, ci++) {
+        Xoshiro rng = g->rng;
+        for (size_t j = 0; j < ci; j++) rng.jump();
+        int64_t prev_cell = -1;
+        bool has_start = false, has_end = false;
+        size_t start = 0, end = 0;
+        for (size_t ip = c0; ip < std::min(nph, c0 + chunk_len); ip++) {
+            Photon& ph = ps[ip];
+            if (ph.chi * ELECTRON_MASS_MEV / (std::sqrt(norm_sqr(ph.k)) * ELECTRON_MASS_MEV) < PHOTON_E_ECRIT_CUTOFF) continue;
+            if (stop_time && t - ph.birth_time > *stop_time) continue;
+            if (max_displacement && std::hypot(ph.y, ph.z) > *max_displacement) continue;
+            if (ph.cell != prev_cell) {
+                size_t from = has_end ? end : 0;
+                has_start = false;
+                for (size_t i = from; i < es.size(); i++) if (es[i].cell == ph.cell) { start = i; has_start = true; break; }
+                has_end = false;
+                if (has_start) for (size_t i = start; i < es.size(); i++) if (es[i].cell != ph.cell) { end = i; has_end = true; break; }
+            }
+            prev_cell = ph.cell;
+            if (!has_start || !has_end) continue;
+            for (size_t j = start; j < end; j++) {
+                int what = interacts_with(ph, es[j], g->dt, g->dx, rng, no_stim, &bad);
+                if (what == 1) { ph.flag = true; absorbed.emplace_back(j, ph); break; }
+                if (what == 2) { Photon clone = ph; clone.weight = es[j].weight; emitted.emplace_back(j, clone); break; }
+            }
+        }
+    }
+    if (bad && g->status == OPAL_OK) { g->status = OPAL_EASSERT_PROB; g->err = "absorb: assert!(partial_prob >= 0.0) (photon.rs:325)"; }
+    if (!absorbed.empty()) {      // per-chunk swap_remove from the back (:291-301)
+        std::vector<Photon> kept;
+        kept.reserve(nph);
+        for (size_t c0 = 0; c0 < nph; c0 += chunk_len) {
+            std::vector<Photon> sub(ps.begin() + (ptrdiff_t)c0, ps.begin() + (ptrdiff_t)std::min(nph, c0 + chunk_len));
+            for (size_t i = sub.size(); i-- > 0;) if (sub[i].flag) { sub[i] = sub.back(); sub.pop_back(); }
+            kept.insert(kept.end(), sub.begin(), sub.end());
+        }
+        ps.swap(kept);
+    }
+    for (auto& ev : emitted) {    // with_optical_depths(rng).at_time(t) on the master rng (:305-310)
+        Photon extra = ev.second;
+        extra.tau[0] = g->rng.exp1(); extra.tau[1] = g->rng.exp1(); extra.tau_abs = g->rng.exp1(); extra.tau_st = g->rng.exp1();
+        extra.birth_time = t;
+        ps.push_back(extra);
+    }
+    auto kick = [](Electron& e, Vec3 k, double weight) {          // electron.rs:256-262
+        double scale = weight / e.weight;
+        e.u.x += scale * k.x / ELECTRON_MASS_MEV; e.u.y += scale * k.y / ELECTRON_MASS_MEV; e.u.z += scale * k.z / ELECTRON_MASS_MEV;
+        e.gamma = std::sqrt(1.0 + norm_sqr(e.u));
+    };
+    for (auto& ev : absorbed) kick(es[ev.first], ev.second.k * ELECTRON_MASS_MEV, ev.second.weight);
+    for (auto& ev : emitted) kick(es[ev.first], -1.0 * (ev.second.k * ELECTRON_MASS_MEV), es[ev.first].weight);
+    g->rng.long_jump();
+}
+
 template <class T> double kinetic(opal_ctx* g, Population<T>& pop) {
     finalize(g, pop);
     double s = 0.0;
@@ -1162,6 +1264,22 @@ opal_status opal_ref_migrants_give(opal_ctx* g, int species, int side, int64_t n
     return OPAL_OK;
 }
 
+opal_status opal_ref_absorb(opal_ctx* g, double t, const double* max_displacement, const double* stop_time) {
+    CHECK_CTX(g);
+    absorb(g, t, max_displacement, stop_time);
+    return (opal_status)g->status;
+}
+opal_status opal_ref_photon_pair_depths(opal_ctx* g, int set, int64_t n, double* tau_abs, double* tau_st) {
+    CHECK_CTX(g);
+    finalize(g, g->photons);
+    std::vector<Photon>& ps = g->photons.store;
+    if (n != (int64_t)ps.size() || !tau_abs || !tau_st) return OPAL_EINVAL;
+    for (size_t o = 0; o < ps.size(); o++) {       // download order == store order here
+        if (set) { ps[o].tau_abs = tau_abs[o]; ps[o].tau_st = tau_st[o]; }
+        else { tau_abs[o] = ps[o].tau_abs; tau_st[o] = ps[o].tau_st; }
+    }
+    return OPAL_OK;
+}
 opal_status opal_ref_emit_radiation(opal_ctx* g, double t, const double* min_energy_mev, const double* max_angle, const double* max_fl) {
     CHECK_CTX(g);
     emit_radiation(g, t, min_energy_mev, max_angle, max_fl);
