@@ -165,6 +165,9 @@ opal_status OPAL_FN(emit_radiation)(opal_ctx*, double t, const double* min_energ
    Reference behaviour kept: the electrons of the slab's LAST occupied cell never interact
    (interactions.rs:216-222 needs a following electron to close the range).                    */
 opal_status OPAL_FN(absorb)(opal_ctx*, double t, const double* max_displacement, const double* stop_time);
+/* makes opal_run_steps call absorb after the three advances of every step, where main.rs:246-248 does
+   (`if photon_absorption { absorb(...) }`), with these two limits (NULL == None)                  */
+opal_status OPAL_FN(set_absorption)(opal_ctx*, int enabled, const double* max_displacement, const double* stop_time);
 /* Photon::tau_abs / tau_st (photon.rs:28-29) in the order particles_download(OPAL_PHOTON) uses;
    set != 0 writes them (n must equal the photon count), set == 0 reads them                     */
 opal_status OPAL_FN(photon_pair_depths)(opal_ctx*, int set, int64_t n, double* tau_abs, double* tau_st);
@@ -185,7 +188,7 @@ opal_status OPAL_FN(laser_x)(opal_ctx*, double* x);
 opal_status OPAL_FN(field_advance)(opal_ctx*);         /* Grid::advance  yee.rs:345 */
 
 /* The whole loop body main.rs:238-267 repeated nsteps times without returning to the host:
-   advance(e), advance(i), advance(ph), [emit], [clear, deposit(e), deposit(i)], synchronize,
+   advance(e), advance(i), advance(ph), [absorb], [emit], [clear, deposit(e), deposit(i)], synchronize,
    field advance, t += dt.  laser_y/laser_z: nsteps precomputed values (NULL => no laser).
    emit_filters3: {min_energy_mev, max_angle, max_formation_length}, NaN == None; NULL == all None.
    When deposition is on and emission off the push and deposit of each charged species run as

@@ -53,6 +53,7 @@ SIGNATURES = {
     "migrants_give": [_vp, _int, _int, _i64, _vp],
     "emit_radiation": [_vp, _f64, _pf64, _pf64, _pf64],
     "absorb": [_vp, _f64, _pf64, _pf64],
+    "set_absorption": [_vp, _int, _pf64, _pf64],
     "photon_pair_depths": [_vp, _int, _i64, _vp, _vp],
     "clear": [_vp],
     "deposit": [_vp, _int],
@@ -269,6 +270,12 @@ class Slab:
         def opt(v):
             return None if v is None else C.byref(C.c_double(v))
         self._ck(self.abi.absorb(self._h, t, opt(max_displacement), opt(stop_time)), "absorb")
+
+    def set_absorption(self, enabled, max_displacement=None, stop_time=None):
+        """run_steps then calls absorb every step (main.rs:246-248)"""
+        def opt(v):
+            return None if v is None else C.byref(C.c_double(v))
+        self._ck(self.abi.set_absorption(self._h, int(enabled), opt(max_displacement), opt(stop_time)), "set_absorption")
 
     def photon_pair_depths(self):
         """(tau_abs, tau_st) of the photons, in download order (photon.rs:28-29)"""

@@ -108,6 +108,7 @@ struct opal_ctx {
     opal_migrant* d_overflow = nullptr;
     // absorb: per-photon event records (opal_absorb.cu)
     int* d_absorb_kind = nullptr; long long* d_absorb_slot = nullptr; int* d_absorb_last = nullptr; int absorb_cap = 0; long long absorb_calls = 0;
+    bool absorb_on = false; double absorb_max_displacement = 0.0, absorb_stop_time = 0.0;   // opal_set_absorption (NaN == None)
     int overflow_cap = 0;
     StripRec* d_cmovers = nullptr; int* d_cmcount = nullptr; int cell_mover_cap = 0;   // per-cell left/right mover strips (lean electrons)
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
@@ -1115,6 +1116,16 @@ opal_status opal_absorb(opal_ctx* c, double t, const double* max_displacement, c
     return (opal_status)c->status;
 }
 
+opal_status opal_set_absorption(opal_ctx* c, int enabled, const double* max_displacement, const double* stop_time) {
+    CHECK_CTX(c);
+    if (enabled && !c->full) return (opal_status)(fail(c, OPAL_EINVAL, "absorption needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)"), c->status);
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    c->absorb_on = enabled != 0;
+    c->absorb_max_displacement = max_displacement ? *max_displacement : nan;
+    c->absorb_stop_time = stop_time ? *stop_time : nan;
+    return OPAL_OK;
+}
+
 opal_status opal_photon_pair_depths(opal_ctx* c, int set, int64_t n, double* tau_abs, double* tau_st) {
     CHECK_CTX(c);
     int nph = 0;
@@ -1204,10 +1215,10 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
                            int current_deposition, int photon_emission, const double* f3) {
     CHECK_CTX(c);
     if (remote(c) && !c->comm) return (opal_status)(fail(c, OPAL_ENCCL, "run_steps with remote neighbours needs opal_comm_init"), c->status);
-    if (!c->full && (photon_emission || !current_deposition))
-        return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context supports only the fused push+deposit step (deposition on, emission off)"), c->status);
+    if (!c->full && (photon_emission || c->absorb_on || !current_deposition))
+        return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context supports only the fused push+deposit step (deposition on, emission and absorption off)"), c->status);
     const double nan = std::numeric_limits<double>::quiet_NaN();
-    const bool fused = current_deposition && !photon_emission;
+    const bool fused = current_deposition && !photon_emission && !c->absorb_on;
     double t = t0;
     c->ke_fused = false;
     int64_t s0 = 0;
@@ -1238,9 +1249,10 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     for (int64_t s = s0; s < nsteps && c->status == OPAL_OK; s++) {   // main.rs:238-267
         if (current_deposition) { c->k.clear(c->stream, c->g); c->launches++; }
         // the last step of the call also sums the electrons' kinetic energy (lean strip kernel): opal_energy then needs no particle pass
-        if (!advance_charged(c, OPAL_ELECTRON, fused, true, s == nsteps - 1 && !photon_emission)) break;
+        if (!advance_charged(c, OPAL_ELECTRON, fused, true, s == nsteps - 1 && !photon_emission && !c->absorb_on)) break;
         if (!advance_charged(c, OPAL_ION, fused, true)) break;
         if (!advance_photons(c, c->ph[0].cap > 0)) break;
+        if (c->absorb_on && !do_absorb(c, t, c->absorb_max_displacement, c->absorb_stop_time)) break;      // main.rs:246-248
         if (photon_emission) { if (!do_emit(c, t, f3 ? f3[0] : nan, f3 ? f3[1] : nan, f3 ? f3[2] : nan)) break; }
         if (current_deposition && !fused) {
             if (c->bk[0].allocated) { c->k.deposit(c->stream, c->g, bdev(c, 0), sparams(c, 0), c->d_status); c->launches++; }

@@ -77,8 +77,9 @@ int run(const Options& opt, Ranks& ranks) {
     const bool has_emin = optional_read([&] { photon_energy_min = 1.0e-6 * input.read_f64("qed", "photon_energy_min") / constants::ELEMENTARY_CHARGE; });
     const bool has_amax = optional_read([&] { photon_angle_max = input.read_f64("qed", "photon_angle_max"); });
     const bool has_fl = optional_read([&] { max_formation_length = input.read_f64("qed", "max_formation_length"); });
-    if (photon_absorption)
-        throw std::runtime_error("qed.photon_absorption: photon absorption / stimulated emission (interactions.rs:145-340) is outside this build's hot path");
+    double disable_qed_after = 0.0, disable_absorption_after = 0.0;                 // main.rs:84-85
+    const bool has_dqa = optional_read([&] { disable_qed_after = input.read_f64("qed", "disable_qed_after"); });
+    const bool has_daa = optional_read([&] { disable_absorption_after = input.read_f64("qed", "disable_absorption_after"); });
 
     // laser (main.rs:88-104): both components or a config error; no laser section => periodic
     std::function<double(double, double)> laser_y, laser_z;
@@ -156,6 +157,11 @@ int run(const Options& opt, Ranks& ranks) {
         }
         if (ppc > 0 || np > 1) upload(OPAL_PHOTON, p);
     }
+
+    // main.rs:246-248: absorb(..., disable_qed_after, disable_absorption_after) -- the first lands in absorb's
+    // max_displacement parameter, the second in stop_time (interactions.rs:145); kept as the reference has it
+    if (photon_absorption)
+        ck(OPAL_FN(set_absorption)(ctx, 1, has_dqa ? &disable_qed_after : nullptr, has_daa ? &disable_absorption_after : nullptr), ctx, "set_absorption");
 
     // ---- time loop (main.rs:184-267) ----
     double t = tstart;

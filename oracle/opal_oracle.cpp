@@ -646,6 +646,7 @@ template <class T> struct Population {
 
 // ---- the context ----------------------------------------------------------------------------
 struct opal_ctx {
+    bool absorb_on = false; double absorb_max_displacement = NAN, absorb_stop_time = NAN;   // opal_ref_set_absorption
     int rank, nranks;
     int left_bdy, right_bdy;              // resolved for this slab (yee.rs:278-292)
     int64_t left_size, right_size, size;  // zone sizes and interior cells
@@ -1269,6 +1270,13 @@ opal_status opal_ref_absorb(opal_ctx* g, double t, const double* max_displacemen
     absorb(g, t, max_displacement, stop_time);
     return (opal_status)g->status;
 }
+opal_status opal_ref_set_absorption(opal_ctx* g, int enabled, const double* max_displacement, const double* stop_time) {
+    CHECK_CTX(g);
+    g->absorb_on = enabled != 0;
+    g->absorb_max_displacement = max_displacement ? *max_displacement : NAN;
+    g->absorb_stop_time = stop_time ? *stop_time : NAN;
+    return OPAL_OK;
+}
 opal_status opal_ref_photon_pair_depths(opal_ctx* g, int set, int64_t n, double* tau_abs, double* tau_st) {
     CHECK_CTX(g);
     finalize(g, g->photons);
@@ -1340,6 +1348,9 @@ opal_status opal_ref_run_steps(opal_ctx* g, int64_t nsteps, double t0, const dou
         advance(g, g->electrons);
         advance(g, g->ions);
         if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons);
+        if (g->absorb_on)                                                       // main.rs:246-248
+            absorb(g, t, std::isnan(g->absorb_max_displacement) ? nullptr : &g->absorb_max_displacement,
+                   std::isnan(g->absorb_stop_time) ? nullptr : &g->absorb_stop_time);
         if (photon_emission) {
             const double* a = (f3 && !std::isnan(f3[0])) ? &f3[0] : nullptr;
             const double* b = (f3 && !std::isnan(f3[1])) ? &f3[1] : nullptr;

@@ -93,6 +93,54 @@ constants:
  kT: 500 * eV
 """
 
+# a beam meeting a laser pulse head on, with photons travelling along (colliding_beams.yaml with a photon population
+# and absorption switched on; emission off so that the photon population changes through absorb only)
+ABSORPTION = """---
+control:
+ dx: 0.01*micro
+ nx: 400
+ xmin: -1*micro
+ start: -2.0e-6/c
+ end: -2.0e-6/c + 300.5 * 0.95 * 0.01*micro / c
+ current_deposition: false
+ n_outputs: 2
+
+qed:
+ photon_emission: false
+ photon_absorption: true
+
+electrons:
+ npc: 20
+ ne: dens * critical(omega) * step(x,xmin,xmax)
+ ux: -1000.0 * (1.0 + 0.01 * nrand)
+ uy: 0.0
+ uz: 0.0
+ output: [x, energy]
+
+ions:
+ npc: 0
+
+photons:
+ npc: 20
+ nph: dens * critical(omega) * step(x,xmin,xmax)
+ ux: -300.0 * (1.0 + urand)
+ uy: 0.3 * nrand
+ uz: 0.3 * nrand
+ output: [x, energy]
+
+laser:
+ Ey: (a0*m*c*omega/e) * sin(omega*(t-x/c)) * exp(-ln(2.0)*(omega*(t-x/c))^2/(2.0*pi^2*ncycles^2))
+ Ez: 0.0
+
+constants:
+ dens: {dens}
+ a0: 100.0
+ omega: 2*pi*c/0.8e-6
+ ncycles: 2.0
+ xmin: 1.0 * micro
+ xmax: 2.5 * micro
+"""
+
 
 def _run(driver, deck, tmp, name, extra=()):
     d = tmp / name
@@ -175,3 +223,31 @@ def test_two_ranks_two_gpus(tmp_path):
         assert abs(e2["electrons"] - e1["electrons"]) <= 1e-3 * e1["electrons"]
     # the field energy grows from noise: same order of magnitude
     assert 0.2 < _energies(two / "2_energy.dat")["em_field"] / _energies(one / "2_energy.dat")["em_field"] < 5.0
+
+
+def test_absorption_deck_gpu_vs_oracle(tmp_path):
+    """qed.photon_absorption: true (main.rs:246-248 -> interactions.rs:145).  At a physical density the pair probabilities
+    are ~1e-15 per step: no event, so the run is deterministic and the two drivers agree like any other deck while the
+    whole absorb path runs every step.  At an (unphysical) 1e17 times that density a few per cent of the photons are
+    absorbed or copied within the run; the two random streams differ, so the surviving photon weight is compared
+    statistically."""
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    a = _run(GPU_DRIVER, ABSORPTION.format(dens="1.0e-6"), tmp_path, "gpu")
+    b = _run(REF_DRIVER, ABSORPTION.format(dens="1.0e-6"), tmp_path, "ref")
+    for idx in (0, 1, 2):
+        ea, eb = _energies(a / f"{idx}_energy.dat"), _energies(b / f"{idx}_energy.dat")
+        for k in eb:
+            assert abs(ea[k] - eb[k]) <= 2e-6 * abs(eb[k]) + 1e-300, (idx, k, ea[k], eb[k])
+        for name in ("photon_x", "photon_energy", "electron_energy"):
+            ca, da = parse_fits(a / f"{idx}_{name}.fits")
+            cb, db = parse_fits(b / f"{idx}_{name}.fits")
+            assert float(ca["TOTAL"]) == pytest.approx(float(cb["TOTAL"]), rel=1e-12)
+            assert np.abs(da - db).sum() <= 5e-3 * np.abs(db).sum()
+    quiet = float(parse_fits(b / "2_photon_x.fits")[0]["TOTAL"]) / float(parse_fits(b / "0_photon_x.fits")[0]["TOTAL"])
+    c = _run(GPU_DRIVER, ABSORPTION.format(dens="1.0e11"), tmp_path, "gpu_dense")
+    d = _run(REF_DRIVER, ABSORPTION.format(dens="1.0e11"), tmp_path, "ref_dense")
+    left = [float(parse_fits(r / "2_photon_x.fits")[0]["TOTAL"]) / float(parse_fits(r / "0_photon_x.fits")[0]["TOTAL"]) for r in (c, d)]
+    assert left[0] < quiet - 0.01 and left[1] < quiet - 0.01, (left, quiet)        # photons were absorbed on both sides
+    assert abs(left[0] - left[1]) < 0.02, (left, quiet)                            # ~3000 photons, ~200 events: sigma ~ 0.005
+    ec, ed = _energies(c / "2_energy.dat"), _energies(d / "2_energy.dat")
+    assert abs(ec["electrons"] - ed["electrons"]) <= 2e-3 * ed["electrons"]         # the kicks are a per-mille effect here
