@@ -114,7 +114,7 @@ opal_status opal_qed_pair_cross_sections(int64_t n, const double* k4, const doub
 // The reference walks, photon by photon, the electrons of the photon's cell in store order, spending the photon's two
 // optical depths pair by pair and stopping at the first event.  Here one WARP takes one photon: the 32 lanes evaluate
 // the two cross sections of 32 electrons of the cell bucket at once (that is where the time goes: up to 40 pow() per
-// Airy function), then every lane replays the sequential optical-depth bookkeeping over those 32 partial probabilities
+// Airy function; the quadratures are shared out over the warp, see airy_warp in opal_absorb.cuh), then every lane replays the sequential optical-depth bookkeeping over those 32 partial probabilities
 // in store order -- the same subtractions in the same order as the reference, so the event, the electron it happens at
 // and the depths left over are those of the sequential loop.  Events are recorded per photon (no atomics); the kicks,
 // the copies made by stimulated emission and the deletion of absorbed photons follow in separate passes, as the
@@ -150,6 +150,9 @@ __global__ void __launch_bounds__(128) k_absorb_scan(GridDev g, BucketDev e, Pho
     const int last = *last_occupied;
     const double cdt_dx = OPAL_C * g.dt / g.dx;
     bool bad = false;
+    __shared__ double s_gl_x[60], s_gl_w[60];               // the quadrature nodes: lanes read different ones (see airy_warp)
+    if (threadIdx.x < 60) { s_gl_x[threadIdx.x] = c_gl_x[threadIdx.x]; s_gl_w[threadIdx.x] = c_gl_w[threadIdx.x]; }
+    __syncthreads();
     for (int i = warp; i < n; i += nwarps) {
         if (lane == 0) { kind[i] = 0; slot[i] = -1; }
         const double kx = ph.f[P_KX][i], ky = ph.f[P_KY][i], kz = ph.f[P_KZ][i];
@@ -168,15 +171,28 @@ __global__ void __launch_bounds__(128) k_absorb_scan(GridDev g, BucketDev e, Pho
         int what = 0;
         long long where = -1;
         for (int j0 = 0; j0 < ne && what == 0; j0 += 32) {
-            double pa = 0.0, ps = 0.0;
-            if (j0 + lane < ne) {
+            double prob[2] = {0.0, 0.0};                          // [0] absorption, [1] stimulated emission
+            double p4[4] = {1.0, 0.0, 0.0, 0.0}, chi_e = 0.0, w = 0.0;
+            const bool have = j0 + lane < ne;
+            if (have) {
                 const long long s = base + j0 + lane;
-                const double p4[4] = {e.f[F_GAMMA][s], e.f[F_UX][s], e.f[F_UY][s], e.f[F_UZ][s]};
-                const double chi_e = e.f[F_CHI][s], w = e.f[F_W][s];
-                double sigma;
-                if (pair_cross_section<+1>(k4, p4, chi_g, chi_e, &sigma)) { pa = w * cdt_dx * sigma; if (!(pa >= 0.0)) bad = true; }
-                if (!a.no_stimulated && pair_cross_section<-1>(k4, p4, chi_g, chi_e, &sigma)) { ps = w * cdt_dx * sigma; if (!(ps >= 0.0)) bad = true; }
+                p4[0] = e.f[F_GAMMA][s]; p4[1] = e.f[F_UX][s]; p4[2] = e.f[F_UY][s]; p4[3] = e.f[F_UZ][s];
+                chi_e = e.f[F_CHI][s];
+                w = e.f[F_W][s];
             }
+#pragma unroll 1
+            for (int which = 0; which < (a.no_stimulated ? 1 : 2); which++) {
+                PairPre pre = {false, 0.0, 0.0, 1.0};
+                if (have) pre = pair_prepare(which == 0 ? +1 : -1, k4, p4, chi_g, chi_e);
+                if (!__any_sync(FULLMASK, pre.ok)) continue;
+                double ai;
+                if (airy_warp(pre.ok, pre.zbar, s_gl_x, s_gl_w, lane, &ai)) {
+                    const double partial = w * cdt_dx * (pre.factor * ai / pre.denom);
+                    if (!(partial >= 0.0)) bad = true;
+                    if (which == 0) prob[0] = partial; else prob[1] = partial;
+                }
+            }
+            const double pa = prob[0], ps = prob[1];
             const int m = min(32, ne - j0);
             for (int l = 0; l < m; l++) {                        // Photon::interacts_with (photon.rs:312-362), in store order
                 const double prob_abs = __shfl_sync(FULLMASK, pa, l), prob_st = __shfl_sync(FULLMASK, ps, l);
