@@ -124,6 +124,9 @@ namespace opal {
 namespace pairs {
 
 constexpr unsigned FULLMASK = 0xffffffffu;
+#ifndef OPAL_ABSORB_MINBLK
+#define OPAL_ABSORB_MINBLK 8    // measured: 4 -> 8.06 ms, 6 -> 7.16 ms, 8 -> 6.76 ms per 16.8e6 pairs (64 regs, occupancy wins over the spills)
+#endif
 constexpr double PHOTON_E_ECRIT_CUTOFF = 1.0e-8;     // interactions.rs:146
 constexpr unsigned ABSORB_STREAM = 8u;               // Philox streams 8..11: apart from emit_radiation's 0..3
 
@@ -142,7 +145,7 @@ __global__ void k_last_occupied(BucketDev e, int* __restrict__ last) {
 }
 
 // kind[i]: 0 nothing, 1 absorbed, 2 stimulated emission; slot[i]: bucket slot of the electron it happened at
-__global__ void __launch_bounds__(128) k_absorb_scan(GridDev g, BucketDev e, PhotonDev ph, AbsorbArgs a, const int* __restrict__ last_occupied,
+__global__ void __launch_bounds__(128, OPAL_ABSORB_MINBLK) k_absorb_scan(GridDev g, BucketDev e, PhotonDev ph, AbsorbArgs a, const int* __restrict__ last_occupied,
                                                       int* __restrict__ kind, long long* __restrict__ slot, StatusDev* __restrict__ st) {
     const int lane = threadIdx.x & 31;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, nwarps = (gridDim.x * blockDim.x) >> 5;
