@@ -62,6 +62,7 @@ struct Buckets {
     int* d_count = nullptr;
     double* d_f[NF_FULL] = {nullptr};
     long long n_hint = 0;             // particle count at the last layout (sizing of the mover buffer)
+    bool movers_sized = false;        // the mover buffer has been sized for this population's crossing rate (size_movers_for)
 };
 
 struct Photons {
@@ -248,6 +249,44 @@ bool ensure_movers(opal_ctx* c, long long n_particles) {
     return true;
 }
 
+// Grow the segmented mover buffer to seg_cap records per segment.  Only between advances: its contents are consumed
+// by the scatter of the advance that wrote them.
+bool reserve_mover_segments(opal_ctx* c, long long seg_cap) {
+    if (seg_cap <= c->mover_seg_cap) return true;
+    if (seg_cap > (1ll << 30)) return fail(c, OPAL_ECAPACITY, "mover buffer: more than 2^30 records per segment");
+    if (c->d_movers) cudaFree(c->d_movers);
+    c->d_movers = nullptr; c->mover_seg_cap = 0;
+    CUB(cudaMalloc(&c->d_movers, (size_t)seg_cap * OPAL_MOVER_SEGMENTS * sizeof(opal_migrant)));
+    c->mover_seg_cap = (int)seg_cap;
+    return true;
+}
+
+// The first advance after an upload / generate: count on the device how many particles the coming push will move to
+// another cell (k_crossing_estimate) and make room for twice that -- a relativistic beam moves nearly every particle
+// every step, which the thermal default of ensure_movers (5 % of a large population) does not hold.  Later growth of
+// the crossing rate (a plasma heating up) is followed by grow_movers_after.
+bool size_movers_for(opal_ctx* c, int sp) {
+    Buckets& B = c->bk[sp];
+    if (!B.allocated || B.movers_sized) return true;
+    B.movers_sized = true;
+    if (B.n_hint == 0) return true;
+    c->k.crossing_estimate(c->stream, bdev(c, sp), c->g.dt / c->g.dx, c->d_energy + 5); c->launches++;
+    double h[2] = {0.0, 0.0};
+    CUB(cudaMemcpyAsync(h, c->d_energy + 5, 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    const double need = std::max(h[0], h[1]);
+    return reserve_mover_segments(c, (long long)std::ceil(2.0 * need / OPAL_MOVER_SEGMENTS) + 1024);
+}
+
+// after an advance whose status has been fetched: a segment more than half full doubles the room for the next one
+bool grow_movers_after(opal_ctx* c) {
+    const int* seg = reinterpret_cast<const int*>(c->h_status + 1);
+    int mx = 0;
+    for (int i = 0; i < OPAL_MOVER_SEGMENTS; i++) mx = std::max(mx, seg[i]);
+    if (2ll * mx <= c->mover_seg_cap) return true;
+    return reserve_mover_segments(c, 2ll * mx + 1024);
+}
+
 // per-cell mover strips for the lean fused electron kernel: MC records per cell, sized for the expected
 // crossing fraction (thermal plasma at 0.95 CFL: a few % of a cell's particles per step)
 bool ensure_cell_movers(opal_ctx* c, long long n_particles) {
@@ -317,7 +356,8 @@ bool reset_status(opal_ctx* c, bool keep_err) {
 
 // copy the status block to the host, translate sticky device-side assertion bits
 bool fetch_status(opal_ctx* c) {
-    CUB(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev), cudaMemcpyDeviceToHost, c->stream));
+    // the per-segment mover counts travel with it (4 KB): advance_charged sizes the mover buffer from them
+    CUB(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUB(cudaStreamSynchronize(c->stream));
     const unsigned e = c->h_status->err;
     if (e & ERR_CFL) return fail(c, OPAL_EASSERT_CFL, "push: assert!(dxi < 1.0) failed (electron.rs:313 / ion.rs:199 / photon.rs:164)");
@@ -390,6 +430,7 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
     B = Buckets();
     if (!alloc_buckets(c, B, demand, old.full)) return false;
     B.n_hint = total;
+    B.movers_sized = old.movers_sized;
     BucketDev src; src.ncell = ncell; src.start = old.d_start; src.count = old.d_count;
     for (int k = 0; k < NF_FULL; k++) src.f[k] = old.d_f[k];
     src.z_star = c->z_star; src.mass_number = c->mass_number;
@@ -479,6 +520,7 @@ bool insert_inbox(opal_ctx* c, int sp, int side, bool dep) {
 bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = false) {
     Buckets& B = c->bk[sp];
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
+    if (check && !size_movers_for(c, sp)) return false;      // (the unchecked callers -- graph capture -- size up front)
     if (!reset_status(c, true)) return false;
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
@@ -508,6 +550,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
         if (!fetch_status(c)) return false;
         c->last_gone[sp][0] = c->h_status->gone[0]; c->last_gone[sp][1] = c->h_status->gone[1];
         if (!handle_overflow(c, sp, dep)) return false;
+        if (!grow_movers_after(c)) return false;
     }
     return true;
 }
@@ -737,7 +780,7 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     for (int k = 0; k < 6; k++) c->eb_alt[k] = p + (10 + k) * n;
     CU(cudaMalloc(&c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int)));
     CU(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
-    CU(cudaMallocHost(&c->h_status, sizeof(StatusDev)));
+    CU(cudaMallocHost(&c->h_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int)));
     memset(c->h_status, 0, sizeof(StatusDev));
     CU(cudaMalloc(&c->d_energy, 8 * sizeof(double)));
     CU(cudaMallocHost(&c->h_energy, 8 * sizeof(double)));
@@ -1222,6 +1265,8 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     double t = t0;
     c->ke_fused = false;
     int64_t s0 = 0;
+    // room for the cell-crossing particles of a freshly loaded population (before any graph capture: it reads back a count)
+    if (!size_movers_for(c, OPAL_ELECTRON) || !size_movers_for(c, OPAL_ION)) return (opal_status)c->status;
     // launch-bound decks: replay the fused step as a CUDA graph (all but the last one or two steps, which also sum the
     // kinetic energy and report the leaver counts)
     const bool burst_ok = fused && !remote(c) && !c->timing && c->ph[0].cap == 0 && env_ll("OPAL_BURST", 1) != 0 &&

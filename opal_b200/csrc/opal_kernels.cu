@@ -1643,6 +1643,28 @@ __global__ void __launch_bounds__(BLOCK) k_kinetic(BucketDev b, double* out) {
     block_atomic_sum(acc, out);
 }
 
+// How many particles will change cell in the next push, to first order (velocity before the push): the mover buffer is
+// sized from this (ensure_movers in opal_host.cu).  v_x = c u_x / sqrt(1 + u^2) for electrons and ions alike.
+__global__ void __launch_bounds__(BLOCK) k_crossing_estimate(BucketDev b, double dt_over_dx, double* out2) {
+    const int lane = threadIdx.x & 31;
+    const int warps_total = gridDim.x * WARPS_PER_BLOCK;
+    double leaving = 0.0, expected = 0.0;
+    for (int c = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
+        const int n = b.count[c];
+        const long long base = b.start[c];
+        for (int i = lane; i < n; i += 32) {
+            const long long s = base + i;
+            const V3 u = {b.f[F_UX][s], b.f[F_UY][s], b.f[F_UZ][s]};
+            const double step = OPAL_C * u.x * rsqrt(1.0 + dot(u, u)) * dt_over_dx;
+            const double x = b.f[F_X][s] + step;
+            if (!(x >= 0.0 && x < 1.0)) leaving += 1.0;
+            expected += fmin(1.0, fabs(step));
+        }
+    }
+    block_atomic_sum(leaving, out2);
+    block_atomic_sum(expected, out2 + 1);
+}
+
 __global__ void __launch_bounds__(256) k_photon_energy(PhotonDev ph, double* out) {   // photon.rs:220-226
     const int n = *ph.n;
     double acc = 0.0;
@@ -1930,8 +1952,15 @@ static void l_copy_buckets(cudaStream_t s, const BucketDev& src, const BucketDev
     else k_copy_buckets<false><<<grid, BLOCK, 0, s>>>(src, dst);
 }
 
+static void l_crossing_estimate(cudaStream_t s, const BucketDev& b, double dt_over_dx, double* out2) {
+    cudaMemsetAsync(out2, 0, 2 * sizeof(double), s);
+    int gr = cell_grid(b.ncell); if (gr > 148 * 8) gr = 148 * 8;
+    k_crossing_estimate<<<gr, BLOCK, 0, s>>>(b, dt_over_dx, out2);
+}
+
 KernelTable table() {
     KernelTable t;
+    t.crossing_estimate = l_crossing_estimate;
     t.push = l_push; t.pull = l_pull; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;

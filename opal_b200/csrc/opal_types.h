@@ -125,6 +125,9 @@ struct KernelTable {
                        const double* r2, const double* r3, int classical, double* out3, StatusDev* st);
     void (*fields_at)(cudaStream_t, const GridDev&, int n, const long long* cell, const double* xi, double* out6, StatusDev* st);
     void (*copy_buckets)(cudaStream_t, const BucketDev& src, const BucketDev& dst, bool full);
+    // sizing of the mover buffer: out2[0] += particles whose ballistic step x + v_x dt/dx leaves [0,1),
+    // out2[1] += sum of min(1, |v_x| dt/dx) (the same count for positions uniform inside their cells)
+    void (*crossing_estimate)(cudaStream_t, const BucketDev&, double dt_over_dx, double* out2);
     // lean electrons: close the holes the fused step kernels leave (strip_count: the push's counter block)
     void (*compact_cells)(cudaStream_t, const BucketDev&, const int* strip_count);
     bool push_leaves_holes;     // the lean strip kernel was built with OPAL_PUSH_HOLES
