@@ -1312,95 +1312,144 @@ __device__ V3 v_rotate_around(V3 v, V3 ax, double theta) {                      
 
 constexpr int QED_TABLE_DOUBLES = 73 * 64;
 
-// K7: one warp per cell over the electron buckets; emission tables staged in shared memory
-// (37.4 KB); new photons appended with a warp-aggregated atomic.  Random numbers: Philox4x32-10
-// keyed by (seed, call index), counter = bucket slot, so a run is reproducible for a given
-// bucket layout irrespective of launch geometry.
-__global__ void __launch_bounds__(BLOCK) k_emit(GridDev g, BucketDev b, PhotonDev ph, StepParams sp, const double* __restrict__ tables_g,
-                                                 double t, double min_energy, double max_angle, double max_fl,
-                                                 uint64_t seed, uint64_t call_index, StatusDev* __restrict__ st) {
+// One emission (electron.rs:209-240 + the filters of interactions.rs:74-95) of the electron in bucket slot s of cell c,
+// whose optical depth has run out.  Random numbers: Philox4x32-10 keyed by (seed, call index), counter = bucket slot,
+// so a run is reproducible for a given bucket layout irrespective of launch geometry and of which thread does the work.
+// Returns true when the photon passes the filters (m is then filled in).
+__device__ __forceinline__ bool emit_one(const BucketDev& b, const StepParams& sp, const double* s_tab, long long s, int c, double t,
+                                         double min_energy, double max_angle, double max_fl, uint64_t seed, uint64_t call_index,
+                                         opal_migrant& m, bool& chi_err) {
+    double r_tau, r1, r2, r3, r4, r5, r6, r7;
+    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 0u, r_tau, r1);
+    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 1u, r2, r3);
+    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 2u, r4, r5);
+    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 3u, r6, r7);
+    b.f[F_TAU][s] = -log1p(-r_tau);                                    // Exp1 by inversion
+    double chi = b.f[F_CHI][s], gamma = b.f[F_GAMMA][s];
+    V3 u = {b.f[F_UX][s], b.f[F_UY][s], b.f[F_UZ][s]};
+    double smp[3];
+    bool ok = true;
+    if (sp.flags & OPAL_FLAG_NO_RADIATION_REACTION) classical_sample(chi, gamma, r1, r2, r3, smp);
+    else ok = quantum_sample(s_tab, chi, gamma, r1, r2, r3, smp);
+    if (!ok) { chi_err = true; return false; }
+    const double omega = smp[0], theta = smp[1], cphi = smp[2];
+    V3 par = v_normalize(u);                                           // electron.rs:221-228
+    V3 perp = v_rotate_around(v_orthogonal(par), par, cphi);
+    V3 k;
+    if (sp.flags & OPAL_FLAG_NO_BEAMING) k = omega * par;
+    else k = omega * (cos(theta) * par + sin(theta) * perp);
+    const double fl = 2.0 * (gamma * gamma) * theta * OPAL_C * OPAL_COMPTON_TIME / chi;   // :231
+    if (!(sp.flags & OPAL_FLAG_NO_RADIATION_REACTION)) {                // :234-239
+        u = u - k;
+        double ng = sqrt(1.0 + dot(u, u));
+        b.f[F_UX][s] = u.x; b.f[F_UY][s] = u.y; b.f[F_UZ][s] = u.z;
+        b.f[F_CHI][s] = chi * ng / gamma;
+        b.f[F_GAMMA][s] = ng;
+    }
+    // filters of interactions.rs:74-95 (NaN == None)
+    bool e_ok = isnan(min_energy) || sqrt(dot(k, k)) * OPAL_ME_MEV >= min_energy;
+    bool a_ok = true;
+    if (!isnan(max_angle)) {
+        V3 pm = OPAL_ME_MEV * k;
+        double mag = sqrt(pm.x * pm.x + pm.y * pm.y + pm.z * pm.z);
+        a_ok = acos(-pm.x / mag) <= max_angle;
+    }
+    bool f_ok = isnan(max_fl) || fl < max_fl;
+    if (!(e_ok && a_ok && f_ok)) return false;
+    m.cell = c; m.x = b.f[F_X][s]; m.prev_x = CUDART_NAN;              // Photon::create with dx = dt = 0
+    m.u[0] = k.x; m.u[1] = k.y; m.u[2] = k.z; m.weight = b.f[F_W][s];
+    m.gamma = sqrt(dot(k, k)); m.chi = 0.0; m.tau = -log1p(-r4); m.work = 0.0; m.y = 0.0; m.z = 0.0;
+    m.birth_time = t; m.pad[0] = -log1p(-r5); m.pad[1] = -log1p(-r6); (void)r7;   // tau_abs, tau_st (photon.rs:130-131)
+    return true;
+}
+
+// append the photons of a (converged) warp to the flat photon store with one atomic per warp
+__device__ __forceinline__ void emit_append(const PhotonDev& ph, bool store_photon, const opal_migrant& m, StatusDev* __restrict__ st) {
+    const int lane = threadIdx.x & 31;
+    const unsigned mk = __ballot_sync(FULLMASK, store_photon);
+    if (!mk) return;
+    int o = 0;
+    const int leader = __ffs(mk) - 1;
+    if (lane == leader) { o = atomicAdd(ph.n, __popc(mk)); atomicAdd(&st->n_new_photons, __popc(mk)); }
+    o = __shfl_sync(FULLMASK, o, leader);
+    if (store_photon) {
+        o += __popc(mk & ((1u << lane) - 1u));
+        if (o < ph.cap) {
+            ph.cell[o] = (int)m.cell;
+            ph.f[P_X][o] = m.x; ph.f[P_PREVX][o] = m.prev_x; ph.f[P_KX][o] = m.u[0]; ph.f[P_KY][o] = m.u[1]; ph.f[P_KZ][o] = m.u[2];
+            ph.f[P_W][o] = m.weight; ph.f[P_CHI][o] = 0.0; ph.f[P_TAU][o] = m.tau; ph.f[P_Y][o] = 0.0; ph.f[P_Z][o] = 0.0;
+            ph.f[P_BIRTH][o] = m.birth_time; ph.f[P_TAU_ABS][o] = m.pad[0]; ph.f[P_TAU_ST][o] = m.pad[1];
+        } else atomicOr(&st->err, ERR_CAPACITY);
+    }
+}
+
+#ifndef OPAL_EMIT_MB
+#define OPAL_EMIT_MB 4              // blocks per SM.  Measured (tools/bench_qed.py, 2e7 electrons, 10 % radiating per step), whole
+                                    // step: 1 -> 14.2 ms, 2 (128 registers, no spills) -> 11.2, 3 -> 12.5, 4 (64 registers, 0.7 KB
+                                    // of spills) -> 10.2: the optical-depth scan wants the resident warps more than the sampling
+                                    // wants the registers
+#endif
+#ifndef OPAL_EMIT_QCAP
+#define OPAL_EMIT_QCAP 1024         // queued emitters per block: 12 KB beside the 37.4 KB of tables
+#endif
+constexpr int EMIT_QCAP = OPAL_EMIT_QCAP;
+
+// K7: emission tables staged in shared memory (37.4 KB); new photons appended with a warp-aggregated atomic.
+// Only a few per cent of the electrons radiate in a step, so sampling where the optical depth is found spent would
+// leave ~3 lanes of 32 busy through the whole table inversion.  Instead every block works in rounds: (1) one warp per
+// cell reads the optical depths and queues the (slot, cell) of the spent ones in shared memory, (2) once a block's
+// worth has collected, all its threads sample one queued electron each.  A warp that finds the queue full samples its
+// electrons in place (every electron radiating: nothing to compact).  Which thread samples an electron does not
+// change its random numbers (keyed by slot); the order of the photon store is arbitrary as before.
+__global__ void __launch_bounds__(BLOCK, OPAL_EMIT_MB) k_emit(GridDev g, BucketDev b, PhotonDev ph, StepParams sp, const double* __restrict__ tables_g,
+                                                    double t, double min_energy, double max_angle, double max_fl,
+                                                    uint64_t seed, uint64_t call_index, StatusDev* __restrict__ st) {
     extern __shared__ double s_tab[];
+    long long* s_qs = reinterpret_cast<long long*>(s_tab + QED_TABLE_DOUBLES);
+    int* s_qc = reinterpret_cast<int*>(s_qs + EMIT_QCAP);
+    __shared__ int s_qn;
     for (int i = threadIdx.x; i < QED_TABLE_DOUBLES; i += blockDim.x) s_tab[i] = tables_g[i];
+    if (threadIdx.x == 0) s_qn = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * WARPS_PER_BLOCK;
     bool chi_err = false;
-    for (int c = blockIdx.x * WARPS_PER_BLOCK + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
-        const int n = b.count[c];
-        const long long base = b.start[c];
+    for (int c0 = blockIdx.x * WARPS_PER_BLOCK; c0 < b.ncell; c0 += warps_total) {     // block-uniform trip count
+        const int c = c0 + (threadIdx.x >> 5);
+        const int n = c < b.ncell ? b.count[c] : 0;
+        const long long base = c < b.ncell ? b.start[c] : 0;
         for (int k0 = 0; k0 < n; k0 += 32) {
             const int i = k0 + lane;
+            const long long s = base + i;
+            const bool spent = i < n && b.f[F_TAU][s] < 0.0;                          // electron.rs:209
+            const unsigned mk = __ballot_sync(FULLMASK, spent);
+            if (!mk) continue;
+            int o = 0;
+            if (lane == 0) o = atomicAdd(&s_qn, __popc(mk));
+            o = __shfl_sync(FULLMASK, o, 0) + __popc(mk & lt_mask);
             bool store_photon = false;
             opal_migrant m;
-            if (i < n) {
-                const long long s = base + i;
-                double tau = b.f[F_TAU][s];
-                if (tau < 0.0) {                                                       // electron.rs:209
-                    double r_tau, r1, r2, r3, r4, r5, r6, r7;
-                    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 0u, r_tau, r1);
-                    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 1u, r2, r3);
-                    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 2u, r4, r5);
-                    philox_uniform2(seed, (uint64_t)s, (uint32_t)call_index, 3u, r6, r7);
-                    b.f[F_TAU][s] = -log1p(-r_tau);                                    // Exp1 by inversion
-                    double chi = b.f[F_CHI][s], gamma = b.f[F_GAMMA][s];
-                    V3 u = {b.f[F_UX][s], b.f[F_UY][s], b.f[F_UZ][s]};
-                    double smp[3];
-                    bool ok = true;
-                    if (sp.flags & OPAL_FLAG_NO_RADIATION_REACTION) classical_sample(chi, gamma, r1, r2, r3, smp);
-                    else ok = quantum_sample(s_tab, chi, gamma, r1, r2, r3, smp);
-                    if (!ok) chi_err = true;
-                    else {
-                        const double omega = smp[0], theta = smp[1], cphi = smp[2];
-                        V3 par = v_normalize(u);                                       // electron.rs:221-228
-                        V3 perp = v_rotate_around(v_orthogonal(par), par, cphi);
-                        V3 k;
-                        if (sp.flags & OPAL_FLAG_NO_BEAMING) k = omega * par;
-                        else k = omega * (cos(theta) * par + sin(theta) * perp);
-                        const double fl = 2.0 * (gamma * gamma) * theta * OPAL_C * OPAL_COMPTON_TIME / chi;   // :231
-                        if (!(sp.flags & OPAL_FLAG_NO_RADIATION_REACTION)) {            // :234-239
-                            u = u - k;
-                            double ng = sqrt(1.0 + dot(u, u));
-                            b.f[F_UX][s] = u.x; b.f[F_UY][s] = u.y; b.f[F_UZ][s] = u.z;
-                            b.f[F_CHI][s] = chi * ng / gamma;
-                            b.f[F_GAMMA][s] = ng;
-                        }
-                        // filters of interactions.rs:74-95 (NaN == None)
-                        bool e_ok = isnan(min_energy) || sqrt(dot(k, k)) * OPAL_ME_MEV >= min_energy;
-                        bool a_ok = true;
-                        if (!isnan(max_angle)) {
-                            V3 pm = OPAL_ME_MEV * k;
-                            double mag = sqrt(pm.x * pm.x + pm.y * pm.y + pm.z * pm.z);
-                            a_ok = acos(-pm.x / mag) <= max_angle;
-                        }
-                        bool f_ok = isnan(max_fl) || fl < max_fl;
-                        if (e_ok && a_ok && f_ok) {
-                            store_photon = true;
-                            m.cell = c; m.x = b.f[F_X][s]; m.prev_x = CUDART_NAN;      // Photon::create with dx = dt = 0
-                            m.u[0] = k.x; m.u[1] = k.y; m.u[2] = k.z; m.weight = b.f[F_W][s];
-                            m.gamma = sqrt(dot(k, k)); m.chi = 0.0; m.tau = -log1p(-r4); m.work = 0.0; m.y = 0.0; m.z = 0.0;
-                            m.birth_time = t; m.pad[0] = -log1p(-r5); m.pad[1] = -log1p(-r6); (void)r7;   // tau_abs, tau_st (photon.rs:130-131)
-                        }
-                    }
-                }
+            if (spent) {
+                if (o < EMIT_QCAP) { s_qs[o] = s; s_qc[o] = c; }
+                else store_photon = emit_one(b, sp, s_tab, s, c, t, min_energy, max_angle, max_fl, seed, call_index, m, chi_err);
             }
-            const unsigned mk = __ballot_sync(FULLMASK, store_photon);
-            if (mk) {
-                int o = 0;
-                const int leader = __ffs(mk) - 1;
-                if (lane == leader) { o = atomicAdd(ph.n, __popc(mk)); atomicAdd(&st->n_new_photons, __popc(mk)); }
-                o = __shfl_sync(FULLMASK, o, leader);
-                if (store_photon) {
-                    o += __popc(mk & lt_mask);
-                    if (o < ph.cap) {
-                        ph.cell[o] = (int)m.cell;
-                        ph.f[P_X][o] = m.x; ph.f[P_PREVX][o] = m.prev_x; ph.f[P_KX][o] = m.u[0]; ph.f[P_KY][o] = m.u[1]; ph.f[P_KZ][o] = m.u[2];
-                        ph.f[P_W][o] = m.weight; ph.f[P_CHI][o] = 0.0; ph.f[P_TAU][o] = m.tau; ph.f[P_Y][o] = 0.0; ph.f[P_Z][o] = 0.0;
-                        ph.f[P_BIRTH][o] = m.birth_time; ph.f[P_TAU_ABS][o] = m.pad[0]; ph.f[P_TAU_ST][o] = m.pad[1];
-                    } else atomicOr(&st->err, ERR_CAPACITY);
-                }
-            }
+            if (__shfl_sync(FULLMASK, o, 31 - __clz(mk)) >= EMIT_QCAP) emit_append(ph, store_photon, m, st);   // warp-uniform
         }
+        __syncthreads();
+        const int nq = min(s_qn, EMIT_QCAP);
+        const bool last = c0 + warps_total >= b.ncell;
+        const int take = last ? nq : (nq / BLOCK) * BLOCK;                             // whole blocks' worth off the tail
+        for (int j0 = nq - take; j0 < nq; j0 += BLOCK) {
+            const int j = j0 + threadIdx.x;
+            bool store_photon = false;
+            opal_migrant m;
+            if (j < nq) store_photon = emit_one(b, sp, s_tab, s_qs[j], s_qc[j], t, min_energy, max_angle, max_fl, seed, call_index, m, chi_err);
+            emit_append(ph, store_photon, m, st);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_qn = nq - take;
+        __syncthreads();
     }
     if (chi_err) atomicOr(&st->err, ERR_CHI);
 }
@@ -1863,10 +1912,10 @@ static void l_emit(cudaStream_t s, const GridDev& g, const BucketDev& e, const P
                    const double* tables, double t, double min_energy, double max_angle, double max_fl, uint64_t seed,
                    uint64_t call_index, StatusDev* st) {
     static bool attr_set = false;
-    const int smem = QED_TABLE_DOUBLES * (int)sizeof(double);
+    const int smem = QED_TABLE_DOUBLES * (int)sizeof(double) + EMIT_QCAP * (int)(sizeof(long long) + sizeof(int));
     if (!attr_set) { cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_set = true; }
     int grid = cell_grid(e.ncell);
-    if (grid > 148 * 4) grid = 148 * 4;
+    if (grid > 148 * OPAL_EMIT_MB) grid = 148 * OPAL_EMIT_MB;
     k_emit<<<grid, BLOCK, smem, s>>>(g, e, ph, sp, tables, t, min_energy, max_angle, max_fl, seed, call_index, st);
 }
 
