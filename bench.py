@@ -97,7 +97,13 @@ def cpu_reference_run(nx, npc, steps, warmup, threads=None):
     from opal_b200.abi import ELECTRON, Slab
     cdll, oracle = load_oracle()
     cdll.opal_ref_max_threads.restype = ctypes.c_int
-    threads = threads or int(os.environ.get("OPAL_CPU_THREADS", cdll.opal_ref_max_threads()))
+    # all host cores this process may run on: torchrun exports OMP_NUM_THREADS=1 for N > 1, which would
+    # shrink omp_get_max_threads() to one thread although rank 0 alone runs the reference arm
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    threads = threads or int(os.environ.get("OPAL_CPU_THREADS", max(avail, cdll.opal_ref_max_threads())))
     cdll.opal_ref_set_threads(threads)
     rng = np.random.default_rng(12345)
     n = nx * npc

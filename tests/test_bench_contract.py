@@ -1,0 +1,32 @@
+"""bench.py's reference arm (the CPU leg the driver times beside the CUDA path) keeps its JSON contract
+and uses every host core it may run on, also when launched by torchrun (which exports OMP_NUM_THREADS=1)."""
+import json
+import os
+import pathlib
+import subprocess
+import sys
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+
+
+def _run(env_extra):
+    env = dict(os.environ, **env_extra)
+    out = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1",
+                          "--cpu-nx", "200", "--npc", "50"], capture_output=True, text=True, env=env, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    return out.stdout.strip()
+
+
+def test_reference_arm_line_and_thread_count():
+    line = json.loads(_run({"RANK": "0", "WORLD_SIZE": "2", "OMP_NUM_THREADS": "1"}).splitlines()[-1])
+    assert line["impl"] == "reference" and line["unit"] == "particle-steps/s" and line["higher_is_better"] is True
+    assert line["n_gpus"] == 2 and line["steps"] == 1 and line["warmup"] == 1
+    assert line["value"] > 0 and line["e2e"] == {"value": line["value"], "unit": line["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    cb = line["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["value"] == line["value"]
+    assert cb["cores"] == len(os.sched_getaffinity(0))
+    assert line["config"]["particles"] == 200 * 50
+
+
+def test_reference_arm_other_ranks_do_no_work():
+    assert _run({"RANK": "1", "WORLD_SIZE": "2"}) == ""
