@@ -273,7 +273,7 @@ def main():
             "clocks": clocks,
             "energies_J": energies,
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:   # the CPU leg is timed on rank 0 at N = 1 only
             cnx = min(args.cpu_nx, nx)
             rate, secs, threads, n = cpu_reference_run(cnx, npc, args.cpu_steps, 1)
             line["cpu_baseline"] = {"value": rate, "unit": "particle-steps/s", "cores": threads, "kind": "port",
