@@ -62,3 +62,10 @@ def test_product_never_references_the_oracle():
 def test_oracle_exports_every_symbol(oracle_cdll):
     for name in declared():
         assert hasattr(oracle_cdll, "opal_ref_" + name), name
+
+
+def test_integration_md_declares_every_symbol():
+    """INTEGRATION.md's extern "C" block (the reference-side binding a maintainer adds) lists every entry point"""
+    text = (ROOT / "INTEGRATION.md").read_text()
+    bound = set(re.findall(r"pub fn opal_(\w+)\(", text))
+    assert sorted(bound) == declared()
