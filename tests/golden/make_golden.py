@@ -12,6 +12,9 @@ Cases (all seeded, numpy default_rng):
   two_stream_small   periodic, 64 cells x 16 e-, 25 fused steps (main.rs:238-267), deposition on
   laser_slab         laser / absorbing boundaries, e- + C6+ slab, 60 call-by-call steps, the pulse reaches the slab
   single_push        one Vay push (electron.rs:268) and one Boris push (ion.rs:168) in random static fields
+  qed_functions      rate (photon_emission.rs:59) over both asymptotic branches and the table, Airy Ai (airy.rs:19) over
+                     its five ranges, absorption / stimulated-emission cross sections (photon_absorption.rs:17,
+                     stimulated_emission.rs:17) for 1500 seeded photon-electron pairs; keys q_*: compared element-wise
 """
 import ctypes
 import math
@@ -101,7 +104,19 @@ def single_push(abi):
     return out
 
 
-CASES = dict(two_stream_small=two_stream_small, laser_slab=laser_slab, single_push=single_push)
+def qed_functions(abi):
+    import kat
+    chi = np.logspace(-4, 3, 400)
+    x = np.concatenate([np.linspace(0.0, 2.0, 201), np.linspace(2.0, 49.99, 400)])
+    ai, ok = abi.airy(x)
+    assert ok.all()
+    k4, p4, cg, ce = kat.pair_cases(seed=51, n=1500)
+    sa, ss, oka, oks = abi.pair_cross_sections(k4, p4, cg, ce)
+    return dict(q_rate=abi.rate(chi, np.full_like(chi, 1234.5)), q_airy=ai, q_sigma_abs=sa, q_sigma_st=ss,
+                q_abs_defined=oka.astype(np.int64), q_st_defined=oks.astype(np.int64))
+
+
+CASES = dict(two_stream_small=two_stream_small, laser_slab=laser_slab, single_push=single_push, qed_functions=qed_functions)
 
 
 def main():
