@@ -1,0 +1,156 @@
+"""Invariants for the parts of the path that no reference test pins (fields_at / weight, flux / deposit,
+sort + migration, Ion::push).  Each one is a property of the reference's formulas that holds independently of the
+restatement, so it checks the oracle on the CPU and -- the same function, `-m gpu` -- the CUDA path.
+
+  * gather (yee.rs:499-529, weight yee.rs:140-149): the order-2 spline weights sum to one and reproduce a field that
+    is linear in x exactly, at the staggered position of every component;
+  * deposit (yee.rs:551-641, flux yee.rs:185-204): jx satisfies the discrete continuity equation against the CORRECT
+    spline charge density (not the reference's rho, whose fourth stencil point is misplaced: quirk Q2);
+  * advance (particle/mod.rs:247-376): the periodic ring keeps every particle (the multiset of weights is unchanged),
+    cells come back sorted and inside the slab, offsets inside [0, 1);
+  * Ion::push (ion.rs:168-214): gamma(t) in a static electric field and |u| in a static magnetic field, the two
+    analytic checks the reference holds for electrons (electron.rs:401-436) with q, M swapped.
+"""
+import math
+
+import numpy as np
+import pytest
+
+from opal_b200.abi import BDY_INTERNAL, ELECTRON, ION, Slab
+from opal_b200.constants import ELEMENTARY_CHARGE, PROTON_MASS, SPEED_OF_LIGHT
+import pic_cases as pc
+
+C = SPEED_OF_LIGHT
+BACKENDS = [pytest.param("oracle", id="oracle"), pytest.param("gpu", id="cuda", marks=pytest.mark.gpu)]
+
+
+@pytest.fixture(params=BACKENDS)
+def abi(request):
+    return request.getfixturevalue(request.param)
+
+
+def spline(s):
+    """Cell::weight (yee.rs:140-149)"""
+    s = np.abs(s)
+    return np.where(s < 0.5, 0.75 - s * s, np.where(s <= 1.5, 1.125 - 1.5 * s + 0.5 * s * s, 0.0))
+
+
+def test_gather_reproduces_constant_and_linear_fields(abi):
+    nx, dx = 48, 2.0
+    s = Slab(abi, nx, 0.0, dx)
+    f = s.fields()
+    left = int(np.argmin(np.abs(f[:, 0] - 0.0)))          # row of cell 0 (cell.x == xmin, yee.rs:296)
+    j = np.arange(f.shape[0]) - left                       # cell index of every row
+    a = np.array([3.0, -2.0, 0.5, 7.0, 1.5, -4.0])
+    b = np.array([0.25, 0.5, -0.125, 0.0, 2.0, -1.0])      # Bx is never staggered: its slope stays 0 (yee.rs:513)
+    # staggered positions in units of dx: Ex, By, Bz at the cell centre j + 1/2; Ey, Ez at the node j
+    pos = {5: j + 0.5, 6: j, 7: j, 8: j, 9: j + 0.5, 10: j + 0.5}
+    for k in range(6):
+        f[:, 5 + k] = a[k] + b[k] * pos[5 + k]
+    s.set_fields(f)
+    rng = np.random.default_rng(5)
+    cell = rng.integers(2, nx - 2, 4000)
+    xi = rng.random(4000)
+    xi[:4] = [0.0, 0.5, np.nextafter(1.0, 0.0), np.nextafter(0.5, 0.0)]
+    E, B = s.fields_at(cell, xi)
+    got = np.concatenate([E, B], axis=1)
+    x = cell + xi
+    for k in range(6):
+        want = a[k] + b[k] * x if k != 3 else np.full_like(x, a[3])
+        assert np.max(np.abs(got[:, k] - want)) <= 1e-13 * np.max(np.abs(want)), k
+    s.close()
+
+
+def test_deposit_obeys_the_continuity_equation(abi):
+    """(rho_new - rho_old) / dt == -(jx_i - jx_{i-1}) / dx with rho the order-2 spline density at the nodes"""
+    nx, npc, dx = 80, 24, 500.0
+    s = Slab(abi, nx, 0.0, dx)
+    cells = np.arange(20, 60)                               # away from the edges: no ghost-cell folding involved
+    p = pc.thermal_particles(nx, npc, dx, 0.2, seed=9, cells=cells)
+    pc.upload(s, ELECTRON, p)
+    s.advance(ELECTRON)
+    s.clear()
+    s.deposit(ELECTRON)
+    f = s.fields()
+    left = int(np.argmin(np.abs(f[:, 0] - 0.0)))
+    d = s.download(ELECTRON)
+    q = d["weight"] * (-ELEMENTARY_CHARGE)
+    node = np.arange(f.shape[0]) - left
+
+    def rho(pos):
+        out = np.zeros(f.shape[0])
+        for k in range(-2, 4):
+            idx = np.floor(pos).astype(np.int64) + k
+            np.add.at(out, idx + left, q * spline(idx - pos) / dx)
+        return out
+
+    new = d["cell"] + d["x"]
+    old = d["cell"] + d["prev_x"]                           # prev_x is relative to the NEW cell (electron.rs:311-329)
+    assert np.any(np.floor(new) != np.floor(old)), "no particle crossed a cell: the test would not see the flux split"
+    lhs = (rho(new) - rho(old)) / s.dt
+    jx = f[:, 2]
+    rhs = -(jx - np.roll(jx, 1)) / dx
+    scale = np.max(np.abs(jx)) / dx
+    assert scale > 0
+    assert np.max(np.abs(lhs - rhs)) <= 1e-12 * scale
+    s.close()
+
+
+def test_periodic_advance_keeps_every_particle_sorted_and_inside(abi):
+    nx, npc, dx = 40, 30, 500.0
+    s = Slab(abi, nx, 0.0, dx)
+    p = pc.thermal_particles(nx, npc, dx, 0.5, seed=13)     # hot: ~20 % of the particles change cell every step
+    pc.upload(s, ELECTRON, p)
+    crossed = 0
+    for _ in range(25):
+        s.advance(ELECTRON)
+        gl, gr = s.last_leavers(ELECTRON)
+        crossed += gl + gr
+    d = s.download(ELECTRON)
+    assert d["cell"].size == nx * npc
+    assert np.array_equal(np.sort(d["weight"]), np.sort(p["weight"]))      # nobody lost, nobody duplicated
+    assert np.all(np.diff(d["cell"]) >= 0)                                   # mod.rs:288
+    assert d["cell"].min() >= 0 and d["cell"].max() < nx
+    assert np.all((d["x"] >= 0.0) & (d["x"] < 1.0))
+    assert crossed > 0, "nobody wrapped around the ring"
+    s.close()
+
+
+def _single_ion(abi, z, a, u0, E, B, dx, dt, nsteps, nx=64):
+    g = Slab(abi, nx, 0.0, dx, dt, BDY_INTERNAL, BDY_INTERNAL)
+    f = g.fields()
+    f[:, 5:8] = E
+    f[:, 8:11] = B
+    g.set_fields(f)
+    g.set_ion(z, a)
+    g.upload(ION, [nx // 2], [0.0], [u0[0]], [u0[1]], [u0[2]], [1.0])
+    for _ in range(nsteps):
+        g.advance(ION)
+    p = g.download(ION)
+    g.close()
+    return p
+
+
+def test_ion_in_a_static_electric_field(abi):
+    """electron.rs:424-436 with q = Z e, M = A m_p: gamma(t) = sqrt(1 + (q E t / M c)^2); Boris is exact here"""
+    z, a, e0, dt, n = 6.0, 12.0, 1.0e6, 1.0e-9, 100
+    p = _single_ion(abi, z, a, (0.0, 0.0, 0.0), (e0, 0.0, 0.0), (0.0, 0.0, 0.0), 1.0, dt, n)
+    ux = z * ELEMENTARY_CHARGE * e0 * n * dt / (a * PROTON_MASS * C)
+    assert abs(p["ux"][0] - ux) <= 1e-12 * ux
+    assert abs(p["gamma"][0] - math.sqrt(1.0 + ux * ux)) <= 1e-12
+    assert p["uy"][0] == 0.0 and p["uz"][0] == 0.0
+
+
+def test_ion_gyration_conserves_energy_and_closes_the_orbit(abi):
+    """electron.rs:401-418 with q, M swapped: one gyro-period in 100 steps; |u| is conserved to round-off by the Boris
+    rotation and the momentum comes back to its start within the scheme's O(dt^2) phase error"""
+    z, a, b0, u0 = 1.0, 1.0, 1.0, 1.0
+    g0 = math.sqrt(1.0 + u0 * u0)
+    omega = z * ELEMENTARY_CHARGE * b0 / (g0 * a * PROTON_MASS)
+    dt = 0.01 * 2.0 * math.pi / omega
+    dx = 10.0 * C * dt                                       # far below the CFL assert (ion.rs: dxi < 1)
+    p = _single_ion(abi, z, a, (u0, 0.0, 0.0), (0.0, 0.0, 0.0), (0.0, 0.0, b0), dx, dt, 100)
+    assert abs(p["gamma"][0] - g0) <= 1e-12
+    assert abs(math.hypot(p["ux"][0], p["uy"][0]) - u0) <= 1e-12
+    assert abs(p["ux"][0] - u0) < 1e-3 and abs(p["uy"][0]) < 5e-3
+    assert p["uz"][0] == 0.0
