@@ -1,5 +1,5 @@
 """Invariants for the parts of the path that no reference test pins (fields_at / weight, flux / deposit,
-sort + migration, Ion::push).  Each one is a property of the reference's formulas that holds independently of the
+sort + migration, Ion::push, Photon::push, sample).  Each one is a property of the reference's formulas that holds independently of the
 restatement, so it checks the oracle on the CPU and -- the same function, `-m gpu` -- the CUDA path.
 
   * gather (yee.rs:499-529, weight yee.rs:140-149): the order-2 spline weights sum to one and reproduce a field that
@@ -9,7 +9,10 @@ restatement, so it checks the oracle on the CPU and -- the same function, `-m gp
   * advance (particle/mod.rs:247-376): the periodic ring keeps every particle (the multiset of weights is unchanged),
     cells come back sorted and inside the slab, offsets inside [0, 1);
   * Ion::push (ion.rs:168-214): gamma(t) in a static electric field and |u| in a static magnetic field, the two
-    analytic checks the reference holds for electrons (electron.rs:401-436) with q, M swapped.
+    analytic checks the reference holds for electrons (electron.rs:401-436) with q, M swapped;
+  * Photon::push (photon.rs:150-183): ballistic motion at c, k untouched, chi from the transverse field;
+  * photon_emission::sample (photon_emission.rs:129): the sampled spectrum's mean energy times the (reference-pinned)
+    rate is the quantum synchrotron power.
 """
 import math
 
@@ -154,3 +157,61 @@ def test_ion_gyration_conserves_energy_and_closes_the_orbit(abi):
     assert abs(math.hypot(p["ux"][0], p["uy"][0]) - u0) <= 1e-12
     assert abs(p["ux"][0] - u0) < 1e-3 and abs(p["uy"][0]) < 5e-3
     assert p["uz"][0] == 0.0
+
+
+@pytest.mark.parametrize("chi", [0.0101, 0.1, 1.0, 10.0, 50.0])
+def test_sampled_spectrum_carries_the_radiated_power(abi, chi):
+    """photon_emission::sample (qed/photon_emission.rs:129) has no live reference test (the intended ones are commented
+    out, :338-410).  Its first moment is tied to `rate` -- which the reference does pin (:299-336) -- by the quantum
+    synchrotron power P = 2/3 alpha chi^2 g(chi) m c^2 / tau_C:  <omega> rate = P, so
+    <omega / m c^2> = 4 pi chi gamma g(chi) / (3 sqrt3 h(chi)) with h recovered from rate() and g the Gaunt factor
+    (Baier et al.'s fit, good to 2 %).  Also: a photon never takes more than the electron has."""
+    from opal_b200.constants import ALPHA_FINE, COMPTON_TIME
+    n, gamma = 100_000, 1000.0
+    rng = np.random.default_rng(17)
+    out = abi.sample(np.full(n, chi), gamma, rng.random(n), rng.random(n), rng.random(n))
+    omega = out[:, 0]
+    assert np.all(omega > 0.0) and np.all(omega < gamma)
+    h = abi.rate(np.array([chi]), np.array([gamma]))[0] * 2.0 * math.pi * gamma * COMPTON_TIME / (math.sqrt(3.0) * ALPHA_FINE * chi)
+    g = (1.0 + 4.8 * (1.0 + chi) * math.log(1.0 + 1.7 * chi) + 2.44 * chi * chi) ** (-2.0 / 3.0)
+    want = 4.0 * math.pi / (3.0 * math.sqrt(3.0)) * chi * gamma * g / h
+    assert abs(omega.mean() / want - 1.0) < 0.03, (chi, omega.mean(), want)
+    assert np.all((out[:, 1] >= 0.0) & (out[:, 1] <= math.pi))            # polar angle
+    assert np.all((out[:, 2] >= 0.0) & (out[:, 2] < 2.0 * math.pi))        # azimuth = 2 pi r3
+
+
+def test_photons_move_at_c_and_see_the_transverse_field(abi):
+    """Photon::push (photon.rs:150-183): ballistic at c along k, k unchanged; chi = |k0 E + c k x B|_perp / E_crit
+    (:159) -- for k along x in a uniform E_y that is k0 E_y / E_crit, and it vanishes when the wave's own field
+    configuration E_y = c B_z travels with the photon."""
+    from opal_b200.abi import PHOTON
+    from opal_b200.constants import CRITICAL_FIELD
+    nx, dx, nsteps = 64, 1.0e-8, 20
+    ey = 1.0e12
+    for bz in (0.0, ey / C):
+        s = Slab(abi, nx, 0.0, dx)
+        f = s.fields()
+        f[:, 6] = ey
+        f[:, 10] = bz
+        s.set_fields(f)
+        k = np.array([[50.0, 0.0, 0.0], [30.0, 40.0, 0.0], [-20.0, 0.0, 21.0]])
+        cell = np.array([10, 20, 40])
+        x0 = np.array([0.25, 0.5, 0.75])
+        s.upload(PHOTON, cell, x0, k[:, 0], k[:, 1], k[:, 2], 1.0 + 1e-9 * np.arange(3))
+        for _ in range(nsteps):
+            s.advance(PHOTON)
+        d = pc.canon(s.download(PHOTON))
+        k0 = np.linalg.norm(k, axis=1)
+        order = np.argsort(cell + x0 + C * k[:, 0] / k0 * nsteps * s.dt / dx)      # canon() sorts by cell
+        k, k0, cell, x0 = k[order], k0[order], cell[order], x0[order]
+        want = cell + x0 + C * k[:, 0] / k0 * nsteps * s.dt / dx
+        assert np.max(np.abs(d["cell"] + d["x"] - want)) < 1e-10
+        assert np.array_equal(d["ux"], k[:, 0]) and np.array_equal(d["uy"], k[:, 1]) and np.array_equal(d["uz"], k[:, 2])
+        assert np.max(np.abs(d["y"] - C * k[:, 1] / k0 * nsteps * s.dt)) <= 1e-12 * C * nsteps * s.dt
+        # |k0 E + c k x B|^2 - (E.k)^2 with E = (0, ey, 0), B = (0, 0, bz)
+        fx, fy, fz = C * k[:, 1] * bz, k0 * ey - C * k[:, 0] * bz, np.zeros(3)
+        chi = np.sqrt(np.maximum(fx * fx + fy * fy + fz * fz - (ey * k[:, 1]) ** 2, 0.0)) / CRITICAL_FIELD
+        assert np.max(np.abs(d["chi"] - chi)) <= 1e-9 * np.max(chi) + 1e-30
+        if bz != 0.0:
+            assert d["chi"][np.argmax(k[:, 0])] <= 1e-7 * np.max(chi)      # co-propagating with the wave: no quantum parameter
+        s.close()
