@@ -12,7 +12,9 @@ restatement, so it checks the oracle on the CPU and -- the same function, `-m gp
     analytic checks the reference holds for electrons (electron.rs:401-436) with q, M swapped;
   * Photon::push (photon.rs:150-183): ballistic motion at c, k untouched, chi from the transverse field;
   * photon_emission::sample (photon_emission.rs:129): the sampled spectrum's mean energy times the (reference-pinned)
-    rate is the quantum synchrotron power.
+    rate is the quantum synchrotron power;
+  * Electron::radiate (electron.rs:208-251): each stored photon's momentum is exactly its emitter's recoil, it is born
+    at the emitter's (cell, x, weight), and electrons that do not emit are left bit-for-bit alone.
 """
 import math
 
@@ -215,3 +217,46 @@ def test_photons_move_at_c_and_see_the_transverse_field(abi):
         if bz != 0.0:
             assert d["chi"][np.argmax(k[:, 0])] <= 1e-7 * np.max(chi)      # co-propagating with the wave: no quantum parameter
         s.close()
+
+
+def test_emission_conserves_momentum_photon_by_photon(abi):
+    """Electron::radiate (electron.rs:208-251): the recoil is u -= k (:235) and the photon inherits the electron's
+    (cell, x, weight) (:243).  Every electron carries a unique weight here, so each stored photon is matched to its
+    emitter: u_before - u_after == k, gamma_after == sqrt(1 + u_after^2), and electrons that did not emit are untouched."""
+    from opal_b200.abi import PHOTON
+    from opal_b200.constants import CRITICAL_FIELD
+    nx, dx, n, gamma0 = 64, 1.0e-8, 3000, 1000.0
+    s = Slab(abi, nx, 0.0, dx, seed=5)
+    e0 = 0.8 * CRITICAL_FIELD / (2.0 * gamma0)
+    f = s.fields()
+    f[:, 6] = e0
+    f[:, 10] = e0 / C
+    s.set_fields(f)
+    rng = np.random.default_rng(23)
+    w = 1.0 + 1.0e-9 * np.arange(n)
+    tau = np.where(np.arange(n) % 3 == 0, 50.0, 1.0e-9)      # two thirds run out of optical depth in the first push
+    s.upload(ELECTRON, rng.integers(0, nx, n), rng.random(n), -gamma0 * (1.0 + 0.01 * rng.standard_normal(n)), np.zeros(n), np.zeros(n), w, tau)
+    s.advance(ELECTRON)
+    before = s.download(ELECTRON)
+    s.emit_radiation(0.0, None, None, None)
+    after = s.download(ELECTRON)
+    ph = s.download(PHOTON)
+    ob, oa = np.argsort(before["weight"]), np.argsort(after["weight"])
+    before = {k: v[ob] for k, v in before.items()}
+    after = {k: v[oa] for k, v in after.items()}
+    assert np.array_equal(before["weight"], w) and np.array_equal(after["weight"], w)
+    idx = np.rint((ph["weight"] - 1.0) * 1.0e9).astype(np.int64)
+    assert np.array_equal(w[idx], ph["weight"]) and np.unique(idx).size == idx.size        # at most one photon per electron and call
+    assert idx.size == np.count_nonzero(tau < 1.0) and np.all(tau[idx] < 1.0)
+    for c, kc in (("ux", "ux"), ("uy", "uy"), ("uz", "uz")):
+        recoil = before[c][idx] - after[c][idx]
+        assert np.max(np.abs(recoil - ph[kc])) <= 1e-12 * gamma0, c
+    u2 = after["ux"] ** 2 + after["uy"] ** 2 + after["uz"] ** 2
+    assert np.max(np.abs(after["gamma"] - np.sqrt(1.0 + u2))) <= 1e-12 * gamma0
+    assert np.array_equal(ph["cell"], before["cell"][idx]) and np.array_equal(ph["x"], before["x"][idx])
+    quiet = np.setdiff1d(np.arange(n), idx)
+    for c in ("ux", "uy", "uz", "gamma", "x"):
+        assert np.array_equal(before[c][quiet], after[c][quiet]), c
+    k0 = np.sqrt(ph["ux"] ** 2 + ph["uy"] ** 2 + ph["uz"] ** 2)
+    assert np.all(k0 > 0.0) and np.all(k0 < before["gamma"][idx])
+    s.close()
