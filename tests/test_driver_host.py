@@ -340,3 +340,35 @@ def test_loader_draw_order_and_moments(host):
     assert n2 == n and np.array_equal(keep[2][:n], ux) and np.array_equal(keep[6][:n], tau)
     n3 = host.opal_drv_load(y.encode(), b"electrons", b"ne", 400, 100, 0.0, 100.0, 6, 1, cap, *(a.ctypes.data for a in keep))
     assert n3 == n and not np.array_equal(keep[2][:n], ux)
+
+
+def test_shipped_example_decks(host, tmp_path):
+    """examples/*.yaml (our own decks for BASELINE configs 4 and 5, in opal's schema): the two full-size ones parse to the
+    bench workload; the small one runs end to end through the driver built over the CPU oracle and conserves energy."""
+    c, e, me = 2.997925e8, 1.602177e-19, 9.109383e-31
+    ex = ROOT / "examples"
+    big = (ex / "thermal_bench.yaml").read_text()
+    assert read(host, big, "control", "nx")[1] == 1.0e6 and read(host, big, "electrons", "npc")[1] == 1000.0
+    assert read(host, big, "control", "end")[1] == pytest.approx(110 * 0.95 * 500 / c, rel=1e-15)
+    u_th = math.sqrt(500 * e / (me * c * c))
+    assert u_th == pytest.approx(0.03128, rel=1e-3)                       # bench.py's U_TH, hole_boring's kT
+    assert read(host, big, "electrons", "uy", kind=5, x=0.0, y=0.3, z=-2.0)[1] == pytest.approx(-2.0 * u_th, rel=1e-15)
+    assert read(host, big, "control", "balance", kind=2)[:2] == (0, 0.0)
+    ws = (ex / "two_stream_weak_scaling.yaml").read_text()
+    assert read(host, ws, "control", "nx")[1] == 8.0e6
+    d = 2.5e-24 / (me * c)
+    assert read(host, ws, "electrons", "ux", kind=5, x=0.0, y=0.75, z=1.0)[1] == d * 1.001
+    assert read(host, ws, "electrons", "ux", kind=5, x=0.0, y=0.25, z=1.0)[1] == -d * 1.001
+
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    (tmp_path / "thermal_small.yaml").write_text((ex / "thermal_small.yaml").read_text())
+    out = subprocess.run([str(ROOT / "oracle" / "opal_ref_driver"), str(tmp_path / "thermal_small.yaml")], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    en = []
+    for idx in (0, 1, 2):                                                   # 220 steps, 2 outputs
+        for name in ("grid.dat", "electron_x-px.fits", "electron_energy.fits", "electron_px-py.fits"):
+            assert (tmp_path / f"{idx}_{name}").exists(), (idx, name)
+        row = dict(line.split() for line in (tmp_path / f"{idx}_energy.dat").read_text().splitlines())
+        en.append(float(row["em_field"]) + float(row["electrons"]))
+    assert not (tmp_path / "3_energy.dat").exists()
+    assert en[0] > 0 and abs(en[2] / en[0] - 1.0) < 1e-4                    # a quiet thermal plasma keeps its energy
