@@ -170,7 +170,11 @@ int run(const Options& opt, Ranks& ranks) {
     double x2 = 0.0;
     ck(OPAL_FN(laser_x)(ctx, &x2), ctx, "laser_x");
     if (id == 0 && !opt.quiet)
+#ifdef OPAL_ORACLE_BUILD          // oracle/opal_ref_driver: the same driver linked over the CPU restatement (test infrastructure)
+        std::printf("Running %d task%s on the CPU oracle (libopal_oracle: one x-slab per task)...\n", np, np > 1 ? "s" : "");
+#else
         std::printf("Running %d task%s on %d GPU%s (libopal_b200: one x-slab per GPU)...\n", np, np > 1 ? "s" : "", np, np > 1 ? "s" : "");
+#endif
 
     auto write_all = [&](size_t index) {                                             // main.rs:218-222
         write_grid(ctx, output_dir, index, ranks);
