@@ -117,6 +117,12 @@ int run(const Options& opt, Ranks& ranks) {
     const int device = opt.device >= 0 ? opt.device + id : id;
     ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, flags), nullptr, "opal_create");
     ranks.connect(ctx);                                                             // NCCL ring (np > 1)
+    const bool staged = ranks.host_staged();                                        // no communicator in the library (ranks.h)
+    if (staged && lean) {                                                           // a lean context takes opal_run_steps only
+        OPAL_FN(destroy)(ctx);
+        ctx = nullptr;
+        ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, 0u), nullptr, "opal_create");
+    }
 
     // ---- particle initialisation (main.rs:117-168) ----
     auto upload = [&](int species, const ParticleArrays& p) {
@@ -190,6 +196,58 @@ int run(const Options& opt, Ranks& ranks) {
     filters[1] = has_amax ? photon_angle_max : nan;
     filters[2] = has_fl ? max_formation_length : nan;
 
+    // One iteration of main.rs:238-267 call by call, the driver moving leavers (mod.rs:296-373) and halo strips
+    // (yee.rs:353-409) between the slabs itself: the path of a host that keeps its own p2p (host_staged(), ranks.h).
+    const bool has_side[2] = {!(id == 0 && left_bdy != OPAL_BDY_INTERNAL), !(id == np - 1 && right_bdy != OPAL_BDY_INTERNAL)};   // yee.rs:329-343
+    auto staged_advance = [&](int species) {
+        ck(OPAL_FN(advance)(ctx, species), ctx, "advance");
+        std::vector<char> out[2], in[2];
+        for (int side = 0; side < 2; side++) {
+            if (!has_side[side]) continue;
+            int64_t cap = 4096, n = 0;
+            for (;;) {
+                out[side].resize((size_t)cap * sizeof(opal_migrant));
+                const opal_status st = OPAL_FN(migrants_take)(ctx, species, side, cap, &n, reinterpret_cast<opal_migrant*>(out[side].data()));
+                if (st == OPAL_ECAPACITY && n > cap) { cap = n; continue; }
+                ck(st, ctx, "migrants_take");
+                break;
+            }
+            out[side].resize((size_t)n * sizeof(opal_migrant));
+        }
+        ranks.ring_exchange(out[OPAL_LEFT], out[OPAL_RIGHT], in[OPAL_LEFT], in[OPAL_RIGHT]);
+        for (int side = 0; side < 2; side++)
+            if (has_side[side] && !in[side].empty())
+                ck(OPAL_FN(migrants_give)(ctx, species, side, (int64_t)(in[side].size() / sizeof(opal_migrant)),
+                                          reinterpret_cast<const opal_migrant*>(in[side].data())), ctx, "migrants_give");
+    };
+    auto staged_step = [&](double tj, double lyj, double lzj) {
+        if (epc > 0) staged_advance(OPAL_ELECTRON);
+        if (ipc > 0) staged_advance(OPAL_ION);
+        if (photons_on) staged_advance(OPAL_PHOTON);
+        if (photon_absorption)
+            ck(OPAL_FN(absorb)(ctx, tj, has_dqa ? &disable_qed_after : nullptr, has_daa ? &disable_absorption_after : nullptr), ctx, "absorb");
+        if (photon_emission)
+            ck(OPAL_FN(emit_radiation)(ctx, tj, has_emin ? &photon_energy_min : nullptr, has_amax ? &photon_angle_max : nullptr,
+                                       has_fl ? &max_formation_length : nullptr), ctx, "emit_radiation");
+        if (current_deposition) {
+            ck(OPAL_FN(clear)(ctx), ctx, "clear");
+            if (epc > 0) ck(OPAL_FN(deposit)(ctx, OPAL_ELECTRON), ctx, "deposit");
+            if (ipc > 0) ck(OPAL_FN(deposit)(ctx, OPAL_ION), ctx, "deposit");
+        }
+        std::vector<char> out[2], in[2];
+        for (int side = 0; side < 2; side++) {
+            if (!has_side[side]) continue;
+            out[side].resize(8 * 11 * sizeof(double));
+            ck(OPAL_FN(halo_take)(ctx, side, reinterpret_cast<double*>(out[side].data())), ctx, "halo_take");
+        }
+        ranks.ring_exchange(out[OPAL_LEFT], out[OPAL_RIGHT], in[OPAL_LEFT], in[OPAL_RIGHT]);
+        for (int side = 0; side < 2; side++)
+            if (has_side[side] && in[side].size() == 8 * 11 * sizeof(double))
+                ck(OPAL_FN(halo_give)(ctx, side, reinterpret_cast<const double*>(in[side].data())), ctx, "halo_give");
+        ck(OPAL_FN(synchronize)(ctx, tj, lyj, lzj), ctx, "synchronize");
+        ck(OPAL_FN(field_advance)(ctx), ctx, "field_advance");
+    };
+
     const auto wall0 = std::chrono::steady_clock::now();
     double loop_seconds = 0.0;
     int64_t particle_steps = 0;
@@ -213,6 +271,10 @@ int run(const Options& opt, Ranks& ranks) {
         OPAL_FN(particles_count)(ctx, OPAL_ELECTRON, &n_e);
         OPAL_FN(particles_count)(ctx, OPAL_ION, &n_i);
         const auto c0 = std::chrono::steady_clock::now();
+        if (staged) {
+            double tj = t0;
+            for (size_t j = 0; j < steps_bt_output; j++, tj += dt) staged_step(tj, ly[j], lz[j]);
+        } else
         ck(OPAL_FN(run_steps)(ctx, (int64_t)steps_bt_output, t0, ly.data(), lz.data(), current_deposition ? 1 : 0, photon_emission ? 1 : 0, filters),
            ctx, "run_steps");                                                        // main.rs:238-267, steps_bt_output times
         loop_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();

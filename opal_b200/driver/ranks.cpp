@@ -8,6 +8,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <cstdint>
 #include <cstdio>
 #include <cstring>
 #include <stdexcept>
@@ -40,11 +41,36 @@ public:
     void connect(opal_ctx* ctx) override {
         if (rank_ == 0) sh_->id_status = (int)OPAL_FN(comm_unique_id)(sh_->nccl_id);
         wait();
-        if (sh_->id_status != OPAL_OK) throw std::runtime_error("opal_comm_unique_id failed (is NCCL available?)");
+        if (sh_->id_status == OPAL_ENCCL) {      // no communicator in the library: host-staged exchange (ranks.h)
+            staged_ = true;
+            wait();
+            return;
+        }
+        if (sh_->id_status != OPAL_OK) throw std::runtime_error("opal_comm_unique_id failed");
         unsigned char id[128];
         std::memcpy(id, sh_->nccl_id, sizeof id);
         const opal_status st = OPAL_FN(comm_init)(ctx, id);
         if (st != OPAL_OK) throw std::runtime_error(std::string("opal_comm_init failed: ") + OPAL_FN(last_error)(ctx));
+        wait();
+    }
+
+    bool host_staged() const override { return staged_; }
+    void ring_exchange(const std::vector<char>& to_left, const std::vector<char>& to_right, std::vector<char>& from_left,
+                       std::vector<char>& from_right) override {
+        const uint64_t hdr[2] = {to_left.size(), to_right.size()};
+        if (sizeof hdr + hdr[0] + hdr[1] > CHUNK * sizeof(double)) throw std::runtime_error("ring_exchange: message larger than the staging slot");
+        char* mine = reinterpret_cast<char*>(slot(rank_));
+        std::memcpy(mine, hdr, sizeof hdr);
+        if (hdr[0]) std::memcpy(mine + sizeof hdr, to_left.data(), hdr[0]);
+        if (hdr[1]) std::memcpy(mine + sizeof hdr + hdr[0], to_right.data(), hdr[1]);
+        wait();
+        uint64_t h[2];
+        const char* l = reinterpret_cast<const char*>(slot((rank_ - 1 + n_) % n_));       // yee.rs:309
+        std::memcpy(h, l, sizeof h);
+        from_left.assign(l + sizeof h + h[0], l + sizeof h + h[0] + h[1]);
+        const char* r = reinterpret_cast<const char*>(slot((rank_ + 1) % n_));            // yee.rs:310
+        std::memcpy(h, r, sizeof h);
+        from_right.assign(r + sizeof h, r + sizeof h + h[0]);
         wait();
     }
 
@@ -96,6 +122,7 @@ private:
         }
     }
     int rank_, n_;
+    bool staged_ = false;
     Shared* sh_;
     double* slots_;
 };

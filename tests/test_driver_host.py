@@ -372,3 +372,118 @@ def test_shipped_example_decks(host, tmp_path):
         en.append(float(row["em_field"]) + float(row["electrons"]))
     assert not (tmp_path / "3_energy.dat").exists()
     assert en[0] > 0 and abs(en[2] / en[0] - 1.0) < 1e-4                    # a quiet thermal plasma keeps its energy
+
+
+COLD_BEAM = """constants:
+  cfl: 0.95
+electrons:
+  npc: 40
+  ne: 20.0
+  ux: 0.3
+  uy: 0.0
+  uz: 0.0
+  output: [x:px, energy]
+ions:
+  npc: 0
+qed:
+  photon_absorption: false
+  photon_emission: false
+control:
+  nx: 120
+  dx: 500.0
+  xmin: 0.0
+  balance: false
+  current_deposition: true
+  start: 0.0
+  end: 60.5 * cfl * 500.0 / c
+  n_outputs: 2
+"""
+
+LASER_SLAB = """constants:
+  omega: 2 * pi * c / 0.8e-6
+  a0: 5.0
+electrons:
+  npc: 16
+  ne: 10.0 * critical(omega) * step(x, 1.0 * micro, 2.0 * micro)
+  ux: 0.01 * nrand
+  uy: 0.01 * nrand
+  uz: 0.0
+  output: [x:px, energy]
+ions:
+  npc: 8
+  name: carbon
+  Z: 6.0
+  A: 12.0
+  ni: 10.0 * critical(omega) * step(x, 1.0 * micro, 2.0 * micro) / 6.0
+  ux: 0.0
+  uy: 0.0
+  uz: 0.0
+  output: [x]
+laser:
+  Ey: (a0 * me * c * omega / e) * sin(omega * (t - x / c))
+  Ez: 0.0
+qed:
+  photon_absorption: false
+  photon_emission: true
+  photon_angle_max: 0.5
+photons:
+  npc: 0
+  output: [energy]
+control:
+  nx: 150
+  dx: 0.02 * micro
+  xmin: 0.0
+  balance: {balance}
+  current_deposition: true
+  start: 0.0
+  end: 120.5 * 0.95 * 0.02 * micro / c
+  n_outputs: 2
+"""
+
+
+def _drive(tmp_path, name, deck, *extra):
+    d = tmp_path / name
+    d.mkdir()
+    (d / "in.yaml").write_text(deck)
+    out = subprocess.run([str(ROOT / "oracle" / "opal_ref_driver"), str(d / "in.yaml"), "--quiet", *extra], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout + out.stderr
+    en = [dict(line.split() for line in (d / f"{i}_energy.dat").read_text().splitlines()) for i in range(3)]
+    return d, [{k: float(v) for k, v in e.items()} for e in en]
+
+
+def test_ranks_with_host_staged_exchange(tmp_path):
+    """`--ranks N` over a library without a communicator (the CPU oracle answers OPAL_ENCCL): the driver moves leavers and halo
+    strips itself through opal_migrants_take/give and opal_halo_take/give (ranks.h, the path of a host that keeps its own
+    p2p).  A cold beam (every particle the same gamma, 640 particles crossing each slab edge; 120 cells, since the
+    reference's even split drops a remainder, grid/mod.rs:128) makes the energies
+    independent of the per-rank loader seeds (main.rs:53), so 1, 2 and 3 ranks must agree to the printed digits."""
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    d1, e1 = _drive(tmp_path, "one", COLD_BEAM)
+    g1 = np.loadtxt(d1 / "2_grid.dat")
+    for n in (2, 3):
+        dn, en = _drive(tmp_path, f"r{n}", COLD_BEAM, "--ranks", str(n))
+        for a, b in zip(e1, en):
+            assert b["electrons"] == pytest.approx(a["electrons"], rel=2e-6)          # nobody lost or doubled at a slab edge
+            assert b["em_field"] == pytest.approx(a["em_field"], rel=1e-4, abs=1e-30)
+        gn = np.loadtxt(dn / "2_grid.dat")
+        assert gn.shape == g1.shape and np.array_equal(gn[:, 0], g1[:, 0])            # slabs gathered in rank order (yee.rs:755-760)
+        assert gn[:, 5].mean() == pytest.approx(g1[:, 5].mean(), rel=1e-6)            # the bulk E_x the uniform current drives
+        assert np.abs(gn[:, 5] - g1[:, 5]).max() < 1e-2 * abs(g1[:, 5].mean())       # no seam at the slab edges
+        c1, h1 = parse_fits(d1 / "2_electron_x-px.fits")
+        cn, hn = parse_fits(dn / "2_electron_x-px.fits")
+        assert float(cn["TOTAL"]) == pytest.approx(float(c1["TOTAL"]), rel=1e-12)
+
+
+@pytest.mark.parametrize("balance", ["true", "false"])
+def test_ranks_laser_deck_with_ions_and_emission(tmp_path, balance):
+    """laser / absorbing boundaries on the outer ranks only (yee.rs:278-292), a slab target that leaves some ranks empty,
+    ions, photon emission: three host-staged ranks run it and stay statistically on the one-rank run"""
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    deck = LASER_SLAB.replace("{balance}", balance)
+    _, e1 = _drive(tmp_path, "one", deck)
+    _, e3 = _drive(tmp_path, "three", deck, "--ranks", "3")
+    assert e1[2]["em_field"] > 0 and e1[2]["electrons"] > 10 * e1[0]["electrons"]     # the laser arrived and heated the slab
+    assert e3[2]["em_field"] == pytest.approx(e1[2]["em_field"], rel=0.02)            # injected pulse: deterministic up to the plasma's response
+    assert e3[2]["electrons"] == pytest.approx(e1[2]["electrons"], rel=0.25)          # different loader seeds per rank: statistical
+    assert e3[2]["ions"] == pytest.approx(e1[2]["ions"], rel=0.35)
+    assert e3[0]["electrons"] == pytest.approx(e1[0]["electrons"], rel=0.2)
