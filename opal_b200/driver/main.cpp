@@ -31,8 +31,11 @@ namespace {
 
 void ck(opal_status st, opal_ctx* ctx, const char* where) {
     if (st != OPAL_OK) {
-        const char* msg = ctx ? OPAL_FN(last_error)(ctx) : "";
-        throw std::runtime_error(std::string(where) + " failed (status " + std::to_string((int)st) + "): " + (msg ? msg : ""));
+        static const char* const names[] = {"OPAL_OK", "OPAL_EINVAL", "OPAL_ECUDA", "OPAL_ENCCL", "OPAL_ENOMEM", "OPAL_EASSERT_CFL",
+                                            "OPAL_EASSERT_INDEX", "OPAL_ECHI_RANGE", "OPAL_ECAPACITY", "OPAL_EASSERT_PROB"};
+        const char* name = (int)st >= 0 && (int)st < 10 ? names[(int)st] : "?";
+        const char* msg = ctx ? OPAL_FN(last_error)(ctx) : (st == OPAL_ECUDA ? "no usable CUDA device (the library has no CPU fallback)" : "");
+        throw std::runtime_error(std::string(where) + " failed (status " + std::to_string((int)st) + " " + name + "): " + (msg ? msg : ""));
     }
 }
 
