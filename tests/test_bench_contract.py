@@ -30,3 +30,15 @@ def test_reference_arm_line_and_thread_count():
 
 def test_reference_arm_other_ranks_do_no_work():
     assert _run({"RANK": "1", "WORLD_SIZE": "2"}) == ""
+
+
+def test_product_arm_fails_loudly_without_a_gpu():
+    """no CPU fallback: bench.py's own arm refuses to run when there is no CUDA device (and never falls back to the oracle)"""
+    import torch
+    if torch.cuda.is_available():
+        import pytest
+        pytest.skip("a GPU is present")
+    out = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--steps", "1", "--warmup", "1", "--nx", "100", "--npc", "10"],
+                         capture_output=True, text=True, timeout=300, cwd=ROOT)
+    assert out.returncode != 0 and "no CUDA device" in (out.stderr + out.stdout)
+    assert out.stdout.strip() == ""          # no JSON line, hence no number
