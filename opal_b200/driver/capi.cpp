@@ -63,8 +63,10 @@ int opal_drv_config_read(const char* yaml, const char* section, const char* fiel
     }
 }
 
-// kind: 0 {:e}, 1 {:.6e}, 2 {}
+// kind: 0 {:e}, 1 {:.6e}, 2 {}, 3 SimulationTime, 4 PrettyDuration
 int opal_drv_format(int kind, double v, char* buf, int cap) {
+    if (kind == 3) return copy_out(fmt_simulation_time(v), buf, cap);
+    if (kind == 4) return copy_out(fmt_pretty_duration(v), buf, cap);
     return copy_out(kind == 0 ? fmt_lower_exp(v) : (kind == 1 ? fmt_lower_exp6(v) : fmt_display(v)), buf, cap);
 }
 

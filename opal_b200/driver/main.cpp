@@ -259,8 +259,15 @@ int run(const Options& opt, Ranks& ranks) {
     for (; i < output_frequency; i++) {
         write_all(i);
         if (id == 0 && !opt.quiet) {
+            // the reference's progress lines (main.rs:224-233): SimulationTime, PrettyDuration and ettc of setup.rs:374-437
             const double rt = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
-            std::printf("Output %4zu at t = %.6e s, RT = %.2f s...\n", i, t, rt);
+            if (i > 0) {
+                const double ettc = rt * (double)(output_frequency - i) / (double)i;   // (total - current) / current in steps
+                std::printf("Output %4zu at t = %s, RT = %s, ETTC = %s...\n", i, fmt_simulation_time(t).c_str(), fmt_pretty_duration(rt).c_str(),
+                            fmt_pretty_duration(ettc).c_str());
+            } else {
+                std::printf("Output %4zu at t = %s...\n", i, fmt_simulation_time(t).c_str());
+            }
             std::fflush(stdout);
         }
         if (opt.outputs >= 0 && (long)i >= opt.outputs) break;
@@ -287,7 +294,7 @@ int run(const Options& opt, Ranks& ranks) {
         write_all(output_frequency);                                                 // main.rs:271-276
         if (id == 0 && !opt.quiet) {
             const double rt = std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count();
-            std::printf("Output %4zu at t = %.6e s, RT = %.2f s\n", output_frequency, t, rt);
+            std::printf("Output %4zu at t = %s, RT = %s\n", output_frequency, fmt_simulation_time(t).c_str(), fmt_pretty_duration(rt).c_str());   // main.rs:278-282
         }
     }
     double ps[2] = {(double)particle_steps, 0.0};

@@ -239,4 +239,37 @@ void Histogram::write_fits(const std::string& filename) const {
     f.write(data.data(), (std::streamsize)data.size());
 }
 
+// SimulationTime's Display (setup.rs:417-437; pinned by the reference's time_format test, setup.rs:487-492)
+std::string fmt_simulation_time(double seconds) {
+    double power = 3.0 * std::floor(std::log10(std::fabs(seconds)) / 3.0);
+    power = std::max(std::min(power, 0.0), -18.0);          // NaN (t == 0: log10 -> -inf -> min/max keep -18) as in Rust's f64::min/max
+    if (std::isnan(power)) power = 0.0;
+    const char* unit = " s";
+    double scale = 1.0;
+    switch ((int)power) {
+        case -18: unit = "as"; scale = 1.0e18; break;
+        case -15: unit = "fs"; scale = 1.0e15; break;
+        case -12: unit = "ps"; scale = 1.0e12; break;
+        case -9: unit = "ns"; scale = 1.0e9; break;
+        case -6: unit = "\u03bcs"; scale = 1.0e6; break;
+        case -3: unit = "ms"; scale = 1.0e3; break;
+        default: break;
+    }
+    char buf[64];
+    std::snprintf(buf, sizeof buf, "%8.2f %s", scale * seconds, unit);
+    return buf;
+}
+
+// PrettyDuration's Display (setup.rs:400-414)
+std::string fmt_pretty_duration(double seconds) {
+    unsigned long long t = seconds > 0.0 ? (unsigned long long)seconds : 0ull;
+    const unsigned long long s = t % 60; t /= 60;
+    const unsigned long long min = t % 60; t /= 60;
+    const unsigned long long hr = t % 24, d = t / 24;
+    char buf[64];
+    if (d > 0) std::snprintf(buf, sizeof buf, "%llud %02llu:%02llu:%02llu", d, hr, min, s);
+    else std::snprintf(buf, sizeof buf, "%02llu:%02llu:%02llu", hr, min, s);
+    return buf;
+}
+
 }  // namespace opal_driver

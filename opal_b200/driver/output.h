@@ -18,6 +18,8 @@ namespace opal_driver {
 std::string fmt_lower_exp(double v);              // {:e}   shortest round-trip digits, e.g. 1.5e-7, 0e0
 std::string fmt_lower_exp6(double v);             // {:.6e} e.g. 1.200135e-6
 std::string fmt_display(double v);                // {}     shortest round-trip digits, positional, e.g. 0.00015
+std::string fmt_simulation_time(double seconds);  // SimulationTime (setup.rs:417-437): "{: >8.2} unit", nearest SI prefix from as to s
+std::string fmt_pretty_duration(double seconds);  // PrettyDuration (setup.rs:400-414): [d"d "]hh:mm:ss of the whole seconds
 
 // sums / minima / maxima over the slabs of a run (the reference: MPI all_reduce); one slab => identity
 struct Reducer {

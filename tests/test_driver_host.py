@@ -487,3 +487,17 @@ def test_ranks_laser_deck_with_ions_and_emission(tmp_path, balance):
     assert e3[2]["electrons"] == pytest.approx(e1[2]["electrons"], rel=0.25)          # different loader seeds per rank: statistical
     assert e3[2]["ions"] == pytest.approx(e1[2]["ions"], rel=0.35)
     assert e3[0]["electrons"] == pytest.approx(e1[0]["electrons"], rel=0.2)
+
+
+def test_reference_time_format(host):
+    """setup.rs:487-492 (the reference's own test) plus the neighbouring SI prefixes and PrettyDuration (setup.rs:400-414)"""
+    def f(kind, v):
+        buf = C.create_string_buffer(64)
+        host.opal_drv_format(kind, v, buf, 64)
+        return buf.value.decode()
+    assert f(3, 2.6e-4) == "  260.00 μs"
+    assert f(3, 1.5) == "    1.50  s" and f(3, 250.0) == "  250.00  s"
+    assert f(3, 3.0e-3) == "    3.00 ms" and f(3, 9.995e-10) == "  999.50 ps"
+    assert f(3, 4.2e-14) == "   42.00 fs" and f(3, 7.0e-17) == "   70.00 as" and f(3, 1.0e-21) == "    0.00 as"
+    assert f(3, -2.0e-5) == "  -20.00 μs" and f(3, 0.0) == "    0.00 as"
+    assert f(4, 59.9) == "00:00:59" and f(4, 3725.0) == "01:02:05" and f(4, 93784.2) == "1d 02:03:04"
