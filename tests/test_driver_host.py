@@ -501,3 +501,53 @@ def test_reference_time_format(host):
     assert f(3, 4.2e-14) == "   42.00 fs" and f(3, 7.0e-17) == "   70.00 as" and f(3, 1.0e-21) == "    0.00 as"
     assert f(3, -2.0e-5) == "  -20.00 μs" and f(3, 0.0) == "    0.00 as"
     assert f(4, 59.9) == "00:00:59" and f(4, 3725.0) == "01:02:05" and f(4, 93784.2) == "1d 02:03:04"
+
+
+SINGLE_POINT = """electrons:
+  npc: 1
+  ne: 20.0 * step(x, 1000.0, 1500.0)
+  ux: 0.5
+  uy: 0.3
+  uz: 0.0
+  output: [energy:p_perp, "energy:p_perp:(log;weight)", x]
+ions:
+  npc: 1
+  name: proton
+  Z: 1.0
+  A: 1.0
+  ni: 0.0
+  ux: 0.0
+  uy: 0.0
+  uz: 0.0
+  output: [x:px]
+qed:
+  photon_absorption: false
+  photon_emission: false
+control:
+  nx: 16
+  dx: 500.0
+  xmin: 0.0
+  balance: false
+  current_deposition: true
+  start: 0.0
+  end: 2.5 * 0.95 * 500.0 / c
+  n_outputs: 1
+"""
+
+
+def test_reference_histogram_smoke_cases(tmp_path):
+    """the reference's three #[ignore]d histogram tests (hgram.rs:435-510) through the driver: a single data point gives a
+    histogram (Automatic and LogScaled bins) that writes as FITS; an empty population gives None, i.e. no file"""
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    (tmp_path / "in.yaml").write_text(SINGLE_POINT)
+    out = subprocess.run([str(ROOT / "oracle" / "opal_ref_driver"), str(tmp_path / "in.yaml"), "--quiet"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    for idx in (0, 1):
+        for name in ("electron_energy-p_perp.fits", "electron_energy-p_perp_log.fits", "electron_x.fits"):
+            cards, data = parse_fits(tmp_path / f"{idx}_{name}")
+            assert float(cards["TOTAL"]) == 20.0 * 500.0                          # one macro-particle carrying the cell's electrons
+            assert data.shape == ((1, 1) if "p_perp" in name else (1,))          # min == max: one bin of unit volume (hgram.rs:131-134, 202)
+            assert data.flat[0] > 0
+            if "log" not in name:
+                assert data.flat[0] == 20.0 * 500.0
+        assert not list(tmp_path.glob(f"{idx}_proton*"))                          # empty_2d: generate_* returns None
