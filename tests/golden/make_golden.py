@@ -15,6 +15,8 @@ Cases (all seeded, numpy default_rng):
   qed_functions      rate (photon_emission.rs:59) over both asymptotic branches and the table, Airy Ai (airy.rs:19) over
                      its five ranges, absorption / stimulated-emission cross sections (photon_absorption.rs:17,
                      stimulated_emission.rs:17) for 1500 seeded photon-electron pairs; keys q_*: compared element-wise
+  absorb_events      absorb (interactions.rs:145): surviving photons, remaining optical depths and kicked electrons of a seeded
+                     scene (oracle regression only; the CUDA path meets the live oracle on it in tests/test_gpu_absorb.py)
 """
 import ctypes
 import math
@@ -29,7 +31,7 @@ ROOT = HERE.parent.parent
 sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "tests"))
 
-from opal_b200.abi import BDY_ABSORBING, BDY_LASER, ELECTRON, ION, OpalABI, Slab  # noqa: E402
+from opal_b200.abi import BDY_ABSORBING, BDY_LASER, ELECTRON, ION, PHOTON, OpalABI, Slab  # noqa: E402
 from opal_b200.constants import ELECTRON_CHARGE, ELECTRON_MASS, SPEED_OF_LIGHT, VACUUM_PERMITTIVITY  # noqa: E402
 import pic_cases as pc  # noqa: E402
 
@@ -116,7 +118,24 @@ def qed_functions(abi):
                 q_abs_defined=oka.astype(np.int64), q_st_defined=oks.astype(np.int64))
 
 
-CASES = dict(two_stream_small=two_stream_small, laser_slab=laser_slab, single_push=single_push, qed_functions=qed_functions)
+def absorb_events(abi):
+    """absorb (interactions.rs:145) on tests/absorb_cases.py's scene with half of the photons close to absorption and the
+    stimulated-emission depth switched off: which photons survive, what is left of their depths, the kicked electrons"""
+    import absorb_cases as ac
+    s = ac.build(abi)
+    n = s.count(PHOTON)
+    rng = np.random.default_rng(1)
+    ac.set_depths(s, np.where(rng.random(n) < 0.5, rng.uniform(0.0, 0.3, n), 50.0), np.full(n, np.inf))
+    s.absorb(0.0)
+    el, ph, ta, ts = ac.snapshot(s)
+    out = {"a_survivors": np.array([ph["cell"].size]), "a_tau_abs": ta}
+    out.update({f"a_e_{k}": el[k] for k in ("cell", "ux", "uy", "uz", "gamma")})
+    out.update({f"a_ph_{k}": ph[k] for k in ("cell", "x", "ux", "uy", "uz", "weight")})
+    return out
+
+
+CPU_ONLY = {"absorb_events"}      # on the GPU this scene needs OPAL_FLAG_STRICT_FP and its own tolerances: tests/test_gpu_absorb.py
+CASES = dict(absorb_events=absorb_events, two_stream_small=two_stream_small, laser_slab=laser_slab, single_push=single_push, qed_functions=qed_functions)
 
 
 def main():

@@ -29,7 +29,9 @@ def _check(name, abi, tol, qtol):
         if k.endswith("_cell") or k.endswith("_weight"):
             assert np.array_equal(got[k], want[k]), f"{name}: {k} differs (bit-exact contract)"
     for k in want.files:
-        if k.endswith("_defined"):
+        if k in ("a_survivors", "a_e_cell", "a_ph_cell", "a_ph_weight"):
+            assert np.array_equal(got[k], want[k]), f"{name}: {k} differs (same photons absorbed by the same electrons)"
+        elif k.endswith("_defined"):
             assert np.array_equal(got[k], want[k]), f"{name}: {k} differs (Some / None pattern)"
         elif k.startswith("q_"):          # pure functions spanning many decades: element-wise relative error
             nz = want[k] != 0.0
@@ -54,6 +56,6 @@ def test_oracle_reproduces_golden(oracle, name):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("name", [c for c in CASES if c not in mg.CPU_ONLY])
 def test_cuda_matches_golden(gpu, name):
     _check(name, gpu, pc.FLOAT_TOL, 1.0e-12)     # the bound of tests/test_gpu_kat.py against the live oracle
