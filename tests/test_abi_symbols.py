@@ -69,3 +69,23 @@ def test_integration_md_declares_every_symbol():
     text = (ROOT / "INTEGRATION.md").read_text()
     bound = set(re.findall(r"pub fn opal_(\w+)\(", text))
     assert sorted(bound) == declared()
+
+
+def test_plain_c_caller(tmp_path, oracle_cdll):
+    """examples/call_from_c.c: the ABI used from C99 with nothing but the header.  Over the oracle it runs 50 steps and keeps
+    its particles and energy; linked against the product library on a box without a GPU it stops at opal_create
+    (OPAL_ECUDA) -- the same source, no fallback."""
+    src = ROOT / "examples" / "call_from_c.c"
+    common = ["/usr/bin/gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", f"-I{ROOT / 'include'}", str(src)]
+    ref = tmp_path / "call_ref"
+    subprocess.check_call(common + ["-DOPAL_PREFIX=opal_ref_", f"-L{ROOT / 'oracle'}", "-lopal_oracle", f"-Wl,-rpath,{ROOT / 'oracle'}", "-lm", "-o", str(ref)])
+    out = subprocess.run([str(ref)], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "particles 16384" in out.stdout and "total energy drift" in out.stdout
+    so = ROOT / "opal_b200" / "csrc"
+    gpu = tmp_path / "call_gpu"
+    subprocess.check_call(common + [f"-L{so}", "-lopal_b200", f"-Wl,-rpath,{so}", "-lm", "-o", str(gpu)])
+    import torch
+    if not torch.cuda.is_available():
+        out = subprocess.run([str(gpu)], capture_output=True, text=True, timeout=120)
+        assert out.returncode == 1 and "status 2" in out.stderr
