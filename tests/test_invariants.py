@@ -80,7 +80,6 @@ def test_deposit_obeys_the_continuity_equation(abi):
     left = int(np.argmin(np.abs(f[:, 0] - 0.0)))
     d = s.download(ELECTRON)
     q = d["weight"] * (-ELEMENTARY_CHARGE)
-    node = np.arange(f.shape[0]) - left
 
     def rho(pos):
         out = np.zeros(f.shape[0])
