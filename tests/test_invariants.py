@@ -259,3 +259,24 @@ def test_emission_conserves_momentum_photon_by_photon(abi):
     k0 = np.sqrt(ph["ux"] ** 2 + ph["uy"] ** 2 + ph["uz"] ** 2)
     assert np.all(k0 > 0.0) and np.all(k0 < before["gamma"][idx])
     s.close()
+
+
+def test_vay_push_keeps_the_exb_drift(oracle):
+    """Electron::vay_push (electron.rs:268-330): the defining property of Vay's scheme -- a particle moving at the drift
+    velocity E x B / B^2 of crossed fields feels no net force and keeps u exactly, for any cyclotron angle per step
+    (the Boris rotation does not).  Formula-independent, so it checks the restatement, not a copy of it.
+    (Oracle only: added after the GPU budget of the round was spent; the CUDA push is held to the oracle at 1e-10 /
+    bit-for-bit by tests/test_gpu_parity.py and tests/test_golden.py::single_push.)"""
+    from opal_b200.constants import ELECTRON_CHARGE, ELECTRON_MASS
+    import kat
+    beta = 0.5
+    u0 = beta / math.sqrt(1.0 - beta * beta)
+    for wc_dt in (0.05, 1.0, 20.0):                                 # cyclotron angle per step, up to far beyond resolved
+        bz = 1.0
+        ey = beta * C * bz                                          # v_d = E x B / B^2 = (Ey / Bz, 0, 0)
+        gamma = math.sqrt(1.0 + u0 * u0)
+        dt = wc_dt * gamma * ELECTRON_MASS / (abs(ELECTRON_CHARGE) * bz)
+        dx = 10.0 * C * dt
+        p = kat._single_electron(oracle, (u0, 0.0, 0.0), (0.0, ey, 0.0), (0.0, 0.0, bz), dx, dt, 40)
+        assert abs(p["ux"][0] - u0) <= 1e-13 and abs(p["uy"][0]) <= 1e-13 and p["uz"][0] == 0.0, (wc_dt, p["ux"][0], p["uy"][0])
+        assert abs(p["gamma"][0] - gamma) <= 1e-13
