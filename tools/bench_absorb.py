@@ -4,6 +4,9 @@ the oracle on one host core, on the same kind of population (every cell holds `e
 of a plane wave at chi ~ 1, optical depths too large for any event so that every pair of a cell is evaluated).
 
   python tools/bench_absorb.py [--nx 4096] [--epc 64] [--ppc 64] [--cpu-nx 128] [--out profiles/r01_absorb.json]
+
+Measurement harness, not product code: oracle/ is executed here only as the timed CPU baseline / checker beside the CUDA
+path (the role bench.py's cpu_baseline leg has); nothing under opal_b200/ depends on it.
 """
 import argparse
 import ctypes

@@ -5,6 +5,9 @@ advance through opal_run_steps (main.rs:238-267).  Electrons at gamma ~ 1000 mee
 so a few per cent of them radiate every step; the photons stay in the periodic slab and are pushed with the rest.
 
   python tools/bench_qed.py [--nx 100000] [--epc 200] [--steps 20] [--cpu-nx 2000] [--out profiles/r01_qed_step.json]
+
+Measurement harness, not product code: oracle/ is executed here only as the timed CPU baseline / checker beside the CUDA
+path (the role bench.py's cpu_baseline leg has); nothing under opal_b200/ depends on it.
 """
 import argparse
 import ctypes

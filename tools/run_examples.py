@@ -4,7 +4,10 @@ end to end through the C++ driver on the GPU, to completion, and the same deck t
 to the first output for a full-size parity check.  Prints one JSON line per deck (also collected in --out).
 
 The decks are regenerated here from the parameters the reference's examples/*.yaml use (the files themselves live under
-/root/reference, which does not travel to the GPU box)."""
+/root/reference, which does not travel to the GPU box).
+
+Measurement harness, not product code: oracle/ is executed here only as the timed CPU baseline / checker beside the CUDA
+path (the role bench.py's cpu_baseline leg has); nothing under opal_b200/ depends on it."""
 import argparse
 import json
 import os
