@@ -2,8 +2,9 @@
 //
 // A statement-by-statement C++ restatement of the reference's arithmetic for the per-timestep
 // loop (src/main.rs:238-267 of tgblackburn/opal v1.5.1).  Only tests/, __graft_entry__.smoke()
-// and bench.py's cpu_baseline / --impl reference legs may load this library; the product
-// (libopal_b200.so) never does.  It exports the C ABI of include/opal_b200.h with the prefix
+// and bench.py's cpu_baseline / --impl reference legs may load this library (plus the measurement
+// scripts under tools/, which time it as their CPU baseline the same way); the product
+// (libopal_b200.so, opal_b200/) never does.  It exports the C ABI of include/opal_b200.h with the prefix
 // `opal_ref_`.
 //
 // Build: g++ -O2 -std=c++17 -fopenmp -ffp-contract=off -fno-fast-math (see oracle/Makefile):
@@ -13,7 +14,9 @@
 // CFITSIO, no network for its 98 crates).  The oracle is pinned against the reference's own 13
 // known-answer tests for this path (tests/test_oracle_kat.py): yee.rs:903-1079 (laser_bc,
 // conducting_bc, periodic_bc), electron.rs:401-436, qed/photon_emission.rs:299-336,
-// qed/pwmci.rs:235-281, vec3.rs:152-169.  Third-party RNG distributions (rand_distr 0.2.2
+// qed/pwmci.rs:235-281, vec3.rs:152-169, and the five Airy tests qed/special_functions/airy.rs:77-112;
+// that state is frozen in tests/golden/ (tests/test_golden.py), and the parts no reference test reaches
+// are held to formula-independent invariants (tests/test_invariants.py).  Third-party RNG distributions (rand_distr 0.2.2
 // ziggurat Exp1/StandardNormal) are NOT restated bit-for-bit: "parity unpinned" for every random
 // draw; QED-on comparisons are statistical.
 //
