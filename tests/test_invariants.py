@@ -280,3 +280,39 @@ def test_vay_push_keeps_the_exb_drift(oracle):
         p = kat._single_electron(oracle, (u0, 0.0, 0.0), (0.0, ey, 0.0), (0.0, 0.0, bz), dx, dt, 40)
         assert abs(p["ux"][0] - u0) <= 1e-13 and abs(p["uy"][0]) <= 1e-13 and p["uz"][0] == 0.0, (wc_dt, p["ux"][0], p["uy"][0])
         assert abs(p["gamma"][0] - gamma) <= 1e-13
+
+
+def test_reference_deposit_quirks_are_kept(oracle):
+    """Parity mode reproduces the reference's two deposit quirks rather than "fixing" them:
+    Q1 -- the fourth transverse-current weight is W(2 + x) == 0 (yee.rs:594-602; the gather uses W(2 - xi)), so a particle
+          right of its cell centre deposits less than its whole current: sum(jy) dx = sum Q v_y (1 - W(2 - x));
+    Q2 -- rho's fourth point carries the right weight to the wrong node (idx - 2, yee.rs:606-609): the total charge is
+          exact, its distribution is not.
+    (Oracle only -- written after the round's GPU budget was spent; the CUDA deposit is held to the oracle's fields at 1e-10.)"""
+    nx, npc, dx = 80, 24, 500.0
+    s = Slab(oracle, nx, 0.0, dx)
+    p = pc.thermal_particles(nx, npc, dx, 0.2, seed=9, cells=np.arange(20, 60))
+    pc.upload(s, ELECTRON, p)
+    s.advance(ELECTRON)
+    s.clear()
+    s.deposit(ELECTRON)
+    f = s.fields()
+    d = s.download(ELECTRON)
+    q = d["weight"] * (-ELEMENTARY_CHARGE)
+    vy, vz = C * d["uy"] / d["gamma"], C * d["uz"] / d["gamma"]
+    lost = spline(2.0 - d["x"])                              # the weight Q1 drops: non-zero for x > 1/2
+    assert 0.01 < lost.mean() < 0.03                         # 1/48 for uniformly distributed offsets
+    for col, v in ((3, vy), (4, vz)):
+        full, kept = np.sum(q * v), np.sum(q * v * (1.0 - lost))
+        got = f[:, col].sum() * dx
+        assert abs(got - kept) <= 1e-12 * np.sum(np.abs(q * v))
+        assert abs(got - full) > 1e-4 * np.sum(np.abs(q * v))            # ... and visibly not the full current
+    assert abs(f[:, 1].sum() * dx - q.sum()) <= 1e-13 * abs(q.sum())      # Q2: every bit of charge is there ...
+    left = int(np.argmin(np.abs(f[:, 0])))
+    pos = d["cell"] + d["x"]
+    good = np.zeros(f.shape[0])
+    for k in range(-2, 4):
+        idx = np.floor(pos).astype(np.int64) + k
+        np.add.at(good, idx + left, q * spline(idx - pos) / dx)
+    assert np.max(np.abs(f[:, 1] - good)) > 1e-3 * np.max(np.abs(good))   # ... at the wrong node
+    s.close()
