@@ -89,3 +89,34 @@ def test_plain_c_caller(tmp_path, oracle_cdll):
     if not torch.cuda.is_available():
         out = subprocess.run([str(gpu)], capture_output=True, text=True, timeout=120)
         assert out.returncode == 1 and "status 2" in out.stderr
+
+
+def test_integration_md_arities_match_the_binding_table():
+    """every `pub fn opal_*` of INTEGRATION.md takes as many arguments as the ctypes table (and hence the header) says,
+    with pointers where the table has pointers"""
+    text = (ROOT / "INTEGRATION.md").read_text()
+    import ctypes as C
+    for name, args in re.findall(r"pub fn opal_(\w+)\(([^)]*)\)", text):
+        params = [a.strip() for a in args.split(",") if a.strip()]
+        want = abi.SIGNATURES[name]
+        assert len(params) == len(want), (name, params, len(want))
+        for p, t in zip(params, want):
+            is_ptr_rust = "*" in p.split(":", 1)[1]
+            is_ptr_c = t is C.c_void_p or t is C.c_char_p or hasattr(t, "contents") or getattr(t, "_type_", None) == "P"
+            assert is_ptr_rust == is_ptr_c, (name, p, t)
+
+
+def test_header_arities_match_the_binding_table():
+    """the C prototypes of include/opal_b200.h and the ctypes table agree argument by argument on count and pointer-ness"""
+    import ctypes as C
+    text = re.sub(r"/\*.*?\*/", "", HEADER, flags=re.S)
+    protos = re.findall(r"OPAL_FN\((\w+)\)\s*\(([^;]*?)\)\s*;", text, flags=re.S)
+    assert sorted(n for n, _ in protos) == declared()
+    for name, args in protos:
+        params = [a.strip() for a in args.replace("\n", " ").split(",") if a.strip() and a.strip() != "void"]
+        want = abi.SIGNATURES[name]
+        assert len(params) == len(want), (name, params, len(want))
+        for p, t in zip(params, want):
+            is_ptr_h = "*" in p or "[" in p
+            is_ptr_c = t is C.c_void_p or t is C.c_char_p or hasattr(t, "contents") or getattr(t, "_type_", None) == "P"
+            assert is_ptr_h == is_ptr_c, (name, p, t)
