@@ -2,12 +2,17 @@
 // libopal_b200.so entry point (include/opal_b200.h).  The reference's driver is Rust; no Rust toolchain exists in
 // this image, so the host side is C++ (INTEGRATION.md shows the Rust `extern "C"` block for the same calls).
 //
-//   opal_b200_driver input.yaml [--ranks N] [--device D] [--lean|--full] [--outputs K] [--quiet]
+//   opal_b200_driver input.yaml [--ranks N] [--device D] [--lean|--full] [--outputs K] [--steps K] [--seed S] [--dump] [--quiet]
 //
 // --ranks N    one process per GPU (the reference: mpirun -n N), x-slabs from GridDesign, NCCL ring inside the library
 // --lean/--full  keep only (x, u, w) per particle -- the 80 B/particle-step layout; automatic when QED is off, deposition on and
 //              no r/work/chi output is requested -- or insist on the reference's whole per-particle state
 // --outputs K  stop after output K (for tests; default: run to `end`)
+// --steps K    at most K steps between outputs (for tests: the unmodified example decks, shortened; default: the deck's)
+// --seed S     seed the loader and the library with S + rank instead of the rank (main.rs:53 hard-wires the rank: one
+//              realisation per deck; the statistical QED comparisons need several)
+// --dump       also write {index}_{species}.bin at every output: the raw per-particle arrays (int64 n, then n doubles each of
+//              cell, x, ux, uy, uz, weight, gamma, chi) -- for sample-level tests (KS on spectra), not a reference output
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -46,13 +51,34 @@ template <class F> bool optional_read(F f) {      // `.ok()` / `.unwrap_or()` of
 struct Options {
     std::string input;
     int ranks = 1, device = -1;
-    bool lean = false, full = false, quiet = false;
-    long outputs = -1;
+    bool lean = false, full = false, quiet = false, dump = false;
+    long outputs = -1, steps = -1;
+    unsigned long long seed = 0;
 };
+
+void dump_species(opal_ctx* ctx, int species, const char* name, const std::string& dir, size_t index, int rank) {
+    int64_t n = 0;
+    ck(OPAL_FN(particles_count)(ctx, species, &n), ctx, "particles_count");
+    std::vector<int64_t> cell((size_t)n);
+    std::vector<double> f[7];
+    for (auto& v : f) v.resize((size_t)n);
+    if (n > 0)
+        ck(OPAL_FN(particles_download)(ctx, species, n, cell.data(), f[0].data(), nullptr, f[1].data(), f[2].data(), f[3].data(), f[4].data(),
+                                       f[5].data(), f[6].data(), nullptr, nullptr, nullptr, nullptr, nullptr), ctx, "particles_download");
+    const std::string path = dir + "/" + std::to_string(index) + "_" + name + (rank > 0 ? ".r" + std::to_string(rank) : std::string()) + ".bin";
+    FILE* fp = std::fopen(path.c_str(), "wb");
+    if (!fp) throw std::runtime_error("cannot write " + path);
+    std::fwrite(&n, sizeof(n), 1, fp);
+    std::vector<double> c((size_t)n);
+    for (int64_t i = 0; i < n; i++) c[(size_t)i] = (double)cell[(size_t)i];
+    std::fwrite(c.data(), sizeof(double), (size_t)n, fp);
+    for (auto& v : f) std::fwrite(v.data(), sizeof(double), (size_t)n, fp);
+    std::fclose(fp);
+}
 
 int run(const Options& opt, Ranks& ranks) {
     const int id = ranks.rank(), np = ranks.nranks();
-    Xoshiro256StarStar rng((uint64_t)id);                                           // main.rs:53
+    Xoshiro256StarStar rng((uint64_t)id + opt.seed);                                // main.rs:53 (--seed 0: the reference's choice)
 
     std::string output_dir = ".";                                                   // main.rs:61 (an empty parent means the cwd here)
     {
@@ -118,13 +144,13 @@ int run(const Options& opt, Ranks& ranks) {
     const uint32_t flags = lean ? OPAL_FLAG_LEAN_STATE : 0u;
     opal_ctx* ctx = nullptr;
     const int device = opt.device >= 0 ? opt.device + id : id;
-    ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, flags), nullptr, "opal_create");
+    ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id + opt.seed, flags), nullptr, "opal_create");
     ranks.connect(ctx);                                                             // NCCL ring (np > 1)
     const bool staged = ranks.host_staged();                                        // no communicator in the library (ranks.h)
     if (staged && lean) {                                                           // a lean context takes opal_run_steps only
         OPAL_FN(destroy)(ctx);
         ctx = nullptr;
-        ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id, 0u), nullptr, "opal_create");
+        ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id + opt.seed, 0u), nullptr, "opal_create");
     }
 
     // ---- particle initialisation (main.rs:117-168) ----
@@ -175,7 +201,8 @@ int run(const Options& opt, Ranks& ranks) {
     // ---- time loop (main.rs:184-267) ----
     double t = tstart;
     const size_t total_steps = (size_t)((tend - tstart) / dt);
-    const size_t steps_bt_output = total_steps / output_frequency;
+    size_t steps_bt_output = total_steps / output_frequency;
+    if (opt.steps >= 0 && (size_t)opt.steps < steps_bt_output) steps_bt_output = (size_t)opt.steps;
     double x2 = 0.0;
     ck(OPAL_FN(laser_x)(ctx, &x2), ctx, "laser_x");
     if (id == 0 && !opt.quiet)
@@ -191,6 +218,11 @@ int run(const Options& opt, Ranks& ranks) {
         if (ipc > 0) write_population(ctx, OPAL_ION, ion_name, iospec, output_dir, index, ranks);
         if (photons_on) write_population(ctx, OPAL_PHOTON, "photon", pospec, output_dir, index, ranks);
         write_energies(ctx, output_dir, index, ranks);
+        if (opt.dump) {
+            dump_species(ctx, OPAL_ELECTRON, "electron", output_dir, index, id);
+            if (ipc > 0) dump_species(ctx, OPAL_ION, ion_name.c_str(), output_dir, index, id);
+            if (photons_on) dump_species(ctx, OPAL_PHOTON, "photon", output_dir, index, id);
+        }
     };
 
     double filters[3];
@@ -314,6 +346,9 @@ int main(int argc, char** argv) {
         if (s == "--ranks" && a + 1 < argc) opt.ranks = std::atoi(argv[++a]);
         else if (s == "--device" && a + 1 < argc) opt.device = std::atoi(argv[++a]);
         else if (s == "--outputs" && a + 1 < argc) opt.outputs = std::atol(argv[++a]);
+        else if (s == "--steps" && a + 1 < argc) opt.steps = std::atol(argv[++a]);
+        else if (s == "--seed" && a + 1 < argc) opt.seed = std::strtoull(argv[++a], nullptr, 10);
+        else if (s == "--dump") opt.dump = true;
         else if (s == "--lean") opt.lean = true;
         else if (s == "--full") opt.full = true;
         else if (s == "--quiet") opt.quiet = true;

@@ -203,6 +203,26 @@ def test_hole_boring_deck_gpu_vs_oracle(tmp_path):
         assert abs(ea[k] - eb[k]) <= 1e-3 * abs(eb[k]), (k, ea[k], eb[k])
 
 
+@pytest.mark.parametrize("name,steps,extra,fits,rel", [
+    ("two_stream", 400, (), ("electron_x-px",), 2e-6),
+    ("hole_boring", 100, (), ("electron_x-px", "electron_x-p_perp", "electron_py-pz", "carbon_x-px", "carbon_py-pz"), 1e-6),
+    # emission on: the two sides draw different random numbers, but in the first 2 x 300 steps the beam is still 10 um away
+    # from the pulse (chi = 0: no photon, tau only counts down), so the run is deterministic up to here
+    ("colliding_beams", 300, (), ("electron_x", "electron_energy", "electron_x-energy"), 1e-6),
+])
+def test_reference_example_files_unmodified(tmp_path, name, steps, extra, fits, rel):
+    """BASELINE configs 1-3: examples/*.yaml are the reference's files byte for byte (test_examples_verbatim.py); both
+    drivers read THE FILE, full size (1e5 / 1e6 / 5e4 particles), shortened only by --steps (steps between outputs)."""
+    import os
+    subprocess.check_call(["make", "-C", str(ROOT / "oracle")], stdout=subprocess.DEVNULL)
+    deck = (ROOT / "examples" / f"{name}.yaml").read_text()
+    os.environ.setdefault("OPAL_REF_THREADS", str(os.cpu_count() or 1))
+    args = ("--steps", str(steps), "--outputs", "2", *extra)
+    a = _run(GPU_DRIVER, deck, tmp_path, "gpu", extra=args)
+    b = _run(REF_DRIVER, deck, tmp_path, "ref", extra=args)
+    _compare_dirs(a, b, (0, 1, 2), fits, rel=rel)
+
+
 def test_two_ranks_two_gpus(tmp_path):
     """`--ranks 2`: one process per GPU (the reference: mpirun -n 2), x-slabs from GridDesign, NCCL ring in the library, host
     collectives for the outputs.  Each rank seeds its loader with its rank id (main.rs:53), so the plasma differs from the

@@ -3,8 +3,9 @@
 end to end through the C++ driver on the GPU, to completion, and the same deck through the oracle build of the driver up
 to the first output for a full-size parity check.  Prints one JSON line per deck (also collected in --out).
 
-The decks are regenerated here from the parameters the reference's examples/*.yaml use (the files themselves live under
-/root/reference, which does not travel to the GPU box).
+The decks are the reference's own files, kept byte for byte under examples/ (/root/reference does not travel to the GPU box).
+--qed-seeds N additionally runs colliding_beams.yaml at full size N times per side (GPU driver / oracle driver, --seed 1..N)
+and compares photon yield, spectra and the electrons' energy loss at the last output (tests/qed_deck_stats.py).
 
 Measurement harness, not product code: oracle/ is executed here only as the timed CPU baseline / checker beside the CUDA
 path (the role bench.py's cpu_baseline leg has); nothing under opal_b200/ depends on it."""
@@ -19,63 +20,15 @@ import time
 ROOT = pathlib.Path(__file__).resolve().parent.parent
 sys.path.insert(0, str(ROOT / "tests"))
 
-C = 2.997925e8
+EXAMPLES = ROOT / "examples"      # the reference's examples/*.yaml, byte for byte (tests/test_examples_verbatim.py)
 
 
-def deck(sections):
-    out = ["---"]
-    for name, fields in sections:
-        out.append(f"{name}:")
-        for k, v in fields:
-            out.append(f" {k}: {v}")
-        out.append("")
-    return "\n".join(out)
+def deck_text(name):
+    return (EXAMPLES / f"{name}.yaml").read_text()
 
 
-def two_stream():
-    return deck([
-        ("control", [("dx", 500), ("nx", 1000), ("xmin", 0.0), ("start", 0.0), ("end", 0.1), ("current_deposition", "true"), ("n_outputs", 20)]),
-        ("qed", [("photon_emission", "false"), ("photon_absorption", "false")]),
-        ("electrons", [("npc", 100), ("ne", 20.0), ("ux", "drift_u * (1.0 + 0.001 * nrand) * (2.0 * floor(urand - 0.5) + 1.0)"), ("uy", 0.0), ("uz", 0.0),
-                       ("output", "x:px")]),
-        ("ions", [("npc", 0)]),
-        ("constants", [("drift_u", "2.5e-24 / (me * c)")]),
-    ])
-
-
-def hole_boring():
-    th_e, th_i = "sqrt(kT/(m*c^2)) * nrand", "sqrt(kT/(A*mp*c^2)) * nrand"
-    return deck([
-        ("control", [("dx", "micro / 1000"), ("nx", 20000), ("xmin", "-10*micro"), ("start", "-20.0e-6/c"), ("end", "10.0e-6/c"),
-                     ("current_deposition", "true"), ("n_outputs", 30)]),
-        ("qed", [("photon_emission", "false"), ("photon_absorption", "false")]),
-        ("electrons", [("npc", 100), ("ne", "density * critical(omega) * step(x,xmin,xmax)"), ("ux", th_e), ("uy", th_e), ("uz", th_e),
-                       ("output", "[x:px, x:p_perp, py:pz]")]),
-        ("ions", [("name", "carbon"), ("npc", 100), ("Z", "Z"), ("A", "A"), ("ni", "density * critical(omega) * step(x,xmin,xmax) / Z"),
-                  ("ux", th_i), ("uy", th_i), ("uz", th_i), ("output", "[x:px, x:p_perp, py:pz]")]),
-        ("laser", [("Ey", "(a0*me*c*omega/e) * gauss_pulse_re(t,x,omega,sigma)"), ("Ez", "(a0*me*c*omega/e) * gauss_pulse_im(t,x,omega,sigma)")]),
-        ("constants", [("density", 100.0), ("a0", 300.0), ("omega", "2*pi*c/0.8e-6"), ("sigma", "pi * 4.0 / sqrt(ln(2.0))"), ("xmin", "0.0 * micro"),
-                       ("xmax", "5.0 * micro"), ("Z", 6.0), ("A", 12.0), ("kT", "500 * eV")]),
-    ])
-
-
-def colliding_beams():
-    ey = ">\n  (a0*m*c*omega/e)\n  *sin(omega*(t-x/c))\n  *exp(-ln(2.0)*(omega*(t-x/c))^2/(2.0*pi^2*ncycles^2))"
-    return deck([
-        ("control", [("dx", "0.01*micro"), ("nx", 4000), ("xmin", "-15*micro"), ("start", "-24.0e-6/c"), ("end", "6.0e-6/c"),
-                     ("current_deposition", "false"), ("n_outputs", 5)]),
-        ("qed", [("photon_emission", "true"), ("photon_absorption", "false"), ("photon_angle_max", "50 * milli")]),
-        ("electrons", [("npc", 100), ("ne", "S * a0 * critical(omega) * step(x,xmin,xmax)"), ("ux", "-1000.0 * (1.0 + 0.01 * nrand)"), ("uy", 0.0),
-                       ("uz", 0.0), ("output", "[x, chi, x:chi, energy, x:energy]")]),
-        ("ions", [("npc", 0)]),
-        ("photons", [("npc", 0), ("output", "[x, energy, energy:(log;energy), longitude:latitude, longitude:latitude:(energy)]")]),
-        ("laser", [("Ey", ey), ("Ez", 0.0)]),
-        ("constants", [("S", "1.0e-6"), ("a0", 20.0), ("omega", "2*pi*c/0.8e-6"), ("ncycles", 4.0), ("xmin", "(20 - 2.5) * micro"),
-                       ("xmax", "(20 + 2.5) * micro")]),
-    ])
-
-
-DECKS = {"two_stream": two_stream, "hole_boring": hole_boring, "colliding_beams": colliding_beams}
+DECKS = {"two_stream": lambda: deck_text("two_stream"), "hole_boring": lambda: deck_text("hole_boring"),
+         "colliding_beams": lambda: deck_text("colliding_beams")}
 
 
 def energies(path):
@@ -103,6 +56,7 @@ def main():
     ap.add_argument("--ref-outputs", type=int, default=1, help="outputs the oracle build runs to (0: skip the oracle arm)")
     ap.add_argument("--ref-threads", type=int, default=os.cpu_count() or 1)
     ap.add_argument("--write-only", action="store_true", help="only write the decks")
+    ap.add_argument("--qed-seeds", type=int, default=0, help="full-size colliding_beams.yaml, this many seeds per side, statistics at the last output")
     args = ap.parse_args()
     work = pathlib.Path(args.work)
     lines = []
@@ -131,6 +85,20 @@ def main():
             line.update({"ref_outputs": k, "ref_wall_s": ref_wall, "ref_particle_steps_per_s": ref_rate, "ref_threads": args.ref_threads,
                          "energies_at_ref_output": {"gpu": eg, "oracle": er},
                          "rel_diff": {q: (abs(eg[q] - er[q]) / abs(er[q]) if er[q] else abs(eg[q])) for q in er}})
+        print(json.dumps(line), flush=True)
+        lines.append(line)
+    if args.qed_seeds > 0 and not args.write_only:
+        import qed_deck_stats as qs
+        deck = deck_text("colliding_beams")
+        seeds = list(range(1, args.qed_seeds + 1))
+        t0 = time.perf_counter()
+        ref_dirs = qs.run_seeds(qs.REF_DRIVER, deck, work / "qed_ref", seeds, parallel=min(len(seeds), os.cpu_count() or 1))
+        t1 = time.perf_counter()
+        gpu_dirs = qs.run_seeds(qs.GPU_DRIVER, deck, work / "qed_gpu", seeds, parallel=1)
+        t2 = time.perf_counter()
+        stats = qs.compare([qs.observables(d) for d in gpu_dirs], [qs.observables(d) for d in ref_dirs])
+        line = {"deck": "colliding_beams", "qed_statistics_gpu_vs_oracle": stats, "violations": qs.verdict(stats),
+                "oracle_wall_s": t1 - t0, "gpu_wall_s": t2 - t1}
         print(json.dumps(line), flush=True)
         lines.append(line)
     if lines:
