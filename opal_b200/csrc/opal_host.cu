@@ -464,6 +464,13 @@ __global__ void k_outbox_headers(opal_migrant* out_l, opal_migrant* out_r, const
     if (threadIdx.x == 0) { out_l[0].cell = st->n_out[0]; out_r[0].cell = st->n_out[1]; }
 }
 __global__ void k_header_to_int(const opal_migrant* in, int* n) { if (threadIdx.x == 0) *n = (int)in[0].cell; }
+// live particles of a species: sum of count[] (out must be zeroed)
+__global__ void __launch_bounds__(256) k_total_count(const int* __restrict__ count, int ncell, unsigned long long* out) {
+    unsigned long long acc = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ncell; i += gridDim.x * blockDim.x) acc += (unsigned long long)count[i];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
 
 // NCCL ring exchange of both outboxes (fixed size: header + out_cap records) -- replaces the
 // even/odd blocking p2p of mod.rs:308-354 with one grouped, deadlock-free exchange.
@@ -586,13 +593,21 @@ bool do_emit(opal_ctx* c, double t, double min_e, double max_a, double max_fl) {
     if (remote(c) && !ensure_photons(c, 1)) return false;
     if (!E.allocated) return true;
     if (!E.full) return fail(c, OPAL_EINVAL, "emit_radiation needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)");
+    // at most one photon per electron per call (electron.rs:208-251): make room up front for the electrons this slab holds
+    // NOW (migrants included -- a slab that started empty may have filled up), counted on the device
+    unsigned long long* d_live = reinterpret_cast<unsigned long long*>(c->d_energy + 7);
+    CUB(cudaMemsetAsync(d_live, 0, sizeof(unsigned long long), c->stream));
+    { int gr = (c->g.nx + 255) / 256; if (gr > 148 * 4) gr = 148 * 4; k_total_count<<<gr, 256, 0, c->stream>>>(E.d_count, c->g.nx, d_live); c->launches++; }
+    unsigned long long live = 0;
+    CUB(cudaMemcpyAsync(&live, d_live, sizeof(live), cudaMemcpyDeviceToHost, c->stream));
     int nph = 0;
-    if (!photon_count(c, &nph)) return false;
-    // at most one photon per electron per call (electron.rs:208-251): make room up front
-    if (!ensure_photons(c, (long long)nph + E.n_hint + c->out_cap)) return false;
+    if (!photon_count(c, &nph)) return false;      // synchronises the stream: `live` has arrived too
+    E.n_hint = (long long)live;
+    if (!ensure_photons(c, (long long)nph + (long long)live + c->out_cap)) return false;
     c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, t, min_e, max_a, max_fl,
               c->seed, c->emit_calls++, c->d_status);
     c->launches++;
+    CUB(cudaGetLastError());
     return fetch_status(c);
 }
 

@@ -1911,9 +1911,9 @@ static void l_photon_insert(cudaStream_t s, const PhotonDev& dst, const opal_mig
 static void l_emit(cudaStream_t s, const GridDev& g, const BucketDev& e, const PhotonDev& ph, const StepParams& sp,
                    const double* tables, double t, double min_energy, double max_angle, double max_fl, uint64_t seed,
                    uint64_t call_index, StatusDev* st) {
-    static bool attr_set = false;
     const int smem = QED_TABLE_DOUBLES * (int)sizeof(double) + EMIT_QCAP * (int)(sizeof(long long) + sizeof(int));
-    if (!attr_set) { cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_set = true; }
+    // per DEVICE, and contexts may live on several devices of one process: set it on every launch (a cheap host-side call)
+    cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     int grid = cell_grid(e.ncell);
     if (grid > 148 * OPAL_EMIT_MB) grid = 148 * OPAL_EMIT_MB;
     k_emit<<<grid, BLOCK, smem, s>>>(g, e, ph, sp, tables, t, min_energy, max_angle, max_fl, seed, call_index, st);
@@ -1987,9 +1987,8 @@ static void l_qed_rate(cudaStream_t s, int n, const double* chi, const double* g
 }
 static void l_qed_sample(cudaStream_t s, int n, const double* tables, const double* chi, const double* gamma, const double* r1,
                          const double* r2, const double* r3, int classical, double* out3, StatusDev* st) {
-    static bool attr_set = false;
     const int smem = QED_TABLE_DOUBLES * (int)sizeof(double);
-    if (!attr_set) { cudaFuncSetAttribute(k_qed_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_set = true; }
+    cudaFuncSetAttribute(k_qed_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);      // per device: see l_emit
     k_qed_sample<<<(n + 127) / 128, 128, smem, s>>>(n, tables, chi, gamma, r1, r2, r3, classical, out3, st);
 }
 static void l_fields_at(cudaStream_t s, const GridDev& g, int n, const long long* cell, const double* xi, double* out6, StatusDev* st) {

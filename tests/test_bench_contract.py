@@ -42,3 +42,19 @@ def test_product_arm_fails_loudly_without_a_gpu():
                          capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert out.returncode != 0 and "no CUDA device" in (out.stderr + out.stdout)
     assert out.stdout.strip() == ""          # no JSON line, hence no number
+
+
+def test_parity_leg_of_the_bench_line(oracle, oracle_cdll):
+    """bench.py's `parity` block (the CPU leg's arrays through the CUDA path, compared with the oracle's result), exercised
+    on the CPU with the oracle standing in for the product library: identical code on both sides => exact agreement"""
+    sys.path.insert(0, str(ROOT))
+    import bench
+    rate, secs, threads, n, state = bench.cpu_reference_run(200, 50, 2, 1, keep_state=True)
+    assert n == 10000 and rate > 0 and state["steps"] == 3
+    out = bench.gpu_parity_leg(oracle, state, 200, 0)
+    assert out["ok"] and out["cells_bit_exact"] and out["n"] == 10000 and out["max_rel_x_u"] == 0.0 and out["max_rel_fields"] == 0.0
+    # a perturbed result is flagged
+    state["particles"]["ux"] = state["particles"]["ux"] * (1.0 + 1e-8)
+    bad = bench.gpu_parity_leg(oracle, state, 200, 0)
+    oracle_cdll.opal_ref_set_threads(1)      # cpu_reference_run raised the (process-wide) thread count of the shared library
+    assert not bad["ok"] and bad["max_rel_x_u"] > 1e-10

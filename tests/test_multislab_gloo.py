@@ -70,3 +70,43 @@ def test_grid_design_matches_reference_rules():
     assert sum(d.nx) == 1000 and d.nx[0] < 200                                # equal integral of ne, not equal cells
     d = GridDesign.balanced(4, 4000, 0.0, 1.0, lambda x: 1.0)
     assert sum(d.nx) == 4000 and all(abs(n - 1000) <= 10 for n in d.nx)
+
+
+@pytest.mark.parametrize("case,world,balanced", [("periodic", 3, False), ("laser", 2, True), ("laser_sparse", 4, False)])
+def test_inprocess_oracle_ring_matches_one_slab(case, world, balanced, oracle):
+    """tests/ring_oracle.py (the checker of the multi-GPU runs): a ring of oracle slabs stepped rank after rank in one process
+    equals one oracle slab covering the domain; the per-step leaver counts it reports are consistent with the particles that
+    changed slab"""
+    import ring_oracle
+    g = w.global_case(case)
+    if balanced:
+        dens = ring_oracle.density_of(g["particles"], g["nx"])
+        design = GridDesign.balanced(world, g["nx"], g["xmin"], g["dx"], lambda x: dens[min(int(round((x - g["xmin"]) / g["dx"])), g["nx"] - 1)],
+                                     left=g["left"], right=g["right"])
+        assert len(set(design.nx)) > 1
+    else:
+        design = GridDesign.unbalanced(world, g["nx"], g["xmin"], g["dx"], left=g["left"], right=g["right"])
+    ring = ring_oracle.OracleRing(oracle, design)
+    ring.upload(ELECTRON, g["particles"])
+    one = Slab(oracle, g["nx"], g["xmin"], g["dx"], None, g["left"], g["right"])
+    pc.upload(one, ELECTRON, g["particles"])
+    laser = w.laser_fns(g["laser"]) if g["laser"] else None
+    fields = ("cell", "x", "ux", "uy", "uz", "weight")
+    t = 0.0
+    total_gone = 0
+    for k in range(g["steps"]):
+        owner_before = {r: set(d["weight"].tolist()) for r, d in enumerate(ring.download(ELECTRON, ("cell", "weight")))} if k < 3 else None
+        t1, gone = ring.step(t, laser=laser, species=(ELECTRON,))
+        if owner_before is not None:     # first steps: count who changed slab by identity (unique weights)
+            owner_after = {r: set(d["weight"].tolist()) for r, d in enumerate(ring.download(ELECTRON, ("cell", "weight")))}
+            for r in range(world):
+                left_r = len(owner_before[r] - owner_after[r])
+                assert left_r == sum(gone[ELECTRON][r]), (r, left_r, gone[ELECTRON][r])
+        total_gone += sum(sum(x) for x in gone[ELECTRON])
+        pc.step_by_calls(one, t, laser=laser, species=(ELECTRON,))
+        t = t1
+    assert total_gone > 0
+    got = {k: np.concatenate([d[k] for d in ring.download(ELECTRON, fields)]) for k in fields}
+    pc.compare_particles(got, one.download(ELECTRON, fields=fields), fields=("x", "ux", "uy", "uz"))
+    pc.compare_fields(np.concatenate(ring.interior_fields()), one.fields()[one.left_size: one.left_size + sum(design.nx)])
+    ring.close()
