@@ -111,7 +111,15 @@ struct opal_ctx {
     int* d_absorb_kind = nullptr; long long* d_absorb_slot = nullptr; int* d_absorb_last = nullptr; int absorb_cap = 0; long long absorb_calls = 0;
     bool absorb_on = false; double absorb_max_displacement = 0.0, absorb_stop_time = 0.0;   // opal_set_absorption (NaN == None)
     int overflow_cap = 0;
-    StripRec* d_cmovers = nullptr; int* d_cmcount = nullptr; int cell_mover_cap = 0;   // per-cell left/right mover strips (lean electrons)
+    // lean layout, per charged species: the per-cell left / right mover strips, double-buffered by step parity (the push of
+    // step n reads what step n-1 wrote: opal_push_lean.cuh), the strip counts and the per-cell free-slot counts
+    struct Lean {
+        StripRec* d_strips[2] = {nullptr, nullptr}; int* d_scount[2] = {nullptr, nullptr}; int* d_hcount = nullptr;
+        int mc = 0;               // records per cell and direction
+        int parity = 0;           // the buffer the NEXT push reads
+        bool pending = false;     // movers of the last push wait in d_strips[parity] (not yet in the buckets)
+        bool holes = false;       // the buckets carry free slots (count[] counts slots in use)
+    } lean[2];
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
     opal_migrant* d_in[2] = {nullptr, nullptr};
     int out_cap = 0;
@@ -125,7 +133,7 @@ struct opal_ctx {
     bool ke_fused = false;
     double* d_laser = nullptr; long long laser_cap = 0;   // burst mode: per-step laser amplitudes on the device
     int64_t burst_steps = 0;         // steps executed through replayed CUDA graphs (instrumentation)
-    bool holes_open = false;         // lean electrons: the last fused step left holes in the buckets (count[] counts slots in use)           // d_energy[4] is the electrons' current total_kinetic_energy
+                                     // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
     double* d_qed_tables = nullptr;
@@ -186,7 +194,7 @@ StepParams sparams(opal_ctx* c, int species) {
     sp.route_left = c->has_left() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap; sp.overflow_cap = c->overflow_cap;
-    sp.cell_mover_cap = (species == OPAL_ELECTRON || species == OPAL_ION) ? c->cell_mover_cap : 0;   // the strips serve one species at a time
+    sp.cell_mover_cap = (species == OPAL_ELECTRON || species == OPAL_ION) ? c->lean[species].mc : 0;
     return sp;
 }
 
@@ -221,7 +229,11 @@ bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand
     CUB(cudaMemcpyAsync(B.d_start, B.h_start.data(), (size_t)(ncell + 1) * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
     CUB(cudaMemsetAsync(B.d_count, 0, (size_t)ncell * sizeof(int), c->stream));
     const int nf = full ? NF_FULL : NF_LEAN;
-    for (int k = 0; k < nf; k++) CUB(cudaMalloc(&B.d_f[k], (size_t)std::max<long long>(B.slots, 1) * sizeof(double)));
+    for (int k = 0; k < nf; k++) {
+        CUB(cudaMalloc(&B.d_f[k], (size_t)std::max<long long>(B.slots, 1) * sizeof(double)));
+        // zero-filled: the lean push runs its arithmetic on every lane of a chunk, also on slots no particle has ever occupied
+        CUB(cudaMemsetAsync(B.d_f[k], 0, (size_t)std::max<long long>(B.slots, 1) * sizeof(double), c->stream));
+    }
     CUB(cudaStreamSynchronize(c->stream));
     B.allocated = true;
     return true;
@@ -287,23 +299,39 @@ bool grow_movers_after(opal_ctx* c) {
     return reserve_mover_segments(c, 2ll * mx + 1024);
 }
 
-// per-cell mover strips for the lean fused electron kernel: MC records per cell, sized for the expected
-// crossing fraction (thermal plasma at 0.95 CFL: a few % of a cell's particles per step)
-bool ensure_cell_movers(opal_ctx* c, long long n_particles) {
+// per-cell mover strips of a lean species: MC records per cell and direction, sized for the expected crossing fraction
+// (thermal plasma at 0.95 CFL: a few % of a cell's particles per step); what does not fit goes to the segmented buffer
+void reset_lean(opal_ctx* c, int sp) {
+    opal_ctx::Lean& L = c->lean[sp];
+    L.parity = 0; L.pending = false; L.holes = false;
+    if (!L.d_hcount) return;
+    for (int k = 0; k < 2; k++) cudaMemsetAsync(L.d_scount[k], 0, (size_t)2 * c->g.nx * sizeof(int), c->stream);
+    cudaMemsetAsync(L.d_hcount, 0, (size_t)c->g.nx * sizeof(int), c->stream);
+}
+
+bool ensure_cell_movers(opal_ctx* c, int sp, long long n_particles) {
     if (c->full || (c->flags & OPAL_FLAG_STRICT_FP)) return true;
+    opal_ctx::Lean& L = c->lean[sp];
     const double ppc = (double)n_particles / (double)c->g.nx;
     long long mc = (long long)std::ceil((env_double("OPAL_CELL_MOVER_FRACTION", 0.02) * ppc + 12.0) / 16.0) * 16;   // per direction
     if (mc < 16) mc = 16;
     if (mc > 256) mc = 256;
-    if (c->d_cmovers && mc <= c->cell_mover_cap) return true;
-    if (c->d_cmovers) cudaFree(c->d_cmovers);
-    if (c->d_cmcount) cudaFree(c->d_cmcount);
-    c->d_cmovers = nullptr; c->d_cmcount = nullptr;
-    CUB(cudaMalloc(&c->d_cmovers, (size_t)mc * 2 * c->g.nx * sizeof(StripRec)));
-    // [2 nx strip counts][nx hole counts][nx x 2 mc hole slots]
-    CUB(cudaMalloc(&c->d_cmcount, (size_t)(3 + 2 * mc) * c->g.nx * sizeof(int)));
-    CUB(cudaMemset(c->d_cmcount, 0, (size_t)3 * c->g.nx * sizeof(int)));
-    c->cell_mover_cap = (int)mc;
+    if (!L.d_hcount || mc > L.mc) {
+        for (int k = 0; k < 2; k++) {
+            if (L.d_strips[k]) cudaFree(L.d_strips[k]);
+            if (L.d_scount[k]) cudaFree(L.d_scount[k]);
+            L.d_strips[k] = nullptr; L.d_scount[k] = nullptr;
+        }
+        if (L.d_hcount) cudaFree(L.d_hcount);
+        L.d_hcount = nullptr;
+        for (int k = 0; k < 2; k++) {
+            CUB(cudaMalloc(&L.d_strips[k], (size_t)mc * 2 * c->g.nx * sizeof(StripRec)));
+            CUB(cudaMalloc(&L.d_scount[k], (size_t)2 * c->g.nx * sizeof(int)));
+        }
+        CUB(cudaMalloc(&L.d_hcount, (size_t)c->g.nx * sizeof(int)));
+        L.mc = (int)mc;
+    }
+    reset_lean(c, sp);
     return true;
 }
 
@@ -376,14 +404,32 @@ bool fetch_status(opal_ctx* c) {
     return true;
 }
 
-// The lean fused step kernels leave holes in the electron buckets (see OPAL_PUSH_HOLES); everything else reads
-// buckets whose first count[c] slots are live.
-bool ensure_compact(opal_ctx* c) {
-    if (!c->holes_open) return true;
-    c->holes_open = false;
-    if (!c->bk[OPAL_ELECTRON].allocated || !c->d_cmcount) return true;
-    c->k.compact_cells(c->stream, bdev(c, OPAL_ELECTRON), c->d_cmcount); c->launches++;
-    CUB(cudaMemsetAsync(c->d_cmcount + 2ll * c->g.nx, 0, (size_t)c->g.nx * sizeof(int), c->stream));
+bool handle_overflow(opal_ctx* c, int sp, bool deposit_parked);
+
+// Between lean steps the last push's movers wait in the strips and the buckets carry free slots (opal_push_lean.cuh).
+// Everything but the step kernels reads buckets whose first count[c] slots are live and complete: append the waiting
+// movers (k_strip_flush; a bucket may overflow -> re-layout), then close the free slots (k_compact_cells).
+bool flush_strips(opal_ctx* c, int sp, bool inside_overflow_handling = false) {
+    opal_ctx::Lean& L = c->lean[sp];
+    if (!L.pending) return true;
+    L.pending = false;
+    if (!c->bk[sp].allocated) return true;
+    // (inside the overflow handling the parked-mover list is in use: what this flush parks is appended to it)
+    if (!inside_overflow_handling) CUB(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
+    c->k.flush(c->stream, bdev(c, sp), sparams(c, sp), L.d_strips[L.parity], L.d_scount[L.parity], c->d_overflow, c->d_status); c->launches++;
+    CUB(cudaMemsetAsync(L.d_scount[L.parity], 0, (size_t)2 * c->g.nx * sizeof(int), c->stream));
+    if (!fetch_status(c)) return false;
+    return inside_overflow_handling ? true : handle_overflow(c, sp, true);
+}
+
+bool settle(opal_ctx* c, int sp) {
+    if (sp != OPAL_ELECTRON && sp != OPAL_ION) return true;
+    opal_ctx::Lean& L = c->lean[sp];
+    if (!flush_strips(c, sp)) return false;
+    if (L.holes) {
+        L.holes = false;
+        if (c->bk[sp].allocated && L.d_hcount) { c->k.compact_cells(c->stream, bdev(c, sp), L.d_hcount); c->launches++; }
+    }
     return true;
 }
 
@@ -451,6 +497,8 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
 
 bool handle_overflow(opal_ctx* c, int sp, bool deposit_parked) {
     int guard = 0;
+    // lean layout: the buckets are re-laid out for the demand in count[] -- bring the movers waiting in the strips in first
+    if (c->h_status->n_overflow > 0 && !flush_strips(c, sp, true)) return false;
     while (c->h_status->n_overflow > 0) {
         if (c->h_status->n_overflow > c->overflow_cap) return fail(c, OPAL_ECAPACITY, "too many parked movers");
         if (!regrid(c, sp, deposit_parked)) return false;
@@ -537,11 +585,13 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
         ke_out = c->d_energy + 4;
         CUB(cudaMemsetAsync(ke_out, 0, sizeof(double), c->stream));
     }
-    { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status, ke_out); c->launches++; }
+    opal_ctx::Lean& L = c->lean[sp];
+    if (!dep && !flush_strips(c, sp)) return false;          // the call-by-call push does not read the strips
+    LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
+    { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                                         c->d_overflow, c->d_status, ke_out); c->launches++; }
     if (ke_out && strips) c->ke_fused = true;
-    if (strips && c->k.push_leaves_holes) c->holes_open = true;
-    if (strips) { Timed tm(c, 1); c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1,
-                 c->d_overflow, c->d_status); c->launches++; }
+    if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }      // this push's movers wait for the next one
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++; }
     if (remote(c)) {
@@ -683,12 +733,14 @@ void enqueue_species(opal_ctx* c, int sp) {     // advance_charged without the h
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
     c->k.burst_mark(c->stream, c->d_status, 0, sp);
-    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, c->d_cmovers, c->d_cmcount, c->d_status, nullptr);
-    if (strips) c->k.pull(c->stream, c->g, bdev(c, sp), p, c->d_cmovers, c->d_cmcount, c->d_out[0] + 1, c->d_out[1] + 1, c->d_overflow, c->d_status);
+    opal_ctx::Lean& L = c->lean[sp];
+    LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
+    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                                  c->d_overflow, c->d_status, nullptr);
+    if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
     c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status);
     c->k.burst_mark(c->stream, c->d_status, 1, sp);
-    if (strips && c->k.push_leaves_holes) c->holes_open = true;
 }
 
 int enqueue_step(opal_ctx* c) {                 // main.rs:238-267 with deposition on, emission off; returns the launch count
@@ -700,7 +752,7 @@ int enqueue_step(opal_ctx* c) {                 // main.rs:238-267 with depositi
     do_field(c);
     c->k.burst_mark(c->stream, c->d_status, 2, 0);
     int n = 4;                                   // clear, sync_bc, field, end mark
-    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) n += 4 + ((sp == OPAL_ELECTRON && !c->bk[sp].full && c->cell_mover_cap > 0 && !(c->flags & OPAL_FLAG_STRICT_FP)) ? 1 : 0);
+    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) n += 4;      // begin mark, push, scatter, check mark
     (void)l0;
     return n;
 }
@@ -725,6 +777,7 @@ bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int per_step = 0;
+    const int parity0[2] = {c->lean[0].parity, c->lean[1].parity};     // two captured steps leave the strip parity where it was
     cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
     if (e == cudaSuccess) {
         per_step = enqueue_step(c);
@@ -753,6 +806,11 @@ bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64
     leave();
     c->burst_steps += *done;
     if (ok && (*done & 1)) swap_fields(c);       // an odd number of steps ran: the fields sit in the other buffer set
+    for (int sp = 0; sp < 2; sp++) {
+        // pushes of this species that ran: one per completed step, plus the half-finished step up to the halting species
+        const int64_t pushes = *done + ((*halted && c->bk[sp].allocated && sp <= c->h_status->halt_species) ? 1 : 0);
+        if (c->lean[sp].d_hcount && c->bk[sp].allocated) c->lean[sp].parity = parity0[sp] ^ (int)(pushes & 1);
+    }
     return ok;
 }
 
@@ -830,9 +888,13 @@ opal_status opal_destroy(opal_ctx* c) {
         if (c->ph[w].d_cell) cudaFree(c->ph[w].d_cell);
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
-    void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_cmovers, c->d_cmcount, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
+    void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
                      c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser};
     for (void* p : frees) if (p) cudaFree(p);
+    for (int sp = 0; sp < 2; sp++) {
+        for (int k = 0; k < 2; k++) { if (c->lean[sp].d_strips[k]) cudaFree(c->lean[sp].d_strips[k]); if (c->lean[sp].d_scount[k]) cudaFree(c->lean[sp].d_scount[k]); }
+        if (c->lean[sp].d_hcount) cudaFree(c->lean[sp].d_hcount);
+    }
     if (c->h_status) cudaFreeHost(c->h_status);
     if (c->h_energy) cudaFreeHost(c->h_energy);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -859,7 +921,6 @@ opal_status opal_set_ion(opal_ctx* c, double z_star, double a) {
 opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int64_t* cell, const double* x, const double* ux,
                                   const double* uy, const double* uz, const double* w, const double* tau) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON) c->holes_open = false;
     c->ke_fused = false;
     if (n < 0 || n > (1ll << 31) - 64 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
     const double dx = c->g.dx, dt = c->g.dt;
@@ -905,7 +966,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = n;
     if (!ensure_movers(c, n)) return (opal_status)c->status;
-    if (!ensure_cell_movers(c, n)) return (opal_status)c->status;
+    if (!ensure_cell_movers(c, species, n)) return (opal_status)c->status;
     // host-side bucketing into the slot layout (stable: keeps the caller's order inside a cell)
     const int nf = c->full ? NF_FULL : NF_LEAN;
     std::vector<std::vector<double>> hf(nf, std::vector<double>((size_t)B.slots, 0.0));
@@ -938,7 +999,6 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
 opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, double weight, const double u_th[3], const double drift[3],
                                     int two_stream, int64_t global_cell_offset, uint64_t seed) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON) c->holes_open = false;
     c->ke_fused = false;
     if ((species != OPAL_ELECTRON && species != OPAL_ION) || npc < 1 || !u_th || !drift) return OPAL_EINVAL;
     Buckets& B = c->bk[species];
@@ -948,7 +1008,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
     if (!alloc_buckets(c, B, demand, c->full)) return (opal_status)c->status;
     B.n_hint = npc * (long long)c->g.nx;
     if (!ensure_movers(c, B.n_hint)) return (opal_status)c->status;
-    if (!ensure_cell_movers(c, B.n_hint)) return (opal_status)c->status;
+    if (!ensure_cell_movers(c, species, B.n_hint)) return (opal_status)c->status;
     c->k.generate(c->stream, bdev(c, species), species, npc, weight, u_th, drift, two_stream, global_cell_offset, seed, c->full, c->g.dx, c->g.dt);
     c->launches++;
     CU(cudaStreamSynchronize(c->stream));
@@ -958,7 +1018,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
 
 opal_status opal_particles_count(opal_ctx* c, int species, int64_t* n) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
+    if (!settle(c, species)) return (opal_status)c->status;
     if (!n) return OPAL_EINVAL;
     *n = 0;
     if (species == OPAL_PHOTON) {
@@ -983,7 +1043,7 @@ opal_status opal_particles_download(opal_ctx* c, int species, int64_t cap, int64
                                     double* uy, double* uz, double* w, double* gamma, double* chi, double* tau, double* work,
                                     double* y, double* z, double* birth) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
+    if (!settle(c, species)) return (opal_status)c->status;
     const double inf = std::numeric_limits<double>::infinity();
     if (species == OPAL_PHOTON) {
         int n = 0;
@@ -1136,7 +1196,7 @@ opal_status opal_migrants_take(opal_ctx* c, int species, int side, int64_t cap, 
 
 opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, const opal_migrant* in) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
+    if (!settle(c, species)) return (opal_status)c->status;
     c->ke_fused = false;
     if (side != OPAL_LEFT && side != OPAL_RIGHT || n < 0 || species < 0 || species > 2) return OPAL_EINVAL;
     if (n == 0) return OPAL_OK;
@@ -1338,7 +1398,7 @@ static bool hgram_args_ok(int species, int ndim, const int* q) {
 
 opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, const int* lg, double* mn, double* mx, int64_t* n) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
+    if (!settle(c, species)) return (opal_status)c->status;
     if (!hgram_args_ok(species, ndim, q) || !mn || !mx || !n) return OPAL_EINVAL;
     for (int d = 0; d < ndim; d++) { mn[d] = std::numeric_limits<double>::max(); mx[d] = -std::numeric_limits<double>::max(); }   // hgram.rs:189
     opal_status st = opal_particles_count(c, species, n);
@@ -1360,7 +1420,7 @@ opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, 
 opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
                            const int64_t* nbins, int weight_kind, int log_density_adjust, double* counts, double* total) {
     CHECK_CTX(c);
-    if (species == OPAL_ELECTRON && !ensure_compact(c)) return (opal_status)c->status;
+    if (!settle(c, species)) return (opal_status)c->status;
     if (!hgram_args_ok(species, ndim, q) || !gmin || !bin_sz || !nbins || !counts || !total) return OPAL_EINVAL;
     if (weight_kind != OPAL_W_WEIGHT && weight_kind != OPAL_W_ENERGY) return OPAL_EINVAL;
     long long nb[2] = {1, 1};
@@ -1395,7 +1455,8 @@ opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, dou
     BucketDev be, bi;
     PhotonDev pp;
     const bool fused_ke = c->ke_fused && c->bk[0].allocated;
-    if (!fused_ke && !ensure_compact(c)) return (opal_status)c->status;
+    if (!fused_ke && !settle(c, OPAL_ELECTRON)) return (opal_status)c->status;
+    if (!settle(c, OPAL_ION)) return (opal_status)c->status;
     const bool he = c->bk[0].allocated && !fused_ke, hi = c->bk[1].allocated, hp = c->ph[0].cap > 0;
     if (he) be = bdev(c, 0);
     if (hi) bi = bdev(c, 1);

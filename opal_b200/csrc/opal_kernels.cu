@@ -214,706 +214,8 @@ __global__ void __launch_bounds__(BLOCK) k_push(GridDev g, BucketDev b, StepPara
 }
 
 #ifdef OPAL_FAST
-// --------------------------------------------------------------------------------------------
-// K1f: the headline kernel -- electrons, lean (x, u, w) layout, fused gather + Vay push + deposit,
-// fast build only.  Same mathematics as k_push<ELECTRON,false,true>, reorganised for the FP64
-// pipe (which, not HBM, bounds this kernel -- see DESIGN.md):
-//   * the order-2 spline is evaluated through R(d), the fraction of the particle's triangle to the
-//     right of a face at displacement d:  W(node j) = R(j-1/2-x) - R(j+1/2-x) and
-//     Cell::flux(x_i, x_f) = R(x_f) - R(x_i)  (verified to 3e-16 against yee.rs:140-204), so the 7
-//     gather weights, the 3 non-zero fluxes of a stayer and the 4 deposit weights come from three
-//     R values per position instead of 7 + 5 + 4 branchy evaluations;
-//   * every division by gamma, dt, dx becomes a multiplication by a reciprocal (rsqrt for 1/gamma);
-//     the per-particle factors q/dt, q/dx, q c/dx are applied once per CELL after the reduction.
-// Results differ from the literal formulas only by re-association (<= 1e-15 relative), far inside the
-// 1e-10 parity tolerance; the strict build keeps the literal arithmetic.
-// --------------------------------------------------------------------------------------------
-#ifndef OPAL_PUSH_STAGES
-#define OPAL_PUSH_STAGES 4
-#endif
-__device__ __forceinline__ void cp_async8(void* smem, const void* gmem) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-
-struct RFaces { double a, b, c; };   // R at the faces -1/2, +1/2, +3/2 of the particle's cell
-// 8 FP64 instructions: |h| enters through the operand modifier, the two branches of the spline share
-// one square ((1 - |h|)^2 is (1+h)^2 left of the cell centre and (1-h)^2 right of it).
-__device__ __forceinline__ RFaces r_faces(double x) {
-    const double h = x - 0.5;
-    const bool lo = h < 0.0;
-    const double q = 0.5 * (h * h);
-    const double t = 1.0 - fabs(h);
-    const double tt = 0.5 * (t * t);
-    RFaces r;
-    r.a = lo ? 1.0 - q : 1.0;
-    r.b = lo ? tt : 1.0 - tt;
-    r.c = lo ? 0.0 : q;
-    return r;
-}
-
-// MUFU.RSQ64H / MUFU.RCP64H seeds (~2^-20 relative: they see only the high word of the operand) refined
-// by ONE third-order step, error ~ e^3 < 2^-58: 5 (rsqrt, +1 for sqrt) / 3 (rcp) FP64 instructions
-// instead of the ~10 of the IEEE-rounded library sequences with their slow-path branches.  Operands here are
-// gamma^2-like quantities in [1, 1e300): no zero / denormal / infinity handling is needed.
-__device__ __forceinline__ double rsqrt_seed(double x) { double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
-__device__ __forceinline__ double rcp_seed(double x) { double y; asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
-__device__ __forceinline__ double fast_rsqrt(double x) {
-    const double y0 = rsqrt_seed(x);
-    const double t = x * y0;
-    const double e = fma(-t, y0, 1.0);             // 1 - x y0^2
-    const double pe = fma(0.375, e, 0.5) * e;      // rsqrt(x) = y0 (1 + e/2 + 3 e^2/8 + O(e^3))
-    return fma(y0, pe, y0);
-}
-__device__ __forceinline__ void fast_rsqrt_sqrt(double x, double& rs, double& sq) {
-    const double y0 = rsqrt_seed(x);
-    const double t = x * y0;                       // ~ sqrt(x)
-    const double e = fma(-t, y0, 1.0);
-    const double pe = fma(0.375, e, 0.5) * e;
-    rs = fma(y0, pe, y0);
-    sq = fma(t, pe, t);
-}
-__device__ __forceinline__ double fast_sqrt(double x) { double rs, sq; fast_rsqrt_sqrt(x, rs, sq); return sq; }
-__device__ __forceinline__ double fast_rcp(double x) {
-    const double y0 = rcp_seed(x);
-    const double e = fma(-x, y0, 1.0);             // 1/x = y0 (1 + e + e^2 + O(e^3))
-    return fma(y0, fma(e, e, e), y0);
-}
-
-// Per-cell gather coefficients of the fast kernel (one copy per warp in shared memory).  With the R-face
-// values a, b, c of a particle at offset x and xm = 1 - x:
-//   alpha E_x   = ex1 + xm^2 dex0 + x^2 dex2        (dex0 = alpha/2 (Ex[j-1]-Ex[j]), dex2 = alpha/2 (Ex[j+1]-Ex[j]))
-//   alpha E_y   = ey0 + a dey0 + b dey1 + c dey2     (dey_k = alpha (Ey[j+k]-Ey[j-1+k]))
-//   alpha c B_y = ty1 + xm^2 dty0 + x^2 dty2, ...    (the Vay rotation vector tau directly)
-// i.e. the spline weights (yee.rs:499-529) with the partition of unity folded into per-cell differences,
-// and alpha = q dt / 2 m c (electron.rs:273) applied once per cell instead of once per particle.
-struct CellPre { double ex1, dex0, dex2, ey0, dey[3], ez0, dez[3], tx, ty1, dty0, dty2, tz1, dtz0, dtz2; };
-__constant__ signed char c_pre_ia[18] = {1, 0, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 12, 14, 16, 15, 17};
-__constant__ signed char c_pre_ib[18] = {18, 1, 1, 18, 3, 4, 5, 18, 7, 8, 9, 18, 18, 13, 13, 18, 16, 16};
-__constant__ signed char c_pre_k[18] = {0, 1, 1, 0, 0, 0, 0, 0, 0, 0, 0, 2, 2, 3, 3, 2, 3, 3};   // alpha, alpha/2, alpha c, alpha c/2
-
-#ifndef OPAL_PUSH_WPB
-#define OPAL_PUSH_WPB 4
-#endif
-#ifndef OPAL_PUSH_SMEM_FIELDS
-#define OPAL_PUSH_SMEM_FIELDS 1
-#endif
-#ifndef OPAL_PUSH_ILP
-#define OPAL_PUSH_ILP 1
-#endif
-#ifndef OPAL_PUSH_MINBLK
-#define OPAL_PUSH_MINBLK 4
-#endif
-// OPAL_PUSH_HOLES (experimental, default off): a particle that stays in its cell is written back to the slot it was
-// read from; a particle that leaves marks its slot (x := OPAL_HOLE_MARK).  The push records the slot indices of all
-// holes of a cell (new and left over) in the cell's hole list; k_pull, which owns the destination bucket, drops the
-// arriving movers into the listed holes and appends the rest.  Holes that find no arrival simply stay (the push skips
-// marked slots), so count[c] counts SLOTS IN USE, live or hole, between steps; any consumer other than the step kernels
-// sees the buckets only after k_compact_cells has closed the holes (host: ensure_compact).
-// Measured at the bench size (1e9 electrons, 1e6 cells, B200): the push no longer rewrites w behind the first mover of a
-// cell (write traffic 39.8 -> 32 B/particle) and drops from 15.4 to 14.5 ms, but the arrivals now land in scattered
-// 8-byte slots whose 32-byte sectors have long left the L2: ~48 x 5 partial-sector read-modify-writes per cell make
-// k_pull 1.5 -> 4.0-4.5 ms.  Net loss (19.1-20.0 vs 17.0 ms per step), so the default stays the in-push shift; the way
-// to keep the push's gain is to consume the strips inside the NEXT push, while the cell's sectors stream through L2.
-// OPAL_PUSH_HOLES == 2 (experimental): in-place stayers as above, but the push closes its own holes before it leaves
-// the cell ("tail fill" from a shared-memory hole list, while the sectors are still in L2): count[] stays the live count
-// and k_pull and every other consumer are untouched.  Measured: DRAM writes drop as intended, but the four dependent
-// round trips of the fill at the end of every cell cost the push more than the 8 B/particle save (16.0 vs 15.4-15.6 ms),
-// step 17.5 vs 17.0-17.1 ms.  Also a net loss; kept selectable for the record.
-#ifndef OPAL_PUSH_HOLES
-#define OPAL_PUSH_HOLES 0
-#endif
-#ifndef OPAL_HOLE_LIST
-#define OPAL_HOLE_LIST 256             // slot indices per warp (shared memory); a cell with more movers falls back to the shift
-#endif
-#define OPAL_HOLE_MARK (__longlong_as_double(0x7ff8dead0000beefll))   // a quiet NaN: never a valid offset
-__device__ __forceinline__ bool is_hole(double x) { return x != x; }
-// BX0: B_x == 0 on the whole grid (the solver never updates it, yee.rs:839-848) => tau_x terms drop out.
-// KE:  also accumulate total_kinetic_energy (electron.rs:122-126: w u^2 mc^2 / (gamma + 1), mod.rs:227-240) of the
-//      pushed particles into *ke_out, so the energy diagnostic that follows a step costs no second pass over HBM.
-// shift the live particles of one lean bucket down over its holes (one warp); returns the live count
-__device__ __forceinline__ int compact_cell(const BucketDev& b, long long base, int n, int lane, unsigned lt_mask) {
-    __syncwarp();
-    int wr = 0;
-    for (int k0 = 0; k0 < n; k0 += 32) {
-        const int i = k0 + lane;
-        double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0, v4 = 0.0;
-        bool live = false;
-        if (i < n) {
-            const long long s = base + i;
-            v0 = b.f[F_X][s]; live = !is_hole(v0);
-            v1 = b.f[F_UX][s]; v2 = b.f[F_UY][s]; v3 = b.f[F_UZ][s]; v4 = b.f[F_W][s];
-        }
-        const unsigned m_live = __ballot_sync(FULLMASK, live);
-        __syncwarp();        // every lane has read its slot before any lane overwrites a lower one
-        const int pos = wr + __popc(m_live & lt_mask);
-        if (live && pos != i) {
-            const long long s = base + pos;
-            b.f[F_X][s] = v0; b.f[F_UX][s] = v1; b.f[F_UY][s] = v2; b.f[F_UZ][s] = v3; b.f[F_W][s] = v4;
-        }
-        wr += __popc(m_live);
-    }
-    __syncwarp();
-    return wr;
-}
-
-// closes the holes of every cell (host: ensure_compact, before anything but the step kernels reads the buckets)
-__global__ void __launch_bounds__(256) k_compact_cells(BucketDev b, const int* __restrict__ hcount) {
-    const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    for (int c = blockIdx.x * 8 + (threadIdx.x >> 5); c < b.ncell; c += gridDim.x * 8) {
-        const int n = b.count[c];
-        if (n == 0) continue;
-        // cells without a recorded hole are skipped; k_pull keeps hcount current (holes left after the arrivals)
-        if (hcount[c] == 0) continue;
-        const int live = compact_cell(b, b.start[c], n, lane, lt_mask);
-        if (lane == 0) b.count[c] = live;
-    }
-}
-
-// SP: OPAL_ELECTRON -> Vay push (electron.rs:268-330); OPAL_ION -> Boris push (ion.rs:168-214) in the same reciprocal
-// arithmetic, alpha and the deposited charge from Z* and A (ion.rs:170-172).
-template <bool BX0, bool KE, int SP>
-__global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK) k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers,
-                                                           int* __restrict__ seg_count, StripRec* __restrict__ strips,
-                                                           int* __restrict__ scount, StatusDev* __restrict__ st, double* __restrict__ ke_out,
-                                                           int* __restrict__ holes, int* __restrict__ hcount) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
-    constexpr int ILP = OPAL_PUSH_ILP;          // particles per lane per iteration (independent dependency chains)
-    constexpr int CH = 32 * ILP;
-    const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const int warps_total = gridDim.x * OPAL_PUSH_WPB;
-    const double qsp = SP == OPAL_ELECTRON ? OPAL_QE : b.z_star * OPAL_E;
-    const double alpha = SP == OPAL_ELECTRON ? OPAL_QE * g.dt / (2.0 * OPAL_ME * OPAL_C) : qsp * g.dt / (2.0 * (b.mass_number * OPAL_MP) * OPAL_C);
-    const double ac = alpha * OPAL_C;
-    const double kdt = OPAL_C * g.dt / g.dx;
-    bool cfl = false, cap_err = false;
-    double ske = 0.0;
-    double* const fx = b.f[F_X]; double* const fux = b.f[F_UX]; double* const fuy = b.f[F_UY]; double* const fuz = b.f[F_UZ];
-    double* const fw = b.f[F_W];
-
-    const int MC = sp.cell_mover_cap;
-    for (int c = blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5); c < b.ncell; c += warps_total) {
-        const int n = b.count[c];
-        if (n == 0) {
-            if (lane < 2) scount[2 * c + lane] = 0;
-#if OPAL_PUSH_HOLES == 1
-            if (lane == 2) hcount[c] = 0;
-#endif
-            continue;
-        }
-        const long long base = b.start[c];
-        const int j = c + g.left;
-        int mloc_l = 0, mloc_r = 0;   // left / right movers of this cell so far (warp-uniform): slots in its two strips
-#if OPAL_PUSH_HOLES
-        int n_holes = 0;              // holes of this cell so far (warp-uniform)
-#endif
-#if OPAL_PUSH_HOLES == 2
-        __shared__ int s_holes[OPAL_PUSH_WPB][OPAL_HOLE_LIST];
-        int* const hole_list = s_holes[threadIdx.x >> 5];
-#endif
-        // the 18 field values every lane of this warp gathers from -> 18 per-cell gather coefficients (CellPre),
-        // one copy per warp in shared memory
-        __shared__ double s_raw[OPAL_PUSH_WPB][20];
-        __shared__ CellPre s_pre[OPAL_PUSH_WPB];
-        double* const raw = s_raw[threadIdx.x >> 5];
-        CellPre& P = s_pre[threadIdx.x >> 5];
-        __syncwarp();
-        if (lane < 3) { raw[lane] = __ldg(g.ex + j - 1 + lane); raw[12 + lane] = __ldg(g.by + j - 1 + lane); raw[15 + lane] = __ldg(g.bz + j - 1 + lane); }
-        if (lane < 4) { raw[3 + lane] = __ldg(g.ey + j - 1 + lane); raw[7 + lane] = __ldg(g.ez + j - 1 + lane); }
-        if (lane == 0) { raw[11] = BX0 ? 0.0 : __ldg(g.bx + j); raw[18] = 0.0; }
-        __syncwarp();
-        if (lane < 18) {
-            const int k = c_pre_k[lane];
-            const double coef = (k & 2 ? ac : alpha) * (k & 1 ? 0.5 : 1.0);
-            reinterpret_cast<double*>(&P)[lane] = coef * (raw[c_pre_ia[lane]] - raw[c_pre_ib[lane]]);
-        }
-        __syncwarp();
-        double sjx0 = 0.0, sjx1 = 0.0, sjx2 = 0.0, sjy0 = 0.0, sjy1 = 0.0, sjy2 = 0.0, sjz0 = 0.0, sjz1 = 0.0, sjz2 = 0.0;
-        double sr0 = 0.0, sr1 = 0.0, sr2 = 0.0, sr3 = 0.0;
-
-#if OPAL_PUSH_STAGES > 0
-        // cp.async ring: the five particle streams of the next OPAL_PUSH_STAGES-1 iterations are in flight
-        // into this warp's shared-memory stages (LDGSTS, no registers held); every lane reads back only
-        // the element it copied itself, so per-thread wait_group is the only synchronisation needed.
-        // In-place safety: chunk k is waited for at the top of iteration k, before any store of iteration k,
-        // and earlier iterations only store below slot 32k.
-        constexpr int NST = OPAL_PUSH_STAGES;
-        __shared__ double s_ring[OPAL_PUSH_WPB][NST][5][CH];
-        double (*ring)[5][CH] = s_ring[threadIdx.x >> 5];
-        __syncwarp();
-#pragma unroll
-        for (int st_ = 0; st_ < NST - 1; st_++) {
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                const int i = st_ * CH + q * 32 + lane;
-                if (i < n) {
-                    const long long s = base + i;
-                    cp_async8(&ring[st_][0][q * 32 + lane], fx + s); cp_async8(&ring[st_][1][q * 32 + lane], fux + s);
-                    cp_async8(&ring[st_][2][q * 32 + lane], fuy + s); cp_async8(&ring[st_][3][q * 32 + lane], fuz + s);
-                    cp_async8(&ring[st_][4][q * 32 + lane], fw + s);
-                }
-            }
-            cp_async_commit();
-        }
-        int stage = 0;
-#else
-        // software pipeline: the next iteration's loads are issued before this iteration's stores
-        double nx0[ILP], nx1[ILP], nx2[ILP], nx3[ILP], nx4[ILP];
-#pragma unroll
-        for (int q = 0; q < ILP; q++) {
-            nx0[q] = nx1[q] = nx2[q] = nx3[q] = nx4[q] = 0.0;
-            const int i = q * 32 + lane;
-            if (i < n) { const long long s = base + i; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
-        }
-#endif
-        int written = 0;
-        for (int k0 = 0; k0 < n; k0 += CH) {
-            double x[ILP], W[ILP], xn[ILP], igam[ILP], gam2[ILP], fl[ILP];
-            V3 u[ILP];
-            RFaces ro[ILP];
-            int d[ILP];
-            bool valid[ILP];
-#if OPAL_PUSH_HOLES == 1
-            bool was_hole[ILP];
-#endif
-#if OPAL_PUSH_STAGES > 0
-            cp_async_wait<NST - 2>();
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                valid[q] = k0 + q * 32 + lane < n;
-                const int e = q * 32 + lane;
-                x[q] = valid[q] ? ring[stage][0][e] : 0.0;
-#if OPAL_PUSH_HOLES == 1
-                was_hole[q] = valid[q] && is_hole(x[q]);      // a hole no arrival has filled yet: skipped, re-listed below
-                if (was_hole[q]) { valid[q] = false; x[q] = 0.0; }
-#endif
-                u[q] = {valid[q] ? ring[stage][1][e] : 0.0, valid[q] ? ring[stage][2][e] : 0.0, valid[q] ? ring[stage][3][e] : 0.0};
-                W[q] = valid[q] ? ring[stage][4][e] : 0.0;
-            }
-            {
-                const int pst = stage == 0 ? NST - 1 : stage - 1;     // the stage consumed in the previous iteration
-#pragma unroll
-                for (int q = 0; q < ILP; q++) {
-                    const int in = k0 + (NST - 1) * CH + q * 32 + lane;
-                    if (in < n) {
-                        const long long s = base + in;
-                        cp_async8(&ring[pst][0][q * 32 + lane], fx + s); cp_async8(&ring[pst][1][q * 32 + lane], fux + s);
-                        cp_async8(&ring[pst][2][q * 32 + lane], fuy + s); cp_async8(&ring[pst][3][q * 32 + lane], fuz + s);
-                        cp_async8(&ring[pst][4][q * 32 + lane], fw + s);
-                    }
-                }
-                cp_async_commit();
-                stage = stage == NST - 1 ? 0 : stage + 1;
-            }
-#else
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                x[q] = nx0[q]; u[q] = {nx1[q], nx2[q], nx3[q]}; W[q] = nx4[q];
-                valid[q] = k0 + q * 32 + lane < n;
-#if OPAL_PUSH_HOLES == 1
-                was_hole[q] = valid[q] && is_hole(x[q]);
-                if (was_hole[q]) { valid[q] = false; x[q] = 0.0; u[q] = {0.0, 0.0, 0.0}; W[q] = 0.0; }
-#endif
-            }
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                const int in = k0 + CH + q * 32 + lane;
-                if (in < n) { const long long s = base + in; nx0[q] = fx[s]; nx1[q] = fux[s]; nx2[q] = fuy[s]; nx3[q] = fuz[s]; nx4[q] = fw[s]; }
-            }
-#endif
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                // ---- gather (yee.rs:499-529): alpha E and tau = alpha c B from the per-cell coefficients ----
-                ro[q] = r_faces(x[q]);
-                const double xm = 1.0 - x[q], xm2 = xm * xm, x2 = x[q] * x[q];
-                V3 aE, tv;
-                aE.x = fma(x2, P.dex2, fma(xm2, P.dex0, P.ex1));
-                aE.y = fma(ro[q].c, P.dey[2], fma(ro[q].b, P.dey[1], fma(ro[q].a, P.dey[0], P.ey0)));
-                aE.z = fma(ro[q].c, P.dez[2], fma(ro[q].b, P.dez[1], fma(ro[q].a, P.dez[0], P.ez0)));
-                tv.x = BX0 ? 0.0 : P.tx;
-                tv.y = fma(x2, P.dty2, fma(xm2, P.dty0, P.ty1));
-                tv.z = fma(x2, P.dtz2, fma(xm2, P.dtz0, P.tz1));
-                double gam;
-                if (SP == OPAL_ELECTRON) {
-                    // ---- Vay push (electron.rs:268-330) ----
-                    // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma
-                    const double ig = fast_rsqrt(fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0))));
-                    const V3 uxt = BX0 ? V3{u[q].y * tv.z - u[q].z * tv.y, -(u[q].x * tv.z), u[q].x * tv.y} : cross(u[q], tv);
-                    const V3 ue = u[q] + aE;
-                    const V3 u_prime = {fma(ig, uxt.x, ue.x) + aE.x, fma(ig, uxt.y, ue.y) + aE.y, fma(ig, uxt.z, ue.z) + aE.z};
-                    const double gp2 = fma(u_prime.x, u_prime.x, fma(u_prime.y, u_prime.y, fma(u_prime.z, u_prime.z, 1.0)));
-                    const double u_star = BX0 ? fma(u_prime.y, tv.y, u_prime.z * tv.z) : dot(u_prime, tv);
-                    const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
-                    const double hs = 0.5 * (gp2 - tau2);
-                    gam2[q] = hs + fast_sqrt(fma(hs, hs, fma(u_star, u_star, tau2)));
-                    fast_rsqrt_sqrt(gam2[q], igam[q], gam);
-                    // u = s (u' + (u'.t) t + u' x t), t = tau/gamma, s = 1/(1+t^2)   ==   (gamma^2 u' + (u'.tau) tau + gamma u' x tau) / (gamma^2 + tau^2)
-                    const double inv = fast_rcp(gam2[q] + tau2);
-                    const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
-                    V3 w = {fma(gam, pxt.x, gam2[q] * u_prime.x), fma(gam, pxt.y, gam2[q] * u_prime.y), fma(gam, pxt.z, gam2[q] * u_prime.z)};
-                    if (!BX0) w.x = fma(u_star, tv.x, w.x);
-                    w.y = fma(u_star, tv.y, w.y); w.z = fma(u_star, tv.z, w.z);
-                    u[q] = inv * w;
-                } else {
-                    // ---- Boris push (ion.rs:168-214): u- = u + alpha E; u' = u- + (u- x tau)/gamma-;
-                    //      u+ = u- + (u' x tau) 2 gamma- / (gamma-^2 + tau^2); u = u+ + alpha E   (tau = alpha c B) ----
-                    const V3 um = u[q] + aE;
-                    const double ig = fast_rsqrt(fma(um.x, um.x, fma(um.y, um.y, fma(um.z, um.z, 1.0))));
-                    const V3 mxt = BX0 ? V3{um.y * tv.z - um.z * tv.y, -(um.x * tv.z), um.x * tv.y} : cross(um, tv);
-                    const V3 u_prime = {fma(ig, mxt.x, um.x), fma(ig, mxt.y, um.y), fma(ig, mxt.z, um.z)};
-                    const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
-                    const double s2 = (2.0 * ig) * fast_rcp(fma(tau2 * ig, ig, 1.0));
-                    const V3 pxt = BX0 ? V3{u_prime.y * tv.z - u_prime.z * tv.y, -(u_prime.x * tv.z), u_prime.x * tv.y} : cross(u_prime, tv);
-                    u[q] = {fma(s2, pxt.x, um.x) + aE.x, fma(s2, pxt.y, um.y) + aE.y, fma(s2, pxt.z, um.z) + aE.z};
-                    gam2[q] = fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, fma(u[q].z, u[q].z, 1.0)));
-                    fast_rsqrt_sqrt(gam2[q], igam[q], gam);
-                }
-                const double dxi = (kdt * igam[q]) * u[q].x;
-                if (valid[q] && !(dxi < 1.0)) cfl = true;
-                xn[q] = x[q] + dxi;
-                fl[q] = floor(xn[q]);
-                d[q] = fl[q] < 0.0 ? -1 : (fl[q] > 0.0 ? 1 : 0);
-                xn[q] -= fl[q];
-                if (KE) {
-                    // leavers through an open slab edge are deleted (mod.rs:372-373): not part of the population any more
-                    const bool dead = (c == 0 && d[q] < 0 && sp.route_left == 0) || (c == b.ncell - 1 && d[q] > 0 && sp.route_right == 0);
-                    const double u2 = fma(u[q].x, u[q].x, fma(u[q].y, u[q].y, u[q].z * u[q].z));
-                    const double e = (W[q] * u2) * fast_rcp(gam + 1.0);      // invalid lanes carry W = 0, u = 0
-                    ske += dead ? 0.0 : e;
-                }
-            }
-            unsigned m_stay[ILP], m_l[ILP], m_r[ILP];
-            int n_l = 0, n_r = 0;
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                m_stay[q] = __ballot_sync(FULLMASK, valid[q] && d[q] == 0);
-                m_l[q] = __ballot_sync(FULLMASK, valid[q] && d[q] < 0);
-                m_r[q] = __ballot_sync(FULLMASK, valid[q] && d[q] > 0);
-                n_l += __popc(m_l[q]); n_r += __popc(m_r[q]);
-            }
-            // Movers go to this cell's private left / right strip of MC records each (no atomics, no
-            // latency); only the excess beyond MC is appended to the shared segmented buffer.
-            int base_l = mloc_l, base_r = mloc_r;
-            int gbase = 0;
-            const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)(k0 / CH) * 0x85EBCA77u) >> 22);   // hashed like k_push: a dense cell spreads over all segments
-            const int first_over_l = mloc_l > MC ? mloc_l : MC, first_over_r = mloc_r > MC ? mloc_r : MC;
-            const int over_l = mloc_l + n_l > first_over_l ? mloc_l + n_l - first_over_l : 0;
-            const int over_r = mloc_r + n_r > first_over_r ? mloc_r + n_r - first_over_r : 0;
-            if (over_l + over_r) {
-                if (lane == 0) gbase = atomicAdd(seg_count + seg, over_l + over_r);
-                gbase = __shfl_sync(FULLMASK, gbase, 0);
-            }
-            mloc_l += n_l; mloc_r += n_r;
-#pragma unroll
-            for (int q = 0; q < ILP; q++) {
-                const int i = k0 + q * 32 + lane;
-                if (valid[q] && d[q] == 0) {
-#if OPAL_PUSH_HOLES
-                    // stayers are written back to the slot they were read from: no shift, w is never rewritten
-                    const long long s = base + i;
-                    fx[s] = xn[q]; fux[s] = u[q].x; fuy[s] = u[q].y; fuz[s] = u[q].z;
-#else
-                    const int pos = written + __popc(m_stay[q] & lt_mask);
-                    const long long s = base + pos;
-                    fx[s] = xn[q]; fux[s] = u[q].x; fuy[s] = u[q].y; fuz[s] = u[q].z;
-                    if (pos != i) fw[s] = W[q];
-#endif
-                    // ---- deposit of a stayer (yee.rs:584-609) ----
-                    const RFaces rn = r_faces(xn[q]);
-                    sjx0 += W[q] * (rn.a - ro[q].a); sjx1 += W[q] * (rn.b - ro[q].b); sjx2 += W[q] * (rn.c - ro[q].c);
-                    const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
-                    sr0 += W[q] * w3; sr1 += W[q] * w0; sr2 += W[q] * w1; sr3 += W[q] * w2;
-                    const double tw = W[q] * igam[q], ty = tw * u[q].y, tz = tw * u[q].z;
-                    sjy0 += ty * w0; sjy1 += ty * w1; sjy2 += ty * w2;
-                    sjz0 += tz * w0; sjz1 += tz * w1; sjz2 += tz * w2;
-                } else if (valid[q]) {
-                    const bool left = d[q] < 0;
-                    const int r = left ? base_l + __popc(m_l[q] & lt_mask) : base_r + __popc(m_r[q] & lt_mask);
-                    const double gam = gam2[q] * igam[q], px = x[q] - fl[q];
-#if OPAL_PUSH_HOLES
-                    fx[base + i] = OPAL_HOLE_MARK;     // the vacated slot
-#endif
-                    if (r < MC) {
-                        StripRec rec = {xn[q], px, u[q].x, u[q].y, u[q].z, W[q]};
-                        strips[((long long)c * 2 + (left ? 0 : 1)) * MC + r] = rec;
-                    } else {
-                        const int rg = gbase + (left ? r - first_over_l : over_l + (r - first_over_r));
-                        if (rg < sp.mover_cap) {
-                            opal_migrant m;
-                            m.cell = (long long)c + d[q]; m.x = xn[q]; m.prev_x = px; m.u[0] = u[q].x; m.u[1] = u[q].y; m.u[2] = u[q].z;
-                            m.weight = W[q]; m.gamma = gam; m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0;
-                            m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
-                            movers[(long long)seg * sp.mover_cap + rg] = m;
-                        } else cap_err = true;
-                    }
-                }
-                written += __popc(m_stay[q]);
-                base_l += __popc(m_l[q]); base_r += __popc(m_r[q]);
-#if OPAL_PUSH_HOLES == 1
-                {   // list every hole of this chunk: slots just vacated and slots still empty from earlier steps
-                    const bool hole = was_hole[q] || (valid[q] && d[q] != 0);
-                    const unsigned m_hole = __ballot_sync(FULLMASK, hole);
-                    if (hole) {
-                        const int k = n_holes + __popc(m_hole & lt_mask);
-                        if (k < 2 * MC) holes[(long long)c * (2 * MC) + k] = i;
-                    }
-                    n_holes += __popc(m_hole);
-                }
-#elif OPAL_PUSH_HOLES == 2
-                {   // the slots this chunk vacated, kept in the warp's shared-memory list for the tail fill below
-                    const unsigned m_hole = m_l[q] | m_r[q];
-                    if ((m_hole >> lane) & 1u) {
-                        const int k = n_holes + __popc(m_hole & lt_mask);
-                        if (k < OPAL_HOLE_LIST) hole_list[k] = i;
-                    }
-                    n_holes += __popc(m_hole);
-                }
-#endif
-            }
-        }
-#if OPAL_PUSH_STAGES > 0
-        cp_async_wait<0>();
-#endif
-#if OPAL_PUSH_HOLES == 1
-        if (n_holes > 2 * MC) {
-            // rare: more holes than the list holds.  Close them all now by shifting the live particles down.
-            const int live = compact_cell(b, base, n, lane, lt_mask);
-            if (lane == 0) b.count[c] = live;
-            n_holes = 0;
-        }
-        if (lane == 0) { scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC; hcount[c] = n_holes; }
-#elif OPAL_PUSH_HOLES == 2
-        // Tail fill: the bucket shrinks by n_holes slots; the live particles of the cut-off tail [n_new, n) move into the
-        // holes below n_new (exactly as many of one as of the other).  The sectors involved were written by this warp
-        // microseconds ago, so the scattered 8-byte moves merge in L2 instead of costing DRAM read-modify-writes.
-        if (n_holes > OPAL_HOLE_LIST) {
-            const int live = compact_cell(b, base, n, lane, lt_mask);      // rare: list too short, shift instead
-            if (lane == 0) b.count[c] = live;
-        } else if (n_holes > 0) {
-            const int n_new = n - n_holes;
-            __syncwarp();                                     // hole_list and this cell's stores are visible warp-wide
-            int n_low = 0;
-            for (int k0 = 0; k0 < n_holes; k0 += 32) {        // keep the holes below n_new, in place
-                const int k = k0 + lane;
-                const int hs = k < n_holes ? hole_list[k] : 0x7fffffff;
-                const unsigned m_low = __ballot_sync(FULLMASK, hs < n_new);
-                __syncwarp();
-                if (hs < n_new) hole_list[n_low + __popc(m_low & lt_mask)] = hs;
-                n_low += __popc(m_low);
-            }
-            __syncwarp();
-            int taken = 0;
-            for (int t0 = n_new; t0 < n && taken < n_low; t0 += 32) {
-                const int t = t0 + lane;
-                double v0 = 0.0;
-                bool live = false;
-                if (t < n) { v0 = __ldcg(fx + base + t); live = !is_hole(v0); }
-                const unsigned m_live = __ballot_sync(FULLMASK, live);
-                if (live) {
-                    const long long from = base + t, to = base + hole_list[taken + __popc(m_live & lt_mask)];
-                    fx[to] = v0; fux[to] = __ldcg(fux + from); fuy[to] = __ldcg(fuy + from); fuz[to] = __ldcg(fuz + from); fw[to] = __ldcg(fw + from);
-                }
-                taken += __popc(m_live);
-            }
-            if (lane == 0) b.count[c] = n_new;
-        }
-        if (lane == 0) { scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC; }
-#else
-        if (lane == 0) {
-            b.count[c] = written;
-            scount[2 * c] = mloc_l < MC ? mloc_l : MC; scount[2 * c + 1] = mloc_r < MC ? mloc_r : MC;
-        }
-#endif
-
-        // one shuffle reduction and <= 13 atomics per CELL; q/dt, q c/dx, q/dx applied here
-        const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
-        double v13[13] = {kx * sjx0, kx * sjx1, kx * sjx2, ky * sjy0, ky * sjy1, ky * sjy2, ky * sjz0, ky * sjz1, ky * sjz2,
-                          kr * sr0, kr * sr1, kr * sr2, kr * sr3};
-#pragma unroll
-        for (int k = 0; k < 13; k++) v13[k] = warp_sum(v13[k]);
-        double mine = 0.0;
-        double* dst = nullptr;
-#pragma unroll
-        for (int k = 0; k < 13; k++) {
-            if (lane == k) {
-                mine = v13[k];
-                dst = k < 3 ? g.jx + j - 1 + k : (k < 6 ? g.jy + j - 1 + (k - 3) : (k < 9 ? g.jz + j - 1 + (k - 6) : g.rho + j - 2 + (k - 9)));
-            }
-        }
-        if (dst && mine != 0.0) atomicAdd(dst, mine);
-    }
-    if (cfl) atomicOr(&st->err, ERR_CFL);
-    if (cap_err) atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_MOVERS);
-    if (KE) {
-        ske = warp_sum(ske) * (1.0e6 * OPAL_ME_MEV * OPAL_E);
-        if (lane == 0 && ske != 0.0) atomicAdd(ke_out, ske);
-    }
-}
-
-// K2p: pull.  One warp per DESTINATION cell c: it reads the right-mover strip of cell c-1 and the
-// left-mover strip of cell c+1 (all destined to c, |dxi| < 1), appends them to bucket c -- the
-// warp owns count[c], so no slot atomics -- and accumulates their deposit (yee.rs:584-609) in
-// registers: one shuffle reduction + <= 15 atomics per cell.  Edge cells route through the slab
-// boundary (mod.rs:290-373): periodic self-neighbour => the strips of the opposite edge; remote
-// neighbour => the edge strips are copied to the outbox here and arrive through the inbox path.
-#ifndef OPAL_PULL_SUB
-#define OPAL_PULL_SUB 16
-#endif
-#if OPAL_PUSH_HOLES == 1 && OPAL_PULL_SUB != 32
-#error "OPAL_PUSH_HOLES=1 needs OPAL_PULL_SUB=32"
-#endif
-template <int W> __device__ __forceinline__ double group_sum(double v, unsigned mask) {
-#pragma unroll
-    for (int o = W / 2; o; o >>= 1) v += __shfl_xor_sync(mask, v, o, W);
-    return v;
-}
-#ifndef OPAL_PULL_MINBLK
-#define OPAL_PULL_MINBLK 4
-#endif
-__global__ void __launch_bounds__(256, OPAL_PULL_MINBLK) k_pull(GridDev g, BucketDev b, StepParams sp, const StripRec* __restrict__ strips,
-                                               const int* __restrict__ scount, opal_migrant* __restrict__ out_l,
-                                               opal_migrant* __restrict__ out_r, opal_migrant* __restrict__ overflow,
-                                               StatusDev* __restrict__ st, const int* __restrict__ holes, int* __restrict__ hcount) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
-    // OPAL_PULL_SUB lanes serve one cell (32: a warp per cell; 16: two cells per warp -- twice the cells in flight per SM
-    // for a kernel that waits on memory: ~48 arrivals per cell are three 16-lane trips instead of two 32-lane ones)
-    constexpr int SUB = OPAL_PULL_SUB;
-    constexpr int CPW = 32 / SUB;                                   // cells per warp
-    const int lane = threadIdx.x & (SUB - 1);                      // lane within the cell's group
-    const unsigned gmask = SUB == 32 ? FULLMASK : (((1u << SUB) - 1u) << ((threadIdx.x & 31) & ~(SUB - 1)));
-    const int groups_total = gridDim.x * 8 * CPW;
-    const int MC = sp.cell_mover_cap;
-    const int nc = b.ncell;
-    for (int c = (blockIdx.x * 8 + (threadIdx.x >> 5)) * CPW + ((threadIdx.x & 31) / SUB); c < nc; c += groups_total) {
-        // source strips: right-movers of the left neighbour cell, left-movers of the right neighbour cell
-        int src_l = c - 1, src_r = c + 1;
-        if (src_l < 0) src_l = sp.route_left == 1 ? nc - 1 : -1;
-        if (src_r >= nc) src_r = sp.route_right == 1 ? 0 : -1;
-        const int n_from_l = src_l >= 0 ? scount[2 * src_l + 1] : 0;
-        const int n_from_r = src_r >= 0 ? scount[2 * src_r] : 0;
-        // leavers of the edge cells: counted (mod.rs:284) and, with a remote neighbour, sent
-        if (c == 0) {
-            const int n = scount[0];
-            if (lane == 0 && n) atomicAdd(&st->gone[0], n);
-            if (sp.route_left == 2 && n) {
-                int o = 0;
-                if (lane == 0) o = atomicAdd(&st->n_out[0], n);
-                o = __shfl_sync(gmask, o, 0, SUB);
-                for (int i = lane; i < n; i += SUB) {
-                    const StripRec r = strips[(long long)0 * MC + i];
-                    if (o + i < sp.out_cap) {
-                        opal_migrant m;
-                        m.cell = -1; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
-                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
-                        out_l[o + i] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
-                }
-            }
-        }
-        if (c == nc - 1) {
-            const int n = scount[2 * c + 1];
-            if (lane == 0 && n) atomicAdd(&st->gone[1], n);
-            if (sp.route_right == 2 && n) {
-                int o = 0;
-                if (lane == 0) o = atomicAdd(&st->n_out[1], n);
-                o = __shfl_sync(gmask, o, 0, SUB);
-                for (int i = lane; i < n; i += SUB) {
-                    const StripRec r = strips[((long long)c * 2 + 1) * MC + i];
-                    if (o + i < sp.out_cap) {
-                        opal_migrant m;
-                        m.cell = 0; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
-                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
-                        out_r[o + i] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_OUTBOX);
-                }
-            }
-        }
-        const int n_in = n_from_l + n_from_r;
-#if OPAL_PUSH_HOLES == 1
-        const int n_holes = hcount[c];         // listed by the push: slots of this bucket that are free
-        if (n_in == 0) continue;
-#else
-        const int n_holes = 0;
-        (void)n_holes;
-        if (n_in == 0) continue;
-#endif
-        const int cnt = b.count[c];
-        const long long bstart = b.start[c];
-        const int cap = (int)(b.start[c + 1] - bstart);
-        const int idx = c + g.left;
-        double acc[15];
-#pragma unroll
-        for (int k = 0; k < 15; k++) acc[k] = 0.0;
-        for (int i0 = 0; i0 < n_in; i0 += SUB) {
-            const int i = i0 + lane;
-            if (i < n_in) {
-                const StripRec r = i < n_from_l ? strips[((long long)src_l * 2 + 1) * MC + i]
-                                                : strips[((long long)src_r * 2) * MC + (i - n_from_l)];
-#if OPAL_PUSH_HOLES == 1
-                // the first n_holes arrivals drop into the listed holes, the rest are appended behind the slots in use
-                const int slot = i < n_holes ? holes[(long long)c * (2 * MC) + i] : cnt + (i - n_holes);
-#else
-                const int slot = cnt + i;
-#endif
-                if (slot < cap) {
-                    const long long s = bstart + slot;
-                    b.f[F_X][s] = r.x; b.f[F_UX][s] = r.ux; b.f[F_UY][s] = r.uy; b.f[F_UZ][s] = r.uz; b.f[F_W][s] = r.w;
-                } else {
-                    // bucket full: park; the host re-lays the buckets out (count[c] keeps the demand)
-                    int o = atomicAdd(&st->n_overflow, 1);
-                    if (o < sp.overflow_cap) {
-                        opal_migrant m;
-                        m.cell = c; m.x = r.x; m.prev_x = r.prev_x; m.u[0] = r.ux; m.u[1] = r.uy; m.u[2] = r.uz; m.weight = r.w; m.gamma = sqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0))));
-                        m.chi = 0.0; m.tau = 0.0; m.work = 0.0; m.y = 0.0; m.z = 0.0; m.birth_time = 0.0; m.pad[0] = 0.0; m.pad[1] = 0.0;
-                        overflow[o] = m;
-                    } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PARKED);
-                }
-                if (slot < cap) {
-                    // R-face form of the mover's deposit in the frame of its new cell c (faces -3/2..+5/2):
-                    // new position: R = (1, a, b, c, 0); old position one cell to the left: (a_o, b_o, c_o, 0, 0),
-                    // one cell to the right: (1, 1, a_o, b_o, c_o);  flux = R_new - R_old  (== Cell::flux, yee.rs:185)
-                    const bool from_l = i < n_from_l;
-                    const RFaces rn = r_faces(r.x);
-                    const RFaces ro = r_faces(from_l ? r.prev_x + 1.0 : r.prev_x - 1.0);
-                    const double f0 = from_l ? 1.0 - ro.a : 0.0;
-                    const double f1 = rn.a - (from_l ? ro.b : 1.0);
-                    const double f2 = rn.b - (from_l ? ro.c : ro.a);
-                    const double f3 = rn.c - (from_l ? 0.0 : ro.b);
-                    const double f4 = from_l ? 0.0 : -ro.c;
-                    acc[0] += r.w * f0; acc[1] += r.w * f1; acc[2] += r.w * f2; acc[3] += r.w * f3; acc[4] += r.w * f4;
-                    const double w0 = 1.0 - rn.a, w1 = rn.a - rn.b, w2 = rn.b - rn.c, w3 = rn.c;
-                    const double tw = r.w * rsqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0)))), ty = tw * r.uy, tz = tw * r.uz;
-                    acc[5] += ty * w0; acc[6] += ty * w1; acc[7] += ty * w2;
-                    acc[8] += tz * w0; acc[9] += tz * w1; acc[10] += tz * w2;
-                    acc[11] += r.w * w3; acc[12] += r.w * w0; acc[13] += r.w * w1; acc[14] += r.w * w2;
-                }
-            }
-        }
-#if OPAL_PUSH_HOLES == 1
-        if (lane == 0) {
-            if (n_in > n_holes) b.count[c] = cnt + (n_in - n_holes);
-            hcount[c] = n_in < n_holes ? n_holes - n_in : 0;       // holes still open (k_compact_cells skips cells without)
-        }
-#else
-        if (lane == 0) b.count[c] = cnt + n_in;
-#endif
-        const double qsp = sp.species == OPAL_ION ? b.z_star * OPAL_E : OPAL_QE;
-        const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
-#pragma unroll
-        for (int k = 0; k < 15; k++) acc[k] = group_sum<SUB>(acc[k], gmask) * (k < 5 ? kx : (k < 11 ? ky : kr));
-#pragma unroll
-        for (int k = 0; k < 15; k++) {
-            if (lane == (k % SUB) && acc[k] != 0.0) {
-                double* const dst = k < 5 ? g.jx + idx - 2 + k : (k < 8 ? g.jy + idx - 1 + (k - 5) : (k < 11 ? g.jz + idx - 1 + (k - 8) : g.rho + idx - 2 + (k - 11)));
-                atomicAdd(dst, acc[k]);
-            }
-        }
-    }
-}
+#include "opal_push_lean.cuh"
+#include "opal_push_full.cuh"
 #endif  // OPAL_FAST
 
 // ============================================================================================
@@ -968,7 +270,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
                 b.f[F_PREVX][s] = m.prev_x; b.f[F_GAMMA][s] = SP == OPAL_ION ? m.pad[0] : m.gamma; b.f[F_CHI][s] = m.chi;
                 b.f[F_TAU][s] = m.tau; b.f[F_WORK][s] = m.work; b.f[F_Y][s] = m.y; b.f[F_Z][s] = m.z;
             }
-            if (DEP) {
+            if (DEP && m.pad[1] == 0.0) {       // pad[1] == 1: the lean push that handed this record over deposited it already
                 const double Q = m.weight * q;
                 const double vy = OPAL_C * m.u[1] / m.gamma, vz = OPAL_C * m.u[2] / m.gamma;
                 deposit_atomic(g, c + g.left, Q, m.prev_x, m.x, vy, vz);
@@ -1817,16 +1119,21 @@ static inline int cell_grid(int ncell) {
 }
 
 static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, bool full, bool dep,
-                   opal_migrant* movers, StripRec* strips, int* scount, StatusDev* st, double* ke_out) {
+                   opal_migrant* movers, const LeanStrips* ls, opal_migrant* out_l, opal_migrant* out_r, opal_migrant* overflow,
+                   StatusDev* st, double* ke_out) {
     // the per-segment counters live directly behind the StatusDev block (see host: status + seg counters)
     int* seg = reinterpret_cast<int*>(st + 1);
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
-    if ((sp.species == OPAL_ELECTRON || sp.species == OPAL_ION) && !full && dep && strips && sp.cell_mover_cap > 0) {
+    if ((sp.species == OPAL_ELECTRON || sp.species == OPAL_ION) && !full && dep && ls && sp.cell_mover_cap > 0) {
         long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
         const int gr = (int)(blocks < 1 ? 1 : blocks);
-#define LAUNCHF(B0, K) k_push_lean_fast<B0, K, OPAL_ELECTRON><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, ke_out, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
-#define LAUNCHI(B0) k_push_lean_fast<B0, false, OPAL_ION><<<gr, OPAL_PUSH_WPB * 32, 0, s>>>(g, b, sp, movers, seg, strips, scount, st, nullptr, scount + 3ll * b.ncell, scount + 2ll * b.ncell)
+        const int smem = OPAL_PUSH_WPB * (int)sizeof(PushScratch);
+        // (the attribute is per device and contexts may live on several devices: set on every launch, a cheap host-side call)
+#define LAUNCHF(B0, K) do { cudaFuncSetAttribute(k_push_lean_fast<B0, K, OPAL_ELECTRON>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+        k_push_lean_fast<B0, K, OPAL_ELECTRON><<<gr, OPAL_PUSH_WPB * 32, smem, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, ke_out); } while (0)
+#define LAUNCHI(B0) do { cudaFuncSetAttribute(k_push_lean_fast<B0, false, OPAL_ION>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+        k_push_lean_fast<B0, false, OPAL_ION><<<gr, OPAL_PUSH_WPB * 32, smem, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, nullptr); } while (0)
         if (sp.species == OPAL_ION) { if (sp.flags & OPAL_STEP_BX_ZERO) LAUNCHI(true); else LAUNCHI(false); }
         else if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
         else { if (ke_out) LAUNCHF(false, true); else LAUNCHF(false, false); }
@@ -1834,7 +1141,20 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
 #undef LAUNCHI
         return true;
     }
+    if (sp.species == OPAL_ELECTRON && full) {
+        // the reference's whole per-particle state in the reciprocal arithmetic (opal_push_full.cuh)
+        long long blocks = ((long long)b.ncell + OPAL_FULL_WPB - 1) / OPAL_FULL_WPB;
+        const int gr = (int)(blocks < 1 ? 1 : blocks);
+        const int smem = OPAL_FULL_WPB * (int)sizeof(FullScratch);
+#define LAUNCHQ(B0, D) do { cudaFuncSetAttribute(k_push_full_fast<B0, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+        k_push_full_fast<B0, D><<<gr, OPAL_FULL_WPB * 32, smem, s>>>(g, b, sp, movers, seg, st); } while (0)
+        if (sp.flags & OPAL_STEP_BX_ZERO) { if (dep) LAUNCHQ(true, true); else LAUNCHQ(true, false); }
+        else { if (dep) LAUNCHQ(false, true); else LAUNCHQ(false, false); }
+#undef LAUNCHQ
+        return false;
+    }
 #endif
+    (void)ls; (void)out_l; (void)out_r; (void)overflow; (void)ke_out;
 #define LAUNCH(SP, F, D) k_push<SP, F, D><<<grid, BLOCK, 0, s>>>(g, b, sp, movers, seg, st)
     if (sp.species == OPAL_ELECTRON) {
         if (full) { if (dep) LAUNCH(OPAL_ELECTRON, true, true); else LAUNCH(OPAL_ELECTRON, true, false); }
@@ -1847,22 +1167,21 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     return false;
 }
 
-static void l_pull(cudaStream_t s, const GridDev& g, const BucketDev& b, const StepParams& sp, const StripRec* strips,
-                   const int* scount, opal_migrant* out_l, opal_migrant* out_r, opal_migrant* overflow, StatusDev* st) {
+// append the arrivals waiting in the strips to their buckets (lean layout; see opal_push_lean.cuh)
+static void l_flush(cudaStream_t s, const BucketDev& b, const StepParams& sp, const StripRec* strips, const int* scount,
+                    opal_migrant* overflow, StatusDev* st) {
 #ifdef OPAL_FAST
-    long long blocks = ((long long)b.ncell + 8 * (32 / OPAL_PULL_SUB) - 1) / (8 * (32 / OPAL_PULL_SUB));
-    // the strip counters are followed by the per-cell hole counts and hole lists (host: ensure_cell_movers)
-    int* sc = const_cast<int*>(scount);
-    k_pull<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(g, b, sp, strips, scount, out_l, out_r, overflow, st, sc + 3ll * b.ncell, sc + 2ll * b.ncell);
+    long long blocks = ((long long)b.ncell + 15) / 16;
+    k_strip_flush<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(b, sp, strips, scount, overflow, st);
 #endif
 }
 
-// close the holes the lean step kernels leave in the buckets (count[] := live particles)
-static void l_compact_cells(cudaStream_t s, const BucketDev& b, const int* scount) {
+// close the free slots the lean push leaves in the buckets (count[] := live particles)
+static void l_compact_cells(cudaStream_t s, const BucketDev& b, int* hcount) {
 #ifdef OPAL_FAST
     long long blocks = ((long long)b.ncell + 7) / 8;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_compact_cells<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(b, scount + 2ll * b.ncell);
+    k_compact_cells<<<(int)(blocks < 1 ? 1 : blocks), 256, 0, s>>>(b, hcount);
 #endif
 }
 
@@ -2009,15 +1328,10 @@ static void l_crossing_estimate(cudaStream_t s, const BucketDev& b, double dt_ov
 KernelTable table() {
     KernelTable t;
     t.crossing_estimate = l_crossing_estimate;
-    t.push = l_push; t.pull = l_pull; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
+    t.push = l_push; t.flush = l_flush; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
     t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
-#if defined(OPAL_FAST) && OPAL_PUSH_HOLES == 1
-    t.push_leaves_holes = true;
-#else
-    t.push_leaves_holes = false;
-#endif
     return t;
 }
 

@@ -72,9 +72,18 @@ enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
        ERR_CAP_MOVERS = 16u, ERR_CAP_PARKED = 32u, ERR_CAP_OUTBOX = 64u, ERR_CAP_PHOTONS = 128u,
        ERR_PROB = 256u };     // assert!(partial_prob >= 0.0) (photon.rs:325)
 
-// compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout);
-// the destination (c-1 / c+1) is implied by the strip it sits in
-struct StripRec { double x, prev_x, ux, uy, uz, w; };   // 48 bytes (gamma is recomputed from u where a consumer needs it)
+// compact record of one cell-crossing particle in a per-cell, per-direction mover strip (lean layout); the destination
+// (c-1 / c+1) is implied by the strip it sits in.  x: offset in the destination cell; prev_x: offset it had in the cell it left
+// (the writing warp deposits its movers from the strip at the end of the cell, all lanes busy; the next step's push ignores it).
+struct __align__(16) StripRec { double x, prev_x, ux, uy, uz, w; };   // 48 bytes
+
+// the strips of one lean species as one push sees them (double-buffered by step parity): it reads the movers its neighbour
+// cells left in `in` during the previous step and writes its own movers to `out`
+struct LeanStrips {
+    const StripRec* in; const int* scount_in;    // [2 * ncell * MC] records, [2 * ncell] counts: cell c's left strip is 2c, its right strip 2c + 1
+    StripRec* out; int* scount_out;
+    int* hcount;                                 // [ncell] free slots inside count[c]
+};
 
 // internal StepParams.flags bit (above the public OPAL_FLAG_* bits): B_x is zero on the whole grid
 #define OPAL_STEP_BX_ZERO (1u << 31)
@@ -90,14 +99,14 @@ struct StepParams {
 
 // one set of kernel launchers; two instances exist (fast: FMA contraction on, strict: off)
 struct KernelTable {
-    // returns true when the kernel used the per-cell mover strips (then scatter_cells must follow)
+    // returns true when the lean strip kernel ran (`ls` given, lean layout, fused deposit, fast build): the movers then
+    // wait in ls->out for the NEXT push (or for flush), and the buckets carry free slots (ls->hcount)
     bool (*push)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool fused_deposit,
-                 opal_migrant* movers, StripRec* strips, int* strip_count, StatusDev* st,
-                 double* ke_out /* null, or accumulator for the pushed particles' kinetic energy (strip kernel only) */);
-    // pull the strips' movers into their destination buckets (+ their deposit); inbox_*: strips received from the
-    // left / right neighbour slab (remote case), may be null
-    void (*pull)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, const StripRec* strips,
-                 const int* strip_count, opal_migrant* outbox_l, opal_migrant* outbox_r, opal_migrant* overflow, StatusDev* st);
+                 opal_migrant* movers, const LeanStrips* ls, opal_migrant* outbox_l, opal_migrant* outbox_r, opal_migrant* overflow,
+                 StatusDev* st, double* ke_out /* null, or accumulator for the pushed particles' kinetic energy (strip kernel only) */);
+    // append the movers waiting in `strips` to their destination buckets (no deposit: the push did it)
+    void (*flush)(cudaStream_t, const BucketDev&, const StepParams&, const StripRec* strips, const int* strip_count,
+                  opal_migrant* overflow, StatusDev* st);
     void (*scatter)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, bool full, bool deposit,
                     const opal_migrant* recs, const int* n_recs, int n_max, long long cell_shift, const int* idx_list,
                     opal_migrant* outbox_l, opal_migrant* outbox_r, int* overflow_idx, StatusDev* st);
@@ -128,9 +137,8 @@ struct KernelTable {
     // sizing of the mover buffer: out2[0] += particles whose ballistic step x + v_x dt/dx leaves [0,1),
     // out2[1] += sum of min(1, |v_x| dt/dx) (the same count for positions uniform inside their cells)
     void (*crossing_estimate)(cudaStream_t, const BucketDev&, double dt_over_dx, double* out2);
-    // lean electrons: close the holes the fused step kernels leave (strip_count: the push's counter block)
-    void (*compact_cells)(cudaStream_t, const BucketDev&, const int* strip_count);
-    bool push_leaves_holes;     // the lean strip kernel was built with OPAL_PUSH_HOLES
+    // lean layout: close the free slots the strip kernel leaves inside the buckets
+    void (*compact_cells)(cudaStream_t, const BucketDev&, int* hcount);
     // burst mode bookkeeping kernels: 0 begin (zero the per-advance counters), 1 check (raise halt on overflow / error), 2 end (step++)
     void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species);
 };
