@@ -512,6 +512,15 @@ __global__ void k_outbox_headers(opal_migrant* out_l, opal_migrant* out_r, const
     if (threadIdx.x == 0) { out_l[0].cell = st->n_out[0]; out_r[0].cell = st->n_out[1]; }
 }
 __global__ void k_header_to_int(const opal_migrant* in, int* n) { if (threadIdx.x == 0) *n = (int)in[0].cell; }
+// burst mode: empty the destination of the photon ping-pong -- unless the burst has halted (a memset node would wipe the live store)
+__global__ void k_burst_zero_int(const StatusDev* st, int* p) {
+    if (threadIdx.x == 0 && !*(volatile const int*)&st->halt) *p = 0;
+}
+// burst mode: before k_emit, is there room for one photon per electron (electron.rs:208-251)?  If not: halt, the host grows the store
+__global__ void k_burst_photon_room(StatusDev* st, const int* ph_n, int cap, long long need, int phase) {
+    if (threadIdx.x != 0 || *(volatile int*)&st->halt) return;
+    if ((long long)*ph_n + need > (long long)cap) { st->halt_species = phase; __threadfence(); st->halt = 1; }
+}
 // live particles of a species: sum of count[] (out must be zeroed)
 __global__ void __launch_bounds__(256) k_total_count(const int* __restrict__ count, int ncell, unsigned long long* out) {
     unsigned long long acc = 0;
@@ -727,7 +736,15 @@ void swap_fields(opal_ctx* c) {
     for (int k = 0; k < 6; k++) std::swap(*cur[k], c->eb_alt[k]);
 }
 
-void enqueue_species(opal_ctx* c, int sp) {     // advance_charged without the host in the loop (fused deposit, local slab)
+// what one iteration of main.rs:238-267 consists of; the phases run in this order
+struct StepCfg {
+    bool dep = true, emit = false;
+    bool fused() const { return dep && !emit; }        // deposit inside the push (absorption, which also forbids it, never runs in a burst)
+    double f3[3] = {0.0, 0.0, 0.0};                    // emit filters (NaN == None)
+};
+enum { PH_ELECTRONS = 0, PH_IONS = 1, PH_PHOTONS = 2, PH_ABSORB = 3, PH_EMIT_ROOM = 4, PH_EMIT = 5, PH_DEPOSIT = 6, PH_GRID = 7 };
+
+void enqueue_species(opal_ctx* c, int sp, bool fused) {     // advance_charged without the host in the loop (local slab)
     Buckets& B = c->bk[sp];
     if (!B.allocated) return;
     c->adv_calls[sp]++;
@@ -735,40 +752,57 @@ void enqueue_species(opal_ctx* c, int sp) {     // advance_charged without the h
     c->k.burst_mark(c->stream, c->d_status, 0, sp);
     opal_ctx::Lean& L = c->lean[sp];
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
-    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                                   c->d_overflow, c->d_status, nullptr);
     if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
-    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, true, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status);
     c->k.burst_mark(c->stream, c->d_status, 1, sp);
 }
 
-int enqueue_step(opal_ctx* c) {                 // main.rs:238-267 with deposition on, emission off; returns the launch count
-    const long long l0 = c->launches;
-    c->k.clear(c->stream, c->g);
-    enqueue_species(c, OPAL_ELECTRON);
-    enqueue_species(c, OPAL_ION);
+int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // one iteration of main.rs:238-267; returns the launch count
+    int n = 0;
+    if (cfg.dep) { c->k.clear(c->stream, c->g); n++; }
+    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { enqueue_species(c, sp, cfg.fused()); n += 4; }
+    if (c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) {
+        const int src = c->ph_cur, dst = 1 - src;
+        k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n);
+        c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status);
+        c->k.burst_mark(c->stream, c->d_status, 1, PH_PHOTONS);
+        c->ph_cur = dst;
+        n += 3;
+    }
+    if (cfg.emit && c->bk[OPAL_ELECTRON].allocated) {
+        k_burst_photon_room<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[c->ph_cur].d_n, c->ph[c->ph_cur].cap, c->bk[OPAL_ELECTRON].n_hint, PH_EMIT_ROOM);
+        // t and the call index of step k come from the device-side step counter (GridDev::step / laser_arr[3k + 2])
+        c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, 0.0, cfg.f3[0], cfg.f3[1], cfg.f3[2],
+                  c->seed, emit_call0, c->d_status);
+        c->k.burst_mark(c->stream, c->d_status, 1, PH_EMIT);
+        n += 3;
+    }
+    if (cfg.dep && !cfg.fused()) {
+        for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { c->k.deposit(c->stream, c->g, bdev(c, sp), sparams(c, sp), c->d_status); n++; }
+    }
     c->k.sync_bc(c->stream, c->g, nullptr, 0.0, 0.0, nullptr);
     do_field(c);
+    c->launches--;                               // (do_field counted itself; the burst accounts launches per replay)
     c->k.burst_mark(c->stream, c->d_status, 2, 0);
-    int n = 4;                                   // clear, sync_bc, field, end mark
-    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) n += 4;      // begin mark, push, scatter, check mark
-    (void)l0;
-    return n;
+    return n + 3;
 }
 
 // Runs up to n (even) steps from laser_y/z[0..n) as graph replays.  *done = steps completed; *halted tells whether the
 // step after them stopped half-way (c->h_status then holds the counters and halt_species of that moment).
-bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64_t* done, bool* halted) {
+bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const double* ly, const double* lz, int64_t* done, bool* halted) {
     *done = 0; *halted = false;
-    if (c->laser_cap < 2 * n) {
+    if (c->laser_cap < 3 * n) {
         if (c->d_laser) cudaFree(c->d_laser);
         c->d_laser = nullptr; c->laser_cap = 0;
-        CUB(cudaMalloc(&c->d_laser, (size_t)(2 * n) * sizeof(double)));
-        c->laser_cap = 2 * n;
+        CUB(cudaMalloc(&c->d_laser, (size_t)(3 * n) * sizeof(double)));
+        c->laser_cap = 3 * n;
     }
-    std::vector<double> lh((size_t)(2 * n), 0.0);
-    for (int64_t k = 0; k < n; k++) { lh[2 * k] = ly ? ly[k] : 0.0; lh[2 * k + 1] = lz ? lz[k] : 0.0; }
+    // per step: the two laser amplitudes and the time, accumulated as main.rs:266 does (t += dt)
+    std::vector<double> lh((size_t)(3 * n), 0.0);
+    { double t = t0; for (int64_t k = 0; k < n; k++) { lh[3 * k] = ly ? ly[k] : 0.0; lh[3 * k + 1] = lz ? lz[k] : 0.0; lh[3 * k + 2] = t; t += c->g.dt; } }
     CUB(cudaMemcpyAsync(c->d_laser, lh.data(), lh.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CUB(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
     CUB(cudaStreamSynchronize(c->stream));
@@ -778,10 +812,12 @@ bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64
     cudaGraphExec_t exec = nullptr;
     int per_step = 0;
     const int parity0[2] = {c->lean[0].parity, c->lean[1].parity};     // two captured steps leave the strip parity where it was
+    const int ph_cur0 = c->ph_cur;                                     // ... and the photon ping-pong
+    const uint64_t emit_call0 = c->emit_calls;
     cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
     if (e == cudaSuccess) {
-        per_step = enqueue_step(c);
-        enqueue_step(c);                         // the second half of the ping-pong: c->g is back where it started
+        per_step = enqueue_step(c, cfg, emit_call0);
+        enqueue_step(c, cfg, emit_call0);        // the second half of the ping-pong: c->g is back where it started
         e = cudaStreamEndCapture(c->stream, &graph);
     }
     if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
@@ -806,11 +842,14 @@ bool run_burst(opal_ctx* c, int64_t n, const double* ly, const double* lz, int64
     leave();
     c->burst_steps += *done;
     if (ok && (*done & 1)) swap_fields(c);       // an odd number of steps ran: the fields sit in the other buffer set
+    const int hphase = *halted ? c->h_status->halt_species : -1;   // the phase of the half-finished step that raised the halt
     for (int sp = 0; sp < 2; sp++) {
-        // pushes of this species that ran: one per completed step, plus the half-finished step up to the halting species
-        const int64_t pushes = *done + ((*halted && c->bk[sp].allocated && sp <= c->h_status->halt_species) ? 1 : 0);
+        // pushes of this species that ran: one per completed step, plus the half-finished step up to the halting phase
+        const int64_t pushes = *done + ((*halted && c->bk[sp].allocated && sp <= hphase) ? 1 : 0);
         if (c->lean[sp].d_hcount && c->bk[sp].allocated) c->lean[sp].parity = parity0[sp] ^ (int)(pushes & 1);
     }
+    if (c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) c->ph_cur = ph_cur0 ^ (int)((*done + (hphase >= PH_PHOTONS ? 1 : 0)) & 1);
+    if (cfg.emit) c->emit_calls = emit_call0 + (uint64_t)*done + (hphase >= PH_EMIT ? 1 : 0);
     return ok;
 }
 
@@ -1329,6 +1368,26 @@ opal_status opal_field_advance(opal_ctx* c) {
     return OPAL_OK;
 }
 
+// One iteration of main.rs:238-267 the ordinary way (status read back after every advance), from phase `from` on: the
+// whole step for from == PH_ELECTRONS; the rest of a step a graph-replayed burst left half-finished otherwise.
+static bool run_phases(opal_ctx* c, const StepCfg& cfg, int from, double t, double ly, double lz, bool want_ke) {
+    const bool fused = cfg.fused() && !c->absorb_on;
+    if (from <= PH_ELECTRONS) {
+        if (cfg.dep) { c->k.clear(c->stream, c->g); c->launches++; }
+        if (!advance_charged(c, OPAL_ELECTRON, fused, true, want_ke)) return false;
+    }
+    if (from <= PH_IONS && !advance_charged(c, OPAL_ION, fused, true)) return false;
+    if (from <= PH_PHOTONS && !advance_photons(c, c->ph[0].cap > 0)) return false;
+    if (from <= PH_ABSORB && c->absorb_on && !do_absorb(c, t, c->absorb_max_displacement, c->absorb_stop_time)) return false;      // main.rs:246-248
+    if (from <= PH_EMIT && cfg.emit && !do_emit(c, t, cfg.f3[0], cfg.f3[1], cfg.f3[2])) return false;
+    if (from <= PH_DEPOSIT && cfg.dep && !fused) {
+        for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { c->k.deposit(c->stream, c->g, bdev(c, sp), sparams(c, sp), c->d_status); c->launches++; }
+    }
+    if (!do_sync(c, ly, lz)) return false;
+    do_field(c);
+    return true;
+}
+
 opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double* laser_y, const double* laser_z,
                            int current_deposition, int photon_emission, const double* f3) {
     CHECK_CTX(c);
@@ -1336,50 +1395,53 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     if (!c->full && (photon_emission || c->absorb_on || !current_deposition))
         return (opal_status)(fail(c, OPAL_EINVAL, "lean-state context supports only the fused push+deposit step (deposition on, emission and absorption off)"), c->status);
     const double nan = std::numeric_limits<double>::quiet_NaN();
-    const bool fused = current_deposition && !photon_emission && !c->absorb_on;
+    StepCfg cfg;
+    cfg.dep = current_deposition != 0; cfg.emit = photon_emission != 0;
+    for (int k = 0; k < 3; k++) cfg.f3[k] = f3 ? f3[k] : nan;
+    if (cfg.emit && c->bk[OPAL_ELECTRON].allocated && !c->bk[OPAL_ELECTRON].full)
+        return (opal_status)(fail(c, OPAL_EINVAL, "emit_radiation needs the full particle state (context created with OPAL_FLAG_LEAN_STATE)"), c->status);
     double t = t0;
     c->ke_fused = false;
     int64_t s0 = 0;
     // room for the cell-crossing particles of a freshly loaded population (before any graph capture: it reads back a count)
     if (!size_movers_for(c, OPAL_ELECTRON) || !size_movers_for(c, OPAL_ION)) return (opal_status)c->status;
-    // launch-bound decks: replay the fused step as a CUDA graph (all but the last one or two steps, which also sum the
-    // kinetic energy and report the leaver counts)
-    const bool burst_ok = fused && !remote(c) && !c->timing && c->ph[0].cap == 0 && env_ll("OPAL_BURST", 1) != 0 &&
+    // Launch- and sync-bound decks: replay the step as a CUDA graph (all but the last one or two steps, which also sum the
+    // kinetic energy and report the leaver counts).  Everything a single slab does in a step is covered -- fused or separate
+    // deposit, photons, emission; absorption, remote neighbours and per-kernel timing take the ordinary path.
+    const bool burst_ok = !remote(c) && !c->timing && !c->absorb_on && env_ll("OPAL_BURST", 1) != 0 &&
                           (long long)c->bk[0].n_hint + c->bk[1].n_hint <= env_ll("OPAL_BURST_MAX_PARTICLES", 20000000);
     while (burst_ok && nsteps - s0 >= 6 && c->status == OPAL_OK) {
+        if (cfg.emit && c->bk[OPAL_ELECTRON].allocated) {
+            // room for a few steps' worth of photons up front (every electron can emit one per step; a few per cent do)
+            int nph = 0;
+            if (!photon_count(c, &nph)) break;
+            if (!ensure_photons(c, (long long)nph + 2 * c->bk[OPAL_ELECTRON].n_hint)) break;
+        }
         const int64_t n = ((nsteps - s0 - 1) / 2) * 2;
         int64_t done = 0;
         bool halted = false;
-        if (!run_burst(c, n, laser_y ? laser_y + s0 : nullptr, laser_z ? laser_z + s0 : nullptr, &done, &halted)) break;
+        if (!run_burst(c, cfg, n, t, laser_y ? laser_y + s0 : nullptr, laser_z ? laser_z + s0 : nullptr, &done, &halted)) break;
         s0 += done;
-        t += (double)done * c->g.dt;
+        for (int64_t k = 0; k < done; k++) t += c->g.dt;             // main.rs:266
         if (!halted) break;
         // step s0 stopped half-way: finish it the ordinary way, then resume
         const unsigned err = c->h_status->err;
-        const int hsp = c->h_status->halt_species;
+        const int hphase = c->h_status->halt_species;
         if (err) { fetch_status(c); break; }                      // an assert: sticky status, as in the ordinary path
-        c->last_gone[hsp][0] = c->h_status->gone[0]; c->last_gone[hsp][1] = c->h_status->gone[1];
-        if (!handle_overflow(c, hsp, true)) break;
-        if (hsp == OPAL_ELECTRON && !advance_charged(c, OPAL_ION, fused, true)) break;
-        if (!do_sync(c, laser_y ? laser_y[s0] : 0.0, laser_z ? laser_z[s0] : 0.0)) break;
-        do_field(c);
+        int resume = hphase + 1;
+        if (hphase == PH_ELECTRONS || hphase == PH_IONS) {        // a bucket overflowed: re-lay out, re-insert the parked movers
+            c->last_gone[hphase][0] = c->h_status->gone[0]; c->last_gone[hphase][1] = c->h_status->gone[1];
+            if (!handle_overflow(c, hphase, cfg.fused())) break;
+        } else if (hphase == PH_EMIT_ROOM) {                      // the photon store is full: do_emit (the next phase) grows it
+            resume = PH_EMIT;
+        }
+        if (!run_phases(c, cfg, resume, t, laser_y ? laser_y[s0] : 0.0, laser_z ? laser_z[s0] : 0.0, false)) break;
         s0++;
         t += c->g.dt;
     }
     for (int64_t s = s0; s < nsteps && c->status == OPAL_OK; s++) {   // main.rs:238-267
-        if (current_deposition) { c->k.clear(c->stream, c->g); c->launches++; }
         // the last step of the call also sums the electrons' kinetic energy (lean strip kernel): opal_energy then needs no particle pass
-        if (!advance_charged(c, OPAL_ELECTRON, fused, true, s == nsteps - 1 && !photon_emission && !c->absorb_on)) break;
-        if (!advance_charged(c, OPAL_ION, fused, true)) break;
-        if (!advance_photons(c, c->ph[0].cap > 0)) break;
-        if (c->absorb_on && !do_absorb(c, t, c->absorb_max_displacement, c->absorb_stop_time)) break;      // main.rs:246-248
-        if (photon_emission) { if (!do_emit(c, t, f3 ? f3[0] : nan, f3 ? f3[1] : nan, f3 ? f3[2] : nan)) break; }
-        if (current_deposition && !fused) {
-            if (c->bk[0].allocated) { c->k.deposit(c->stream, c->g, bdev(c, 0), sparams(c, 0), c->d_status); c->launches++; }
-            if (c->bk[1].allocated) { c->k.deposit(c->stream, c->g, bdev(c, 1), sparams(c, 1), c->d_status); c->launches++; }
-        }
-        if (!do_sync(c, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0)) break;
-        do_field(c);
+        if (!run_phases(c, cfg, PH_ELECTRONS, t, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0, s == nsteps - 1 && !cfg.emit && !c->absorb_on)) break;
         t += c->g.dt;
     }
     if (c->status == OPAL_OK) {

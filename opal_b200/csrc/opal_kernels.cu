@@ -285,6 +285,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
 // ============================================================================================
 template <int SP>
 __global__ void __launch_bounds__(BLOCK) k_deposit(GridDev g, BucketDev b) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     const int lane = threadIdx.x & 31;
     const int warps_total = gridDim.x * WARPS_PER_BLOCK;
     const double q = species_charge(SP, b.z_star);
@@ -329,6 +330,7 @@ __global__ void __launch_bounds__(BLOCK) k_deposit(GridDev g, BucketDev b) {
 __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, PhotonDev dst, StepParams sp,
                                                       opal_migrant* __restrict__ out_l, opal_migrant* __restrict__ out_r,
                                                       StatusDev* __restrict__ st) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     const int n = *src.n;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -706,6 +708,12 @@ constexpr int EMIT_QCAP = OPAL_EMIT_QCAP;
 __global__ void __launch_bounds__(BLOCK, OPAL_EMIT_MB) k_emit(GridDev g, BucketDev b, PhotonDev ph, StepParams sp, const double* __restrict__ tables_g,
                                                     double t, double min_energy, double max_angle, double max_fl,
                                                     uint64_t seed, uint64_t call_index, StatusDev* __restrict__ st) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (g.step) {                                         // burst mode: step k of the burst -> its time and its random-number call index
+        const int k = *(volatile const int*)g.step;
+        t = g.laser_arr[3 * k + 2];
+        call_index += (uint64_t)k;
+    }
     extern __shared__ double s_tab[];
     long long* s_qs = reinterpret_cast<long long*>(s_tab + QED_TABLE_DOUBLES);
     int* s_qc = reinterpret_cast<int*>(s_qs + EMIT_QCAP);
@@ -825,7 +833,7 @@ __global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __rest
     __syncthreads();
     if (g.left_bdy == OPAL_BDY_LASER && tid == 0) {       // yee.rs:456-462
         if (laser_dev) { laser_y = laser_dev[0]; laser_z = laser_dev[1]; }
-        if (g.laser_arr) { const int k = *(volatile const int*)g.step; laser_y = g.laser_arr[2 * k]; laser_z = g.laser_arr[2 * k + 1]; }
+        if (g.laser_arr) { const int k = *(volatile const int*)g.step; laser_y = g.laser_arr[3 * k]; laser_z = g.laser_arr[3 * k + 1]; }
         const int start = g.left - 2;
         const double r = OPAL_C * g.dt / g.dx;
         g.ey[start] += 2.0 * r * laser_y;

@@ -34,21 +34,27 @@
 #pragma once
 
 #ifndef OPAL_PUSH_STAGES
-#define OPAL_PUSH_STAGES 2             // ring stages in flight per warp ...
+#define OPAL_PUSH_STAGES 3             // ring stages in flight per warp ...
 #endif
 #ifndef OPAL_PUSH_SUP
-#define OPAL_PUSH_SUP 3                // ... of this many 32-particle chunks each: one bulk copy per stream moves 256 B x SUP
+#define OPAL_PUSH_SUP 2                // ... of this many 32-particle chunks each: one bulk copy per stream moves 256 B x SUP
 #endif
+// One warp per block and 18 blocks per SM: the compiler then fits the kernel into 96 registers without spilling (124 when
+// given 128), and 18 resident warps hide the FP64 dependency chains of the Vay push far better than 16 (measured: 17.0 ->
+// 16.2 ms per 1e9-particle step; 20-24 warps gain nothing more, the part then sits on its power cap).
 #ifndef OPAL_PUSH_WPB
-#define OPAL_PUSH_WPB 4
+#define OPAL_PUSH_WPB 1
 #endif
 #ifndef OPAL_PUSH_MINBLK
-#define OPAL_PUSH_MINBLK 4
+#define OPAL_PUSH_MINBLK 18
 #endif
 #ifndef OPAL_HOLE_MAX
 #define OPAL_HOLE_MAX 48               // free slots a bucket may carry between steps before the cell compacts itself
 #endif
-constexpr int PUSH_ARR = 32;           // arrivals per side staged in shared memory by one bulk copy (more: read from global)
+#ifndef OPAL_PUSH_ARR
+#define OPAL_PUSH_ARR 32
+#endif
+constexpr int PUSH_ARR = OPAL_PUSH_ARR; // arrivals per side staged in shared memory by one bulk copy (more: read from global)
 constexpr int PUSH_FREE_CAP = 64;      // free-slot indices remembered per cell and step (more free slots simply stay free)
 
 // A free slot inside a bucket carries x = -1 (valid offsets are in [0, 1)): FINITE, like everything else a lane can find in a
@@ -313,7 +319,8 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
         __syncwarp();
         if (lane < 18) {
             const int k = c_pre_k[lane];
-            const double coef = (k & 2 ? ac : alpha) * (k & 1 ? 0.5 : 1.0);
+            // the Vay push needs E only as u' = u + 2 alpha E + ...: its E coefficients carry the factor 2 (the Boris push adds alpha E twice)
+            const double coef = (k & 2 ? ac : (SP == OPAL_ELECTRON ? 2.0 * alpha : alpha)) * (k & 1 ? 0.5 : 1.0);
             reinterpret_cast<double*>(&S.pre)[lane] = coef * (S.raw[c_pre_ia[lane]] - S.raw[c_pre_ib[lane]]);
         }
         __syncwarp();
@@ -345,11 +352,11 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
             double gam;
             if (SP == OPAL_ELECTRON) {
                 // ---- Vay push (electron.rs:268-330) ----
-                // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma
+                // u_half = u + alpha (E + v x B) with v = c u / gamma  ==  u + alpha E + (u x tau) / gamma;  u' = u_half + alpha E
+                // (aE holds 2 alpha E here)
                 const double ig = fast_rsqrt(fma(u.x, u.x, fma(u.y, u.y, fma(u.z, u.z, 1.0))));
                 const V3 uxt = BX0 ? V3{u.y * tv.z - u.z * tv.y, -(u.x * tv.z), u.x * tv.y} : cross(u, tv);
-                const V3 ue = u + aE;
-                const V3 u_prime = {fma(ig, uxt.x, ue.x) + aE.x, fma(ig, uxt.y, ue.y) + aE.y, fma(ig, uxt.z, ue.z) + aE.z};
+                const V3 u_prime = {fma(ig, uxt.x, u.x + aE.x), fma(ig, uxt.y, u.y + aE.y), fma(ig, uxt.z, u.z + aE.z)};
                 const double gp2 = fma(u_prime.x, u_prime.x, fma(u_prime.y, u_prime.y, fma(u_prime.z, u_prime.z, 1.0)));
                 const double u_star = BX0 ? fma(u_prime.y, tv.y, u_prime.z * tv.z) : dot(u_prime, tv);
                 const double tau2 = BX0 ? fma(tv.y, tv.y, tv.z * tv.z) : dot(tv, tv);
@@ -399,8 +406,8 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
             const int route = left ? route_l : route_r;
             if (route == 1) {
                 if (r < MC) {
-                    const StripRec rec = {xn, x_old, u.x, u.y, u.z, W};
-                    strips_out[((long long)c * 2 + (left ? 0 : 1)) * MC + r] = rec;
+                    double2* const rec = reinterpret_cast<double2*>(strips_out + ((long long)c * 2 + (left ? 0 : 1)) * MC + r);   // 3 x 16-byte stores
+                    rec[0] = make_double2(xn, x_old); rec[1] = make_double2(u.x, u.y); rec[2] = make_double2(u.z, W);
                 } else {
                     // strip full (a cell far hotter or denser than the strips were sized for): the shared segmented buffer;
                     // k_scatter, right after this kernel, puts it into its bucket and deposits it
@@ -434,32 +441,12 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
         };
 
         // ================= the residents: in place =================
-        int stage = 0, sub = 0;
-        for (int k0 = 0; k0 < n; k0 += 32) {
-            if (sub == 0) {
-                mbar_wait(&S.bar[stage], (phase >> stage) & 1u);
-                phase ^= 1u << stage;
-                __syncwarp();                                  // every lane is done with the stage the next copy refills
-                if (elect_one()) {
-                    const int nxt = k0 / SUPN + NST - 1;
-                    if (nxt < n_sup) {
-                        const int ps = stage == 0 ? NST - 1 : stage - 1;      // consumed before this one
-                        const unsigned bytes = 256u * (unsigned)min(SUP, n_chunks - nxt * SUP);
-                        mbar_expect_tx(&S.bar[ps], 5 * bytes);
-                        const long long o = base + (long long)nxt * SUPN;
-                        bulk_g2s(S.ring[ps][0], fx + o, bytes, &S.bar[ps]); bulk_g2s(S.ring[ps][1], fux + o, bytes, &S.bar[ps]);
-                        bulk_g2s(S.ring[ps][2], fuy + o, bytes, &S.bar[ps]); bulk_g2s(S.ring[ps][3], fuz + o, bytes, &S.bar[ps]);
-                        bulk_g2s(S.ring[ps][4], fw + o, bytes, &S.bar[ps]);
-                    }
-                }
-            }
-            const int e = sub * 32 + lane;
+        auto resident_chunk = [&](int k0, const double (*R)[32 * SUP], int e) {
             const int i = k0 + lane;
-            const double x = S.ring[stage][0][e];
-            V3 u = {S.ring[stage][1][e], S.ring[stage][2][e], S.ring[stage][3][e]};
+            const double x = R[0][e];
+            V3 u = {R[1][e], R[2][e], R[3][e]};
             const bool live = i < n && !is_hole(x);
-            const double W = live ? S.ring[stage][4][e] : 0.0;
-            if (++sub == SUP) { sub = 0; stage = stage == NST - 1 ? 0 : stage + 1; }
+            const double W = live ? R[4][e] : 0.0;
             double xn, fl, igam, gam2;
             RFaces ro;
             push(x, u, W, live, xn, fl, igam, gam2, ro);
@@ -486,6 +473,29 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                 n_free += __popc(m_free);
                 mloc_l += __popc(m_l); mloc_r += __popc(m_r);
             }
+        };
+        int stage = 0;
+        for (int ks = 0; ks < n_sup; ks++) {                      // one ring stage = SUP chunks of 32
+            mbar_wait(&S.bar[stage], (phase >> stage) & 1u);
+            phase ^= 1u << stage;
+            __syncwarp();                                          // every lane is done with the stage the next copy refills
+            if (elect_one()) {
+                const int nxt = ks + NST - 1;
+                if (nxt < n_sup) {
+                    const int ps = stage == 0 ? NST - 1 : stage - 1;      // consumed before this one
+                    const unsigned bytes = 256u * (unsigned)min(SUP, n_chunks - nxt * SUP);
+                    mbar_expect_tx(&S.bar[ps], 5 * bytes);
+                    const long long o = base + (long long)nxt * SUPN;
+                    bulk_g2s(S.ring[ps][0], fx + o, bytes, &S.bar[ps]); bulk_g2s(S.ring[ps][1], fux + o, bytes, &S.bar[ps]);
+                    bulk_g2s(S.ring[ps][2], fuy + o, bytes, &S.bar[ps]); bulk_g2s(S.ring[ps][3], fuz + o, bytes, &S.bar[ps]);
+                    bulk_g2s(S.ring[ps][4], fw + o, bytes, &S.bar[ps]);
+                }
+            }
+            const int k_base = ks * SUPN;
+#pragma unroll
+            for (int sub = 0; sub < SUP; sub++)
+                if (sub == 0 || k_base + sub * 32 < n) resident_chunk(k_base + sub * 32, S.ring[stage], sub * 32 + lane);
+            stage = stage == NST - 1 ? 0 : stage + 1;
         }
 
         // ================= the arrivals: into the free slots, the rest behind the bucket =================
@@ -588,32 +598,30 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
             }
         }
 
-        // one shuffle reduction and <= 21 atomics per CELL; q/dt, q c/dx, q/dx applied here
-        const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
+        // ONE transposing reduction (31 shuffles of doubles: lane k ends up with the warp total of sum k) and <= 21 atomics
+        // per CELL; q/dt, q c/dx, q/dx applied here.
         // targets: 0-2 jx j-1..j+1 | 3-5 jy | 6-8 jz | 9-12 rho j-2..j+1 | 13-15 jx, jy, jz j-2 | 16 rho j-3 | 17-19 jx, jy, jz j+2 | 20 rho j+2
-        double v[21] = {sjx0, sjx1, sjx2, sjy0, sjy1, sjy2, sjz0, sjz1, sjz2, sr0, sr1, sr2, sr3, ejx_m, ejy_m, ejz_m, er_m, ejx_p, ejy_p, ejz_p, er_p};
+        double v[32] = {sjx0, sjx1, sjx2, sjy0, sjy1, sjy2, sjz0, sjz1, sjz2, sr0, sr1, sr2, sr3, ejx_m, ejy_m, ejz_m, er_m, ejx_p, ejy_p, ejz_p, er_p,
+                        0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-        for (int k = 0; k < 13; k++) v[k] = warp_sum(v[k]);
-        if (dep_l) {
+        for (int width = 16; width >= 1; width >>= 1) {
+            const bool upper = (lane & width) != 0;
 #pragma unroll
-            for (int k = 13; k < 17; k++) v[k] = warp_sum(v[k]);
-        }
-        if (dep_r) {
-#pragma unroll
-            for (int k = 17; k < 21; k++) v[k] = warp_sum(v[k]);
-        }
-        double mine = 0.0;
-        double* dst = nullptr;
-#pragma unroll
-        for (int k = 0; k < 21; k++) {
-            if (lane == k) {
-                mine = v[k] * (k < 3 || k == 13 || k == 17 ? kx : ((k >= 9 && k < 13) || k == 16 || k == 20 ? kr : ky));
-                dst = k < 3 ? g.jx + j - 1 + k : k < 6 ? g.jy + j - 1 + (k - 3) : k < 9 ? g.jz + j - 1 + (k - 6) : k < 13 ? g.rho + j - 2 + (k - 9)
-                    : k == 13 ? g.jx + j - 2 : k == 14 ? g.jy + j - 2 : k == 15 ? g.jz + j - 2 : k == 16 ? g.rho + j - 3
-                    : k == 17 ? g.jx + j + 2 : k == 18 ? g.jy + j + 2 : k == 19 ? g.jz + j + 2 : g.rho + j + 2;
+            for (int k = 0; k < width; k++) {
+                const double send = upper ? v[k] : v[k + width];
+                const double keep = upper ? v[k + width] : v[k];
+                v[k] = keep + __shfl_xor_sync(FULLMASK, send, width);
             }
         }
-        if (dst && mine != 0.0) atomicAdd(dst, mine);
+        if (lane < 21) {
+            const double kx = qsp / g.dt, kr = qsp / g.dx, ky = qsp * OPAL_C / g.dx;
+            const int k = lane;
+            const double scale = (k < 3 || k == 13 || k == 17) ? kx : (((k >= 9 && k < 13) || k == 16 || k == 20) ? kr : ky);
+            double* const dst = k < 3 ? g.jx + j - 1 + k : k < 6 ? g.jy + j - 1 + (k - 3) : k < 9 ? g.jz + j - 1 + (k - 6) : k < 13 ? g.rho + j - 2 + (k - 9)
+                              : k == 13 ? g.jx + j - 2 : k == 14 ? g.jy + j - 2 : k == 15 ? g.jz + j - 2 : k == 16 ? g.rho + j - 3
+                              : k == 17 ? g.jx + j + 2 : k == 18 ? g.jy + j + 2 : k == 19 ? g.jz + j + 2 : g.rho + j + 2;
+            if (v[0] != 0.0) atomicAdd(dst, scale * v[0]);
+        }
     }
     if (cfl) atomicOr(&st->err, ERR_CFL);
     if (cap_err) atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_MOVERS);

@@ -28,7 +28,7 @@ struct GridDev {
     double *ex, *ey, *ez, *bx, *by, *bz;
     // graph-replayed bursts of steps (host: run_burst): every step kernel returns at once when *halt is set (a bucket
     // overflowed or an assert fired in an earlier kernel of the burst); the laser amplitudes of step *step are
-    // laser_arr[2 * *step .. +1].  All three are null outside a burst.
+    // laser_arr[3 * *step .. +1], its time laser_arr[3 * *step + 2].  All three are null outside a burst.
     const int* halt;
     const int* step;
     const double* laser_arr;
