@@ -122,7 +122,9 @@ struct opal_ctx {
     } lean[2];
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
     opal_migrant* d_in[2] = {nullptr, nullptr};
-    int out_cap = 0;
+    int out_cap = 0;           // records the outboxes hold: grown before a push to the edge-cell populations (ensure_outbox)
+    int in_cap = 0;            // records the inboxes hold: grown to what the neighbours announce (exchange_migrants)
+    long long edge_bound[3][2] = {{-1, -1}, {-1, -1}, {-1, -1}};   // per species and side: most particles that can leave next step; -1 unknown
     int64_t pending_in[3][2] = {{0, 0}, {0, 0}, {0, 0}};   // host-staged migrants given, per species/side (for bookkeeping)
     double* d_halo_send = nullptr;   // [2][8][11]
     double* d_halo_recv = nullptr;   // [2][8][11]
@@ -139,6 +141,8 @@ struct opal_ctx {
     double* d_qed_tables = nullptr;
     int64_t last_gone[3][2] = {{0, 0}, {0, 0}, {0, 0}};
     uint64_t emit_calls = 0;
+    // emitter queue (BucketDev::eq_slot): filled by the electrons' push + scatter of a step of opal_run_steps with emission on
+    long long* d_eq_slot = nullptr; int* d_eq_cell = nullptr; int* d_eq_n = nullptr; int eq_cap = 0; bool eq_on = false;
     int64_t launches = 0;
     ncclComm_t comm = nullptr;
     // optional per-kernel timing (opal_timing): event pairs per category
@@ -179,7 +183,23 @@ BucketDev bdev(opal_ctx* c, int sp) {
     b.ncell = c->g.nx; b.start = B.d_start; b.count = B.d_count;
     for (int k = 0; k < NF_FULL; k++) b.f[k] = B.d_f[k];
     b.z_star = c->z_star; b.mass_number = c->mass_number;
+    if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) { b.eq_slot = c->d_eq_slot; b.eq_cell = c->d_eq_cell; b.eq_n = c->d_eq_n; b.eq_cap = c->eq_cap; }
     return b;
+}
+
+// the emitter queue holds at most one entry per electron of this slab
+bool ensure_emit_queue(opal_ctx* c) {
+    const long long want = std::max<long long>(c->bk[OPAL_ELECTRON].n_hint + c->bk[OPAL_ELECTRON].n_hint / 4 + 4096, 1 << 16);
+    if (c->d_eq_n && want <= c->eq_cap) return true;
+    if (want > (1ll << 30)) { c->eq_on = false; return true; }        // k_emit then scans
+    if (c->d_eq_slot) cudaFree(c->d_eq_slot);
+    if (c->d_eq_cell) cudaFree(c->d_eq_cell);
+    c->d_eq_slot = nullptr; c->d_eq_cell = nullptr;
+    if (!c->d_eq_n) { CUB(cudaMalloc(&c->d_eq_n, sizeof(int))); CUB(cudaMemset(c->d_eq_n, 0xFF, sizeof(int))); }
+    CUB(cudaMalloc(&c->d_eq_slot, (size_t)want * sizeof(long long)));
+    CUB(cudaMalloc(&c->d_eq_cell, (size_t)want * sizeof(int)));
+    c->eq_cap = (int)want;
+    return true;
 }
 PhotonDev pdev(opal_ctx* c, int which) {
     PhotonDev p;
@@ -487,7 +507,12 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
     CUB(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
     StepParams sp_ = sparams(c, sp);
     sp_.route_left = sp_.route_right = 0;
-    c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, old.full, deposit_parked, c->d_overflow, c->d_tmp_int, c->overflow_cap, 0, nullptr,
+    BucketDev dst_b = bdev(c, sp);
+    if (dst_b.eq_n) {            // the slots just moved: the emitter list of this step is void (k_emit scans instead)
+        CUB(cudaMemsetAsync(dst_b.eq_n, 0xFF, sizeof(int), c->stream));
+        dst_b.eq_slot = nullptr; dst_b.eq_cell = nullptr; dst_b.eq_n = nullptr; dst_b.eq_cap = 0;
+    }
+    c->k.scatter(c->stream, c->g, dst_b, sp_, old.full, deposit_parked, c->d_overflow, c->d_tmp_int, c->overflow_cap, 0, nullptr,
                  nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
     (void)n_parked;
     CUB(cudaStreamSynchronize(c->stream));
@@ -508,8 +533,12 @@ bool handle_overflow(opal_ctx* c, int sp, bool deposit_parked) {
 }
 
 // write the record counts into the header records of both outboxes
-__global__ void k_outbox_headers(opal_migrant* out_l, opal_migrant* out_r, const StatusDev* st) {
-    if (threadIdx.x == 0) { out_l[0].cell = st->n_out[0]; out_r[0].cell = st->n_out[1]; }
+// (charged species: also the populations of the slab's two edge cells, the bound on the next step's leavers)
+__global__ void k_outbox_headers(opal_migrant* out_l, opal_migrant* out_r, StatusDev* st, const int* count, int ncell) {
+    if (threadIdx.x == 0) {
+        out_l[0].cell = st->n_out[0]; out_r[0].cell = st->n_out[1];
+        if (count) { st->edge[0] = count[0]; st->edge[1] = count[ncell - 1]; }
+    }
 }
 __global__ void k_header_to_int(const opal_migrant* in, int* n) { if (threadIdx.x == 0) *n = (int)in[0].cell; }
 // burst mode: empty the destination of the photon ping-pong -- unless the burst has halted (a memset node would wipe the live store)
@@ -517,8 +546,10 @@ __global__ void k_burst_zero_int(const StatusDev* st, int* p) {
     if (threadIdx.x == 0 && !*(volatile const int*)&st->halt) *p = 0;
 }
 // burst mode: before k_emit, is there room for one photon per electron (electron.rs:208-251)?  If not: halt, the host grows the store
-__global__ void k_burst_photon_room(StatusDev* st, const int* ph_n, int cap, long long need, int phase) {
+// (eq_n: the emitter list's count when the push kept one -- then the exact number of photons this step can add)
+__global__ void k_burst_photon_room(StatusDev* st, const int* ph_n, int cap, long long need, const int* eq_n, int eq_cap, int phase) {
     if (threadIdx.x != 0 || *(volatile int*)&st->halt) return;
+    if (eq_n) { const int q = *eq_n; if (q >= 0 && q <= eq_cap) need = q; }
     if ((long long)*ph_n + need > (long long)cap) { st->halt_species = phase; __threadfence(); st->halt = 1; }
 }
 // live particles of a species: sum of count[] (out must be zeroed)
@@ -564,16 +595,109 @@ struct Timed {   // RAII bracket of one launch with a cudaEvent pair when timing
 
 bool remote(opal_ctx* c) { return !c->self_nbr() && (c->has_left() || c->has_right()); }
 
+// The outboxes must hold every leaver of the coming push: a particle moves less than a cell per step (assert dxi < 1,
+// electron.rs:313), so the leavers through an edge are at most the particles sitting in that edge cell now.
+bool ensure_outbox(opal_ctx* c, int sp) {
+    if (!remote(c)) return true;
+    long long need = 0;
+    for (int side = 0; side < 2; side++) {
+        if (c->edge_bound[sp][side] < 0) {             // unknown (fresh upload / first step): read it
+            if (sp == OPAL_PHOTON) {
+                int n = 0;
+                if (!photon_count(c, &n)) return false;
+                c->edge_bound[sp][side] = n;
+            } else if (c->bk[sp].allocated) {
+                int v = 0;
+                CUB(cudaMemcpyAsync(&v, c->bk[sp].d_count + (side == 0 ? 0 : c->g.nx - 1), sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+                CUB(cudaStreamSynchronize(c->stream));
+                c->edge_bound[sp][side] = v;
+            } else c->edge_bound[sp][side] = 0;
+        }
+        need = std::max(need, c->edge_bound[sp][side]);
+    }
+    need += 64;
+    if (need <= c->out_cap) return true;
+    if (need > (1ll << 24)) return fail(c, OPAL_ECAPACITY, "neighbour outbox: more than 2^24 particles in an edge cell");
+    const long long cap = std::max<long long>(need + need / 4, 2ll * c->out_cap);
+    for (int s_ = 0; s_ < 2; s_++) {
+        if (c->d_out[s_]) cudaFree(c->d_out[s_]);
+        c->d_out[s_] = nullptr;
+        CUB(cudaMalloc(&c->d_out[s_], (size_t)(cap + 1) * sizeof(opal_migrant)));
+    }
+    c->out_cap = (int)cap;
+    return true;
+}
+
+bool insert_inbox(opal_ctx* c, int sp, int side, bool dep);
+
+bool ensure_inbox(opal_ctx* c, long long need) {
+    if (need <= c->in_cap) return true;
+    if (need > (1ll << 24)) return fail(c, OPAL_ECAPACITY, "neighbour inbox: more than 2^24 particles announced");
+    const long long cap = std::max<long long>(need + need / 4, 2ll * c->in_cap);
+    for (int side = 0; side < 2; side++) {
+        opal_migrant* fresh = nullptr;
+        CUB(cudaMalloc(&fresh, (size_t)(cap + 1) * sizeof(opal_migrant)));
+        CUB(cudaMemcpyAsync(fresh, c->d_in[side], sizeof(opal_migrant), cudaMemcpyDeviceToDevice, c->stream));    // keep the header
+        CUB(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_in[side]);
+        c->d_in[side] = fresh;
+    }
+    c->in_cap = (int)cap;
+    return true;
+}
+
+// Neighbour exchange of the leavers of species `sp` (mod.rs:290-373) over NCCL, in two phases: the counts first (one
+// 128-byte header each way), then exactly that many records -- the reference sends unbounded Vecs; nothing here is
+// capped: the sender sized its outbox before the push (ensure_outbox), the receiver grows its inbox to what is announced.
+bool exchange_migrants(opal_ctx* c, int sp, bool dep) {
+    k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status, sp == OPAL_PHOTON ? nullptr : c->bk[sp].d_count, c->g.nx);
+    c->launches++;
+    if (!c->comm) {                                   // host-staged exchange: opal_migrants_take / give
+        c->edge_bound[sp][0] = c->edge_bound[sp][1] = -1;          // (re-read before the next push: the gives come later)
+        return true;
+    }
+    if (!nccl_exchange(c, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], sizeof(opal_migrant))) return false;
+    opal_migrant hdr[2];
+    memset(hdr, 0, sizeof(hdr));
+    for (int side = 0; side < 2; side++)
+        CUB(cudaMemcpyAsync(&hdr[side], c->d_in[side], sizeof(opal_migrant), cudaMemcpyDeviceToHost, c->stream));
+    if (!fetch_status(c)) return false;               // synchronises: the headers have arrived too
+    const long long n_out[2] = {c->has_left() ? c->h_status->n_out[0] : 0, c->has_right() ? c->h_status->n_out[1] : 0};
+    const long long n_in[2] = {c->has_left() ? hdr[0].cell : 0, c->has_right() ? hdr[1].cell : 0};
+    if (!ensure_inbox(c, std::max(n_in[0], n_in[1]))) return false;
+    if (n_out[0] + n_out[1] + n_in[0] + n_in[1] > 0) {
+        int rc = g_nccl.GroupStart();
+        // (both neighbours may be the same rank: my send-to-right pairs with its recv-from-left -- same order on both ends)
+        if (n_out[1]) rc |= g_nccl.Send(c->d_out[1] + 1, (size_t)n_out[1] * sizeof(opal_migrant), NCCL_CHAR, c->right_rank(), c->comm, c->stream);
+        if (n_out[0]) rc |= g_nccl.Send(c->d_out[0] + 1, (size_t)n_out[0] * sizeof(opal_migrant), NCCL_CHAR, c->left_rank(), c->comm, c->stream);
+        if (n_in[0]) rc |= g_nccl.Recv(c->d_in[0] + 1, (size_t)n_in[0] * sizeof(opal_migrant), NCCL_CHAR, c->left_rank(), c->comm, c->stream);
+        if (n_in[1]) rc |= g_nccl.Recv(c->d_in[1] + 1, (size_t)n_in[1] * sizeof(opal_migrant), NCCL_CHAR, c->right_rank(), c->comm, c->stream);
+        rc |= g_nccl.GroupEnd();
+        if (rc) return fail(c, OPAL_ENCCL, "ncclSend/ncclRecv failed");
+    }
+    if (n_in[0]) insert_inbox(c, sp, OPAL_LEFT, dep);
+    if (n_in[1]) insert_inbox(c, sp, OPAL_RIGHT, dep);
+    // what can leave in the next step: who sits in the edge cells now, plus who just arrived there
+    for (int side = 0; side < 2; side++) c->edge_bound[sp][side] = (long long)c->h_status->edge[side] + n_in[side];
+    if (sp == OPAL_PHOTON)       // ... plus one photon per electron of the edge cell (emit_radiation comes after the photons' advance)
+        for (int side = 0; side < 2; side++) {
+            c->edge_bound[sp][side] += std::max<long long>(c->edge_bound[OPAL_ELECTRON][side], 0);
+            if (c->absorb_on) c->edge_bound[sp][side] *= 2;       // ... and a stimulated copy of each photon there (photon.rs:312-362)
+        }
+    return true;
+}
+
+
 // insert what the neighbours sent (d_in[side], header + records) into species `sp`
 bool insert_inbox(opal_ctx* c, int sp, int side, bool dep) {
     k_header_to_int<<<1, 32, 0, c->stream>>>(c->d_in[side], c->d_tmp_int + 1 + side); c->launches++;
     const long long shift = side == OPAL_RIGHT ? c->g.nx : 0;   // mod.rs:366-368
     if (sp == OPAL_PHOTON) {
-        c->k.photon_insert(c->stream, pdev(c, c->ph_cur), c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->out_cap, shift, c->d_status);
+        c->k.photon_insert(c->stream, pdev(c, c->ph_cur), c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->in_cap, shift, c->d_status);
     } else {
         StepParams sp_ = sparams(c, sp);
         sp_.route_left = sp_.route_right = 0;
-        c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, c->bk[sp].full, dep, c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->out_cap, shift,
+        c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, c->bk[sp].full, dep, c->d_in[side] + 1, c->d_tmp_int + 1 + side, c->in_cap, shift,
                      nullptr, nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status);
     }
     c->launches++;
@@ -585,6 +709,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     Buckets& B = c->bk[sp];
     if (!B.allocated) { c->last_gone[sp][0] = c->last_gone[sp][1] = 0; return true; }
     if (check && !size_movers_for(c, sp)) return false;      // (the unchecked callers -- graph capture -- size up front)
+    if (!ensure_outbox(c, sp)) return false;
     if (!reset_status(c, true)) return false;
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
@@ -595,6 +720,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
         CUB(cudaMemsetAsync(ke_out, 0, sizeof(double), c->stream));
     }
     opal_ctx::Lean& L = c->lean[sp];
+    if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) CUB(cudaMemsetAsync(c->d_eq_n, 0, sizeof(int), c->stream));   // this step's emitter list starts empty
     if (!dep && !flush_strips(c, sp)) return false;          // the call-by-call push does not read the strips
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
     { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
@@ -603,15 +729,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }      // this push's movers wait for the next one
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++; }
-    if (remote(c)) {
-        k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status); c->launches++;
-        if (c->comm) {
-            const size_t bytes = (size_t)(c->out_cap + 1) * sizeof(opal_migrant);
-            if (!nccl_exchange(c, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], bytes)) return false;
-            if (c->has_left()) insert_inbox(c, sp, OPAL_LEFT, dep);
-            if (c->has_right()) insert_inbox(c, sp, OPAL_RIGHT, dep);
-        }
-    }
+    if (remote(c) && !exchange_migrants(c, sp, dep)) return false;
     if (check) {
         if (!fetch_status(c)) return false;
         c->last_gone[sp][0] = c->h_status->gone[0]; c->last_gone[sp][1] = c->h_status->gone[1];
@@ -624,21 +742,14 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
 bool advance_photons(opal_ctx* c, bool check) {
     if (c->flags & OPAL_FLAG_IMMOBILE_PHOTONS) return true;
     if (c->ph[0].cap == 0) { c->last_gone[2][0] = c->last_gone[2][1] = 0; return true; }
+    if (!ensure_outbox(c, OPAL_PHOTON)) return false;
     if (!reset_status(c, true)) return false;
     const int src = c->ph_cur, dst = 1 - src;
     CUB(cudaMemsetAsync(c->ph[dst].d_n, 0, sizeof(int), c->stream));
     c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status);
     c->launches++;
     c->ph_cur = dst;
-    if (remote(c)) {
-        k_outbox_headers<<<1, 32, 0, c->stream>>>(c->d_out[0], c->d_out[1], c->d_status); c->launches++;
-        if (c->comm) {
-            const size_t bytes = (size_t)(c->out_cap + 1) * sizeof(opal_migrant);
-            if (!nccl_exchange(c, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], bytes)) return false;
-            if (c->has_left()) insert_inbox(c, OPAL_PHOTON, OPAL_LEFT, false);
-            if (c->has_right()) insert_inbox(c, OPAL_PHOTON, OPAL_RIGHT, false);
-        }
-    }
+    if (remote(c) && !exchange_migrants(c, OPAL_PHOTON, false)) return false;
     if (check) {
         if (!fetch_status(c)) return false;
         c->last_gone[2][0] = c->h_status->gone[0]; c->last_gone[2][1] = c->h_status->gone[1];
@@ -750,6 +861,7 @@ void enqueue_species(opal_ctx* c, int sp, bool fused) {     // advance_charged w
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
     c->k.burst_mark(c->stream, c->d_status, 0, sp);
+    if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->d_eq_n);
     opal_ctx::Lean& L = c->lean[sp];
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
     const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
@@ -773,7 +885,8 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
         n += 3;
     }
     if (cfg.emit && c->bk[OPAL_ELECTRON].allocated) {
-        k_burst_photon_room<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[c->ph_cur].d_n, c->ph[c->ph_cur].cap, c->bk[OPAL_ELECTRON].n_hint, PH_EMIT_ROOM);
+        k_burst_photon_room<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[c->ph_cur].d_n, c->ph[c->ph_cur].cap, c->bk[OPAL_ELECTRON].n_hint,
+                                                     c->eq_on ? c->d_eq_n : nullptr, c->eq_cap, PH_EMIT_ROOM);
         // t and the call index of step k come from the device-side step counter (GridDev::step / laser_arr[3k + 2])
         c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, 0.0, cfg.f3[0], cfg.f3[1], cfg.f3[2],
                   c->seed, emit_call0, c->d_status);
@@ -897,10 +1010,10 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     CU(cudaMalloc(&c->d_energy, 8 * sizeof(double)));
     CU(cudaMallocHost(&c->h_energy, 8 * sizeof(double)));
     CU(cudaMalloc(&c->d_tmp_int, 8 * sizeof(int)));
-    c->out_cap = (int)env_ll("OPAL_EXCHANGE_CAP", 4096);
+    c->out_cap = c->in_cap = (int)env_ll("OPAL_EXCHANGE_CAP", 4096);      // initial sizes: both grow on demand
     for (int s = 0; s < 2; s++) {
         CU(cudaMalloc(&c->d_out[s], (size_t)(c->out_cap + 1) * sizeof(opal_migrant)));
-        CU(cudaMalloc(&c->d_in[s], (size_t)(c->out_cap + 1) * sizeof(opal_migrant)));
+        CU(cudaMalloc(&c->d_in[s], (size_t)(c->in_cap + 1) * sizeof(opal_migrant)));
         CU(cudaMemsetAsync(c->d_in[s], 0, sizeof(opal_migrant), c->stream));
     }
     CU(cudaMalloc(&c->d_halo_send, 2 * OPAL_HALO_CELLS * OPAL_CELL_DOUBLES * sizeof(double)));
@@ -928,7 +1041,7 @@ opal_status opal_destroy(opal_ctx* c) {
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
     void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
-                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser};
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n};
     for (void* p : frees) if (p) cudaFree(p);
     for (int sp = 0; sp < 2; sp++) {
         for (int k = 0; k < 2; k++) { if (c->lean[sp].d_strips[k]) cudaFree(c->lean[sp].d_strips[k]); if (c->lean[sp].d_scount[k]) cudaFree(c->lean[sp].d_scount[k]); }
@@ -961,6 +1074,7 @@ opal_status opal_particles_upload(opal_ctx* c, int species, int64_t n, const int
                                   const double* uy, const double* uz, const double* w, const double* tau) {
     CHECK_CTX(c);
     c->ke_fused = false;
+    if (species >= 0 && species <= 2) c->edge_bound[species][0] = c->edge_bound[species][1] = -1;
     if (n < 0 || n > (1ll << 31) - 64 || (n > 0 && (!cell || !x || !ux || !uy || !uz || !w))) return OPAL_EINVAL;
     const double dx = c->g.dx, dt = c->g.dt;
     const double inf = std::numeric_limits<double>::infinity();
@@ -1039,6 +1153,7 @@ opal_status opal_particles_generate(opal_ctx* c, int species, int64_t npc, doubl
                                     int two_stream, int64_t global_cell_offset, uint64_t seed) {
     CHECK_CTX(c);
     c->ke_fused = false;
+    if (species == OPAL_ELECTRON || species == OPAL_ION) c->edge_bound[species][0] = c->edge_bound[species][1] = -1;
     if ((species != OPAL_ELECTRON && species != OPAL_ION) || npc < 1 || !u_th || !drift) return OPAL_EINVAL;
     Buckets& B = c->bk[species];
     free_buckets(B);
@@ -1239,7 +1354,7 @@ opal_status opal_migrants_give(opal_ctx* c, int species, int side, int64_t n, co
     c->ke_fused = false;
     if (side != OPAL_LEFT && side != OPAL_RIGHT || n < 0 || species < 0 || species > 2) return OPAL_EINVAL;
     if (n == 0) return OPAL_OK;
-    if (n > c->out_cap) return OPAL_ECAPACITY;
+    if (!ensure_inbox(c, n)) return (opal_status)c->status;
     opal_migrant hdr;
     memset(&hdr, 0, sizeof(hdr));
     hdr.cell = n;
@@ -1403,6 +1518,8 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     double t = t0;
     c->ke_fused = false;
     int64_t s0 = 0;
+    c->eq_on = cfg.emit && !c->absorb_on && c->bk[OPAL_ELECTRON].allocated && !(c->flags & OPAL_FLAG_STRICT_FP);
+    if (c->eq_on && !ensure_emit_queue(c)) return (opal_status)c->status;
     // room for the cell-crossing particles of a freshly loaded population (before any graph capture: it reads back a count)
     if (!size_movers_for(c, OPAL_ELECTRON) || !size_movers_for(c, OPAL_ION)) return (opal_status)c->status;
     // Launch- and sync-bound decks: replay the step as a CUDA graph (all but the last one or two steps, which also sum the
@@ -1444,6 +1561,7 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
         if (!run_phases(c, cfg, PH_ELECTRONS, t, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0, s == nsteps - 1 && !cfg.emit && !c->absorb_on)) break;
         t += c->g.dt;
     }
+    if (c->eq_on) { c->eq_on = false; cudaMemsetAsync(c->d_eq_n, 0xFF, sizeof(int), c->stream); }     // the list belongs to a step of this call
     if (c->status == OPAL_OK) {
         cudaError_t e = cudaStreamSynchronize(c->stream);
         if (e == cudaSuccess) e = cudaGetLastError();

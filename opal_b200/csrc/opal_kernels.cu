@@ -269,6 +269,10 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
             if (FULL) {
                 b.f[F_PREVX][s] = m.prev_x; b.f[F_GAMMA][s] = SP == OPAL_ION ? m.pad[0] : m.gamma; b.f[F_CHI][s] = m.chi;
                 b.f[F_TAU][s] = m.tau; b.f[F_WORK][s] = m.work; b.f[F_Y][s] = m.y; b.f[F_Z][s] = m.z;
+                if (SP == OPAL_ELECTRON && b.eq_n && m.tau < 0.0) {        // an emitter of this step (see BucketDev::eq_slot)
+                    const int k = atomicAdd(b.eq_n, 1);
+                    if (k >= 0 && k < b.eq_cap) { b.eq_slot[k] = s; b.eq_cell[k] = c; }
+                }
             }
             if (DEP && m.pad[1] == 0.0) {       // pad[1] == 1: the lean push that handed this record over deposited it already
                 const double Q = m.weight * q;
@@ -380,6 +384,10 @@ __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, P
             const int leader = __ffs(mk) - 1;
             if (lane == leader) base = atomicAdd(dst.n, __popc(mk));
             base = __shfl_sync(FULLMASK, base, leader);
+        }
+        if (sp.route_left == 2 || sp.route_right == 2) {      // a neighbour slab: who sits in the edge cells now can leave next step
+            const unsigned e0 = __ballot_sync(FULLMASK, keep && cell == 0), e1 = __ballot_sync(FULLMASK, keep && cell == g.nx - 1);
+            if (lane == 0) { if (e0) atomicAdd(&st->edge[0], __popc(e0)); if (e1) atomicAdd(&st->edge[1], __popc(e1)); }
         }
         if (keep) {
             const int o = base + __popc(mk & lt_mask);
@@ -725,6 +733,19 @@ __global__ void __launch_bounds__(BLOCK, OPAL_EMIT_MB) k_emit(GridDev g, BucketD
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * WARPS_PER_BLOCK;
     bool chi_err = false;
+    const int qn = b.eq_n ? *b.eq_n : -1;
+    if (qn >= 0 && qn <= b.eq_cap) {
+        // the push and the scatter of this step listed the emitters: sample exactly those, every lane busy
+        const int n_round = (qn + 31) & ~31;
+        for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_round; j += gridDim.x * blockDim.x) {      // whole warps: emit_append votes
+            bool store_photon = false;
+            opal_migrant m;
+            if (j < qn) store_photon = emit_one(b, sp, s_tab, b.eq_slot[j], b.eq_cell[j], t, min_energy, max_angle, max_fl, seed, call_index, m, chi_err);
+            emit_append(ph, store_photon, m, st);
+        }
+        if (chi_err) atomicOr(&st->err, ERR_CHI);
+        return;
+    }
     for (int c0 = blockIdx.x * WARPS_PER_BLOCK; c0 < b.ncell; c0 += warps_total) {     // block-uniform trip count
         const int c = c0 + (threadIdx.x >> 5);
         const int n = c < b.ncell ? b.count[c] : 0;

@@ -197,9 +197,21 @@ k_push_full_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                     if (lane == leader) mbase = atomicAdd(seg_count + seg, __popc(m_move));
                     mbase = __shfl_sync(FULLMASK, mbase, leader);
                 }
+                // electrons whose optical depth has run out (electron.rs:209) and that stay here: listed for k_emit
+                const unsigned m_q = b.eq_n ? __ballot_sync(FULLMASK, stay && tau < 0.0) : 0u;
+                int qbase = 0;
+                if (m_q) {
+                    const int leader = __ffs(m_q) - 1;
+                    if (lane == leader) qbase = atomicAdd(b.eq_n, __popc(m_q));
+                    qbase = __shfl_sync(FULLMASK, qbase, leader);
+                }
                 if (stay) {
                     const int pos = written + __popc(m_stay & lt_mask);
                     const long long s = base + pos;
+                    if ((m_q >> lane) & 1u) {
+                        const int k = qbase + __popc(m_q & lt_mask);
+                        if (k >= 0 && k < b.eq_cap) { b.eq_slot[k] = s; b.eq_cell[k] = c; }
+                    }
                     b.f[F_X][s] = xn; b.f[F_PREVX][s] = prev_x; b.f[F_UX][s] = u.x; b.f[F_UY][s] = u.y; b.f[F_UZ][s] = u.z;
                     b.f[F_GAMMA][s] = gam; b.f[F_CHI][s] = chi; b.f[F_TAU][s] = tau; b.f[F_WORK][s] = work; b.f[F_Y][s] = y; b.f[F_Z][s] = z;
                     if (pos != i) b.f[F_W][s] = W;

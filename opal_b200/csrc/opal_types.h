@@ -43,6 +43,11 @@ struct BucketDev {
     int* count;
     double* f[NF_FULL];
     double z_star, mass_number;     // ions (ion.rs:236)
+    // Emitter queue (electrons, full state, emission inside opal_run_steps; null otherwise): the push and the scatter that
+    // precede emit_radiation in a step know which electrons' optical depth has run out (electron.rs:209) and where they ended
+    // up -- they list (slot, cell), and k_emit samples exactly those with every lane busy instead of scanning tau of all.
+    // *eq_n < 0 or > eq_cap: the list is not valid (a re-layout moved the slots / it overflowed) -> k_emit scans.
+    long long* eq_slot = nullptr; int* eq_cell = nullptr; int* eq_n = nullptr; int eq_cap = 0;
 };
 
 struct PhotonDev {
@@ -64,8 +69,10 @@ struct StatusDev {
     // burst mode (see GridDev::halt)
     int halt;            // set by k_burst_check: the host has to intervene before the next kernel may run
     int step;            // steps of the burst completed so far
-    int halt_species;    // the species whose advance raised the halt
+    int halt_species;    // the species (phase) whose advance raised the halt
     int pad2;
+    int edge[2];         // multi-slab: particles of the species just advanced that sit in the slab's first / last cell -- all that can
+                         // leave through that edge in the NEXT step (|dxi| < 1): the sender sizes its outbox from it
 };
 enum { ERR_CFL = 1u, ERR_INDEX = 2u, ERR_CHI = 4u, ERR_CAPACITY = 8u,
        // which fixed-capacity buffer overflowed (set together with ERR_CAPACITY)

@@ -134,10 +134,17 @@ def main():
     cases = (("periodic_1e6", FLAG_LEAN_STATE, True, True),          # the layout bench.py and SCALE run
              ("laser_balanced_1e6", FLAG_LEAN_STATE, True, True),    # unequal slabs (GridDesign.balanced), open edges
              ("periodic", FLAG_LEAN_STATE, True, True), ("periodic", 0, True, True), ("periodic", 0, True, False),
-             ("laser", 0, False, True), ("laser_sparse", 0, False, True), ("laser_sparse", 0, True, True))
+             ("laser", 0, False, True), ("laser_sparse", 0, False, True), ("laser_sparse", 0, True, True),
+             # the neighbour exchange is unbounded (mod.rs:296-354 sends Vecs): outbox and inbox start at TWO records and grow
+             ("periodic_tiny_boxes", FLAG_LEAN_STATE, True, True), ("periodic_tiny_boxes", 0, True, True))
     for case, flags, fused, per_step in cases:
         if only and case not in only.split(","):
             continue
+        if case == "periodic_tiny_boxes":
+            os.environ["OPAL_EXCHANGE_CAP"] = "2"
+            case = "periodic"
+        else:
+            os.environ.pop("OPAL_EXCHANGE_CAP", None)
         res = run_ring_parity(gpu, dist, rank, world, local, ring_case(case), flags, fused, per_step=per_step)
         if rank == 0:
             ok = ok and res["ok"]

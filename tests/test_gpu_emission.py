@@ -83,3 +83,50 @@ def test_emission_filters_and_bookkeeping(gpu, oracle):
     # and with it its Philox counter, depends on atomic ordering -- like the reference's thread-dependent streams)
     se = np.sqrt(elg["gamma"].var() / elg["gamma"].size + ela["gamma"].var() / ela["gamma"].size)
     assert abs(elg["gamma"].mean() - ela["gamma"].mean()) < 5.0 * se
+
+
+def _run_fused(abi, monkeypatch, burst, chi0=0.5, n=40000, chunks=(37, 6, 50)):
+    """the same beam through opal_run_steps with emission on (main.rs:238-267), several calls of uneven length"""
+    monkeypatch.setenv("OPAL_BURST", burst)
+    nx, dx = 256, 1.0e-8
+    s = Slab(abi, nx, 0.0, dx, seed=7)
+    gamma0 = 1000.0
+    e0 = chi0 * CRITICAL_FIELD / (2.0 * gamma0)
+    f = s.fields()
+    f[:, 6] = e0
+    f[:, 10] = e0 / SPEED_OF_LIGHT
+    s.set_fields(f)
+    rng = np.random.default_rng(4242)
+    w = 1.0 + 1.0e-6 * np.arange(n)                                   # unique weights: photons inherit them (electron.rs:243)
+    s.upload(ELECTRON, rng.integers(0, nx, n), rng.random(n), -gamma0 * (1.0 + 0.01 * rng.standard_normal(n)), np.zeros(n), np.zeros(n), w,
+             rng.exponential(1.0, n))
+    t = 0.0
+    for k in chunks:
+        s.run_steps(k, t, current_deposition=False, photon_emission=True, emit_filters=(None, 0.05, None))
+        t += k * s.dt
+    ph, el, bursts = s.download(PHOTON), s.download(ELECTRON), s.burst_steps()
+    s.close()
+    return ph, el, bursts
+
+
+def test_emission_inside_graph_replayed_bursts_matches_the_step_by_step_path(gpu, monkeypatch):
+    """opal_run_steps with emission on runs as replayed CUDA graphs too (photon push, the push-built emitter list, the
+    device-side room check of the photon store, k_emit reading time and call index from the device-side step counter).
+    The draws are keyed by (seed, call index, bucket slot) and the slots of cell-crossing particles are handed out by
+    atomics, so two runs are two realisations: yields and spectra are compared statistically; the times of birth -- the
+    device-side step counter at work -- must be the very same set of values main.rs:266 accumulates."""
+    pa, ea, ba = _run_fused(gpu, monkeypatch, "1")
+    pb, eb, bb = _run_fused(gpu, monkeypatch, "0")
+    assert ba > 60 and bb == 0
+    na, nb = pa["cell"].size, pb["cell"].size
+    assert na > 10000 and abs(na - nb) < 4.0 * np.sqrt(na + nb), (na, nb)
+    assert np.array_equal(np.unique(pa["birth_time"]), np.unique(pb["birth_time"]))
+    assert stats.ks_2samp(np.log(pa["gamma"]), np.log(pb["gamma"])).pvalue > 1.0e-3
+    assert stats.ks_2samp(pa["x"] + pa["cell"], pb["x"] + pb["cell"]).pvalue > 1.0e-3
+    # every photon carries the weight of the electron that emitted it (electron.rs:243); no electron is lost
+    assert np.isin(pa["weight"], ea["weight"]).all() and ea["weight"].size == eb["weight"].size == 40000
+    ga, gb = ea["gamma"], eb["gamma"]
+    assert abs(ga.mean() - gb.mean()) < 4.0 * np.sqrt(ga.var() / ga.size + gb.var() / gb.size)
+    # what the electrons lost is what the photons carry (recoil bookkeeping, electron.rs:234-239), on both paths
+    for ph, el in ((pa, ea), (pb, eb)):
+        assert ph["gamma"].dot(ph["weight"]) == pytest.approx((1000.0 * el["weight"]).sum() - el["gamma"].dot(el["weight"]), rel=0.05)

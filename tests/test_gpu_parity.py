@@ -308,7 +308,7 @@ def test_two_gpu_nccl_ring_matches_the_oracle_ring_step_by_step():
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                           "--master-port", "29531", str(script)], capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert out.stdout.count("MGPU OK") == 8, out.stdout[-3000:]
+    assert out.stdout.count("MGPU OK") == 10, out.stdout[-3000:]
 
 
 @pytest.mark.parametrize("flags", [0, FLAG_LEAN_STATE])
