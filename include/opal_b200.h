@@ -65,6 +65,15 @@ enum {
     OPAL_FLAG_NO_BEAMING            = 1u << 1,
     OPAL_FLAG_IMMOBILE_PHOTONS      = 1u << 2,
     OPAL_FLAG_NO_STIMULATED_EMISSION = 1u << 3,
+    /* EXTENSION, off by default, no counterpart in the reference (north_star names it under src/qed; opal only carries the
+       unused optical depth Photon.tau, photon.rs:27,126-132 -- parity unpinned): nonlinear Breit-Wheeler pair creation.
+       Every photon advance lowers Photon.tau by W dt, W = alpha_f F(chi) / (tau_C k0) (Baier-Katkov / Ritus; tables from
+       tools/gen_bw_tables.py); a photon whose depth runs out is replaced by an electron with momentum f k and a positron
+       with (1 - f) k (f sampled from dW/df; momentum conserved exactly) at its position, both with its weight and fresh
+       optical depths.  POSITRONS LIVE IN THE ION SLOT (Z* = +1, A = m_e / m_p: Boris push ion.rs:168-214, deposit, migration,
+       outputs as `ions`; they do not radiate): the flag therefore needs a run without ions, and opal_set_ion is refused.
+       With the flag off every result is bit-identical to a build without the extension.                                     */
+    OPAL_FLAG_PAIR_CREATION         = 1u << 4,
     /* Charged species keep only (x, u, weight) per particle; prev_x, gamma and velocity are
        recomputed in registers by the fused push+deposit kernel and work/chi/tau/y/z (which are
        unobservable with QED and such outputs off) are not maintained.  Only opal_run_steps()
@@ -255,6 +264,12 @@ opal_status OPAL_FN(qed_rate)(int64_t n, const double* chi, const double* gamma,
 /* photon_emission::sample (:129) -> out[3n] = (omega/mc^2, theta, phi) */
 opal_status OPAL_FN(qed_sample)(int64_t n, const double* chi, const double* gamma, const double* r1,
                                 const double* r2, const double* r3, int classical, double* out3);
+/* EXTENSION (OPAL_FLAG_PAIR_CREATION; nothing in the reference): F(chi) = chi T(chi) of nonlinear Breit-Wheeler pair creation --
+   the rate is alpha_f F(chi) / (tau_C k0) -- and the electron's share f of the photon energy for uniforms r1, r2 */
+opal_status OPAL_FN(bw_rate)(int64_t n, const double* chi, double* out);
+opal_status OPAL_FN(bw_sample)(int64_t n, const double* chi, const double* r1, const double* r2, double* out);
+/* pairs created so far on this slab (0 unless OPAL_FLAG_PAIR_CREATION) */
+opal_status OPAL_FN(pairs_created)(opal_ctx*, int64_t* n);
 /* airy_ai_for_positive (qed/special_functions/airy.rs:19): ai[i] = Ai(x[i]); defined[i] = 0 where the
    reference returns None (x < 0, x >= 50 or NaN), and ai[i] = 0 there */
 opal_status OPAL_FN(qed_airy)(int64_t n, const double* x, double* ai, int* defined);

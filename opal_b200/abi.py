@@ -20,6 +20,7 @@ FLAG_NO_RADIATION_REACTION = 1 << 0
 FLAG_NO_BEAMING = 1 << 1
 FLAG_IMMOBILE_PHOTONS = 1 << 2
 FLAG_NO_STIMULATED_EMISSION = 1 << 3
+FLAG_PAIR_CREATION = 1 << 4      # extension: nonlinear Breit-Wheeler pair creation (no reference counterpart)
 FLAG_LEAN_STATE = 1 << 8
 FLAG_STRICT_FP = 1 << 9
 GHOST_SIZE, LASER_BDY_SIZE, ABSORBING_BDY_SIZE, CONDUCTING_BDY_SIZE = 4, 4, 200, 4
@@ -79,6 +80,9 @@ SIGNATURES = {
     "qed_airy": [_i64, _vp, _vp, _vp],
     "qed_pair_cross_sections": [_i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "fields_at": [_vp, _i64, _vp, _vp, _vp],
+    "bw_rate": [_i64, _vp, _vp],
+    "bw_sample": [_i64, _vp, _vp, _vp, _vp],
+    "pairs_created": [_vp, _pi64],
 }
 
 
@@ -128,6 +132,26 @@ class OpalABI:
         st = self.qed_sample(n, _ptr(chi), _ptr(gamma), _ptr(r1), _ptr(r2), _ptr(r3), int(classical), _ptr(out))
         if st:
             raise OpalError(st, "qed_sample")
+        return out
+
+    def bw_f(self, chi):
+        """F(chi) = chi T(chi) of the Breit-Wheeler extension (rate = alpha_f F / (tau_C k0))"""
+        chi = _f64arr(np.atleast_1d(chi))
+        out = np.empty_like(chi)
+        st = self.bw_rate(chi.size, _ptr(chi), _ptr(out))
+        if st:
+            raise OpalError(st, "bw_rate")
+        return out
+
+    def bw_share(self, chi, r1, r2):
+        """the electron's share f of the photon energy in a Breit-Wheeler pair, for uniforms r1, r2"""
+        chi = _f64arr(np.atleast_1d(chi))
+        n = chi.size
+        r1, r2 = (_f64arr(np.broadcast_to(np.atleast_1d(v), (n,))) for v in (r1, r2))
+        out = np.empty(n)
+        st = self.bw_sample(n, _ptr(chi), _ptr(r1), _ptr(r2), _ptr(out))
+        if st:
+            raise OpalError(st, "bw_sample")
         return out
 
     def airy(self, x):
@@ -367,6 +391,11 @@ class Slab:
         s = C.c_void_p()
         self._ck(self.abi.stream(self._h, C.byref(s)), "stream")
         return s.value or 0
+
+    def pairs_created(self):
+        n = C.c_int64(0)
+        self._ck(self.abi.pairs_created(self._h, C.byref(n)), "pairs_created")
+        return n.value
 
     def launch_count(self):
         n = C.c_int64()

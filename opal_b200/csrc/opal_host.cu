@@ -141,6 +141,9 @@ struct opal_ctx {
     double* d_qed_tables = nullptr;
     int64_t last_gone[3][2] = {{0, 0}, {0, 0}, {0, 0}};
     uint64_t emit_calls = 0;
+    // Breit-Wheeler extension (OPAL_FLAG_PAIR_CREATION): the pairs one photon advance creates, as electron / positron records
+    opal_migrant* d_pair[2] = {nullptr, nullptr}; int* d_pair_n = nullptr; int pair_cap = 0; unsigned pair_calls = 0; int64_t pairs_created = 0;
+    bool ion_slot_is_user = false;   // opal_set_ion was called: the ion slot holds real ions
     // emitter queue (BucketDev::eq_slot): filled by the electrons' push + scatter of a step of opal_run_steps with emission on
     long long* d_eq_slot = nullptr; int* d_eq_cell = nullptr; int* d_eq_n = nullptr; int eq_cap = 0; bool eq_on = false;
     int64_t launches = 0;
@@ -739,6 +742,48 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     return true;
 }
 
+// ---- Breit-Wheeler extension: room for the pairs of one photon advance, and their insertion into the charged species ----
+bool prepare_pairs(opal_ctx* c) {
+    if (c->ion_slot_is_user) return fail(c, OPAL_EINVAL, "OPAL_FLAG_PAIR_CREATION keeps the positrons in the ion slot: a run with ions cannot use it");
+    if (!c->full) return fail(c, OPAL_EINVAL, "pair creation needs the full particle state");
+    c->z_star = 1.0; c->mass_number = 9.109383e-31 / 1.672622e-27;          // a positron: charge +e, mass m_e (constants.rs)
+    for (int sp = 0; sp < 2; sp++) {
+        if (c->bk[sp].allocated) continue;
+        std::vector<long long> demand(c->g.nx, 0);
+        if (!alloc_buckets(c, c->bk[sp], demand, true)) return false;
+    }
+    const int want = std::max(1 << 16, c->ph[0].cap / 8);                     // a photon that finds no room converts a step later
+    if (want > c->pair_cap) {
+        for (int k = 0; k < 2; k++) { if (c->d_pair[k]) cudaFree(c->d_pair[k]); c->d_pair[k] = nullptr; CUB(cudaMalloc(&c->d_pair[k], (size_t)want * sizeof(opal_migrant))); }
+        c->pair_cap = want;
+    }
+    if (!c->d_pair_n) CUB(cudaMalloc(&c->d_pair_n, sizeof(int)));
+    return true;
+}
+
+bool insert_pairs(opal_ctx* c) {
+    int n = 0;
+    CUB(cudaMemcpyAsync(&n, c->d_pair_n, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CUB(cudaStreamSynchronize(c->stream));
+    n = std::min(n, c->pair_cap);
+    if (n == 0) return true;
+    c->pairs_created += n;
+    CUB(cudaMemcpyAsync(c->d_pair_n, &n, sizeof(int), cudaMemcpyHostToDevice, c->stream));      // (clamped: what the scatter reads)
+    for (int sp = 0; sp < 2; sp++) {
+        CUB(cudaMemsetAsync(&c->d_status->n_overflow, 0, sizeof(int), c->stream));
+        StepParams sp_ = sparams(c, sp);
+        sp_.route_left = sp_.route_right = 0;
+        c->k.scatter(c->stream, c->g, bdev(c, sp), sp_, true, false, c->d_pair[sp], c->d_pair_n, c->pair_cap, 0, nullptr, nullptr, nullptr,
+                     reinterpret_cast<int*>(c->d_overflow), c->d_status);
+        c->launches++;
+        if (!fetch_status(c)) return false;
+        if (!handle_overflow(c, sp, false)) return false;
+        c->bk[sp].n_hint += n;
+        c->edge_bound[sp][0] = c->edge_bound[sp][1] = -1;
+    }
+    return true;
+}
+
 bool advance_photons(opal_ctx* c, bool check) {
     if (c->flags & OPAL_FLAG_IMMOBILE_PHOTONS) return true;
     if (c->ph[0].cap == 0) { c->last_gone[2][0] = c->last_gone[2][1] = 0; return true; }
@@ -746,9 +791,17 @@ bool advance_photons(opal_ctx* c, bool check) {
     if (!reset_status(c, true)) return false;
     const int src = c->ph_cur, dst = 1 - src;
     CUB(cudaMemsetAsync(c->ph[dst].d_n, 0, sizeof(int), c->stream));
-    c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status);
+    PairDev pairs;
+    if (c->flags & OPAL_FLAG_PAIR_CREATION) {
+        if (!prepare_pairs(c)) return false;
+        pairs.e_recs = c->d_pair[0]; pairs.p_recs = c->d_pair[1]; pairs.n = c->d_pair_n; pairs.cap = c->pair_cap;
+        pairs.seed = c->seed; pairs.call = c->pair_calls++;
+        CUB(cudaMemsetAsync(c->d_pair_n, 0, sizeof(int), c->stream));
+    }
+    c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status, pairs);
     c->launches++;
     c->ph_cur = dst;
+    if (pairs.n && !insert_pairs(c)) return false;
     if (remote(c) && !exchange_migrants(c, OPAL_PHOTON, false)) return false;
     if (check) {
         if (!fetch_status(c)) return false;
@@ -879,7 +932,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
     if (c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) {
         const int src = c->ph_cur, dst = 1 - src;
         k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n);
-        c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status);
+        c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status, PairDev());
         c->k.burst_mark(c->stream, c->d_status, 1, PH_PHOTONS);
         c->ph_cur = dst;
         n += 3;
@@ -1041,7 +1094,7 @@ opal_status opal_destroy(opal_ctx* c) {
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
     void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
-                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n};
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n, c->d_pair[0], c->d_pair[1], c->d_pair_n};
     for (void* p : frees) if (p) cudaFree(p);
     for (int sp = 0; sp < 2; sp++) {
         for (int k = 0; k < 2; k++) { if (c->lean[sp].d_strips[k]) cudaFree(c->lean[sp].d_strips[k]); if (c->lean[sp].d_scount[k]) cudaFree(c->lean[sp].d_scount[k]); }
@@ -1066,6 +1119,8 @@ opal_status opal_grid_shape(opal_ctx* c, int64_t* total, int64_t* l, int64_t* r)
 
 opal_status opal_set_ion(opal_ctx* c, double z_star, double a) {
     CHECK_CTX(c);
+    if (c->flags & OPAL_FLAG_PAIR_CREATION) return (opal_status)(fail(c, OPAL_EINVAL, "OPAL_FLAG_PAIR_CREATION keeps the positrons in the ion slot: a run with ions cannot use it"), c->status);
+    c->ion_slot_is_user = true;
     c->z_star = z_star; c->mass_number = a;
     return OPAL_OK;
 }
@@ -1486,7 +1541,7 @@ opal_status opal_field_advance(opal_ctx* c) {
 // One iteration of main.rs:238-267 the ordinary way (status read back after every advance), from phase `from` on: the
 // whole step for from == PH_ELECTRONS; the rest of a step a graph-replayed burst left half-finished otherwise.
 static bool run_phases(opal_ctx* c, const StepCfg& cfg, int from, double t, double ly, double lz, bool want_ke) {
-    const bool fused = cfg.fused() && !c->absorb_on;
+    const bool fused = cfg.fused() && !c->absorb_on && !(c->flags & OPAL_FLAG_PAIR_CREATION);   // (leptons born mid-step are deposited by the separate pass)
     if (from <= PH_ELECTRONS) {
         if (cfg.dep) { c->k.clear(c->stream, c->g); c->launches++; }
         if (!advance_charged(c, OPAL_ELECTRON, fused, true, want_ke)) return false;
@@ -1525,7 +1580,7 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     // Launch- and sync-bound decks: replay the step as a CUDA graph (all but the last one or two steps, which also sum the
     // kinetic energy and report the leaver counts).  Everything a single slab does in a step is covered -- fused or separate
     // deposit, photons, emission; absorption, remote neighbours and per-kernel timing take the ordinary path.
-    const bool burst_ok = !remote(c) && !c->timing && !c->absorb_on && env_ll("OPAL_BURST", 1) != 0 &&
+    const bool burst_ok = !remote(c) && !c->timing && !c->absorb_on && !(c->flags & OPAL_FLAG_PAIR_CREATION) && env_ll("OPAL_BURST", 1) != 0 &&
                           (long long)c->bk[0].n_hint + c->bk[1].n_hint <= env_ll("OPAL_BURST_MAX_PARTICLES", 20000000);
     while (burst_ok && nsteps - s0 >= 6 && c->status == OPAL_OK) {
         if (cfg.emit && c->bk[OPAL_ELECTRON].allocated) {
@@ -1747,6 +1802,39 @@ opal_status opal_qed_sample(int64_t n, const double* chi, const double* gamma, c
     cudaFree(d_o); cudaFree(d_t); cudaFree(d_st);
     if (e != cudaSuccess) return OPAL_ECUDA;
     return (st.err & ERR_CHI) ? OPAL_ECHI_RANGE : OPAL_OK;
+}
+
+opal_status opal_bw_rate(int64_t n, const double* chi, double* out) {
+    if (n < 0 || (n > 0 && (!chi || !out))) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    double *d_c = nullptr, *d_o = nullptr;
+    const size_t b = (size_t)n * sizeof(double);
+    if (cudaMalloc(&d_c, b) != cudaSuccess || cudaMalloc(&d_o, b) != cudaSuccess) return OPAL_ECUDA;
+    cudaMemcpy(d_c, chi, b, cudaMemcpyHostToDevice);
+    fast::table().bw_rate(0, (int)n, d_c, d_o);
+    const cudaError_t e = cudaMemcpy(out, d_o, b, cudaMemcpyDeviceToHost);
+    cudaFree(d_c); cudaFree(d_o);
+    return e == cudaSuccess ? OPAL_OK : OPAL_ECUDA;
+}
+
+opal_status opal_bw_sample(int64_t n, const double* chi, const double* r1, const double* r2, double* out) {
+    if (n < 0 || (n > 0 && (!chi || !r1 || !r2 || !out))) return OPAL_EINVAL;
+    if (n == 0) return OPAL_OK;
+    const size_t b = (size_t)n * sizeof(double);
+    double* d[4] = {nullptr, nullptr, nullptr, nullptr};
+    const double* h[3] = {chi, r1, r2};
+    for (int k = 0; k < 4; k++) if (cudaMalloc(&d[k], b) != cudaSuccess) return OPAL_ECUDA;
+    for (int k = 0; k < 3; k++) cudaMemcpy(d[k], h[k], b, cudaMemcpyHostToDevice);
+    fast::table().bw_sample(0, (int)n, d[0], d[1], d[2], d[3]);
+    const cudaError_t e = cudaMemcpy(out, d[3], b, cudaMemcpyDeviceToHost);
+    for (int k = 0; k < 4; k++) cudaFree(d[k]);
+    return e == cudaSuccess ? OPAL_OK : OPAL_ECUDA;
+}
+
+opal_status opal_pairs_created(opal_ctx* c, int64_t* n) {
+    if (!c || !n) return OPAL_EINVAL;
+    *n = c->pairs_created;
+    return OPAL_OK;
 }
 
 opal_status opal_fields_at(opal_ctx* c, int64_t n, const int64_t* cell, const double* xi, double* out6) {

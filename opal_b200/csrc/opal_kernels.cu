@@ -328,12 +328,57 @@ __global__ void __launch_bounds__(BLOCK) k_deposit(GridDev g, BucketDev b) {
 }
 
 // ============================================================================================
+// EXTENSION (OPAL_FLAG_PAIR_CREATION; no counterpart in the reference -- parity unpinned): nonlinear Breit-Wheeler pair
+// creation.  W = alpha_f F(chi) / (tau_C k0); dW/df and F from tools/gen_bw_tables.py (Baier-Katkov / Ritus).
+// ============================================================================================
+#include "bw_tables.inc"
+__constant__ double c_bw_ln_f[BW_NCHI] = BW_LN_F_INIT;
+__constant__ double c_bw_cdf[BW_NCHI][BW_NF] = BW_CDF_INIT;
+
+// F(chi) = chi T(chi): tabulated for 0.05 <= chi <= 500, its asymptotes outside
+__device__ double bw_big_f(double chi) {
+    if (!(chi > 0.0)) return 0.0;
+    const double lc = log(chi);
+    if (lc < BW_LN_CHI0) return 0.22963966338592295 * chi * exp(-8.0 / (3.0 * chi));          // 3 sqrt(3) / (16 sqrt(2)) chi e^(-8/3chi)
+    const double idx = (lc - BW_LN_CHI0) / BW_DLN_CHI;
+    if (idx >= (double)(BW_NCHI - 1)) return exp(c_bw_ln_f[BW_NCHI - 1] + (2.0 / 3.0) * (lc - (BW_LN_CHI0 + (BW_NCHI - 1) * BW_DLN_CHI)));   // ~ chi^(2/3)
+    const int i = (int)idx;
+    const double w = idx - (double)i;
+    return exp((1.0 - w) * c_bw_ln_f[i] + w * c_bw_ln_f[i + 1]);
+}
+// the electron's share f in (0, 1/2] of the photon energy with P(f' < f) = r at the table's chi node `row`
+__device__ double bw_invert_row(int row, double r) {
+    int j = 0;
+    while (j < BW_NF - 2 && c_bw_cdf[row][j + 1] <= r) j++;
+    const double lo = c_bw_cdf[row][j], hi = c_bw_cdf[row][j + 1];
+    const double frac = hi > lo ? (r - lo) / (hi - lo) : 0.5;
+    return ((double)j + fmin(fmax(frac, 0.0), 1.0)) / (2.0 * (BW_NF - 1));
+}
+// f in (0, 1): r1 picks the share below 1/2 (interpolated between the two neighbouring chi nodes), r2 which lepton gets it
+__device__ double bw_sample_f(double chi, double r1, double r2) {
+    double idx = (log(chi) - BW_LN_CHI0) / BW_DLN_CHI;
+    idx = fmin(fmax(idx, 0.0), (double)(BW_NCHI - 1) - 1.0e-9);
+    const int i = (int)idx;
+    const double w = idx - (double)i;
+    const double f = (1.0 - w) * bw_invert_row(i, r1) + w * bw_invert_row(i + 1, r1);
+    return r2 < 0.5 ? f : 1.0 - f;
+}
+__global__ void k_bw_rate(int n, const double* chi, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = bw_big_f(chi[i]);
+}
+__global__ void k_bw_sample(int n, const double* chi, const double* r1, const double* r2, double* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = bw_sample_f(chi[i], r1[i], r2[i]);
+}
+
+// ============================================================================================
 // Photons: flat explicit-cell store (they are never deposited, so no bucketing is needed);
 // push = photon.rs:150-183, out-of-place with warp-aggregated compaction of survivors.
 // ============================================================================================
 __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, PhotonDev dst, StepParams sp,
                                                       opal_migrant* __restrict__ out_l, opal_migrant* __restrict__ out_r,
-                                                      StatusDev* __restrict__ st) {
+                                                      StatusDev* __restrict__ st, PairDev pr) {
     if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
     const int n = *src.n;
     const int lane = threadIdx.x & 31;
@@ -376,6 +421,30 @@ __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, P
                         (side == 0 ? out_l : out_r)[r] = m;
                     } else atomicOr(&st->err, ERR_CAPACITY);
                 }
+            }
+        }
+        if (pr.n && keep) {
+            // ---- Breit-Wheeler (extension): the optical depth against pair creation runs down; at zero the photon becomes a pair ----
+            const double k0 = sqrt(dot(p.k, p.k));
+            tau -= (OPAL_ALPHA_FINE / OPAL_COMPTON_TIME) * bw_big_f(p.chi) / k0 * g.dt;
+            if (tau < 0.0) {
+                const int slot = atomicAdd(pr.n, 1);
+                if (slot < pr.cap) {
+                    double r1, r2, r3, r4;
+                    philox_uniform2(pr.seed, (uint64_t)i, pr.call, 20u, r1, r2);
+                    philox_uniform2(pr.seed, (uint64_t)i, pr.call, 21u, r3, r4);
+                    const double f = bw_sample_f(p.chi, r1, r2);
+                    const V3 ue = f * p.k, up = p.k - ue;                       // momentum is conserved exactly: u_e + u_p = k
+                    opal_migrant m;
+                    m.cell = cell; m.x = p.x; m.prev_x = p.x; m.weight = p.w; m.chi = 0.0; m.work = 0.0; m.y = p.y; m.z = p.z;
+                    m.birth_time = 0.0; m.pad[1] = 0.0;
+                    m.u[0] = ue.x; m.u[1] = ue.y; m.u[2] = ue.z; m.gamma = sqrt(1.0 + dot(ue, ue)); m.tau = -log1p(-r3); m.pad[0] = 0.0;
+                    pr.e_recs[slot] = m;
+                    const double up2 = dot(up, up), gm1 = up2 / (1.0 + sqrt(1.0 + up2));                 // ion.rs:83-85
+                    m.u[0] = up.x; m.u[1] = up.y; m.u[2] = up.z; m.gamma = 1.0 + gm1; m.pad[0] = gm1; m.tau = CUDART_INF; (void)r4;
+                    pr.p_recs[slot] = m;
+                    keep = false;
+                }                                                               // (no room left this call: the photon converts next step)
             }
         }
         const unsigned mk = __ballot_sync(FULLMASK, keep);
@@ -1242,11 +1311,11 @@ static void l_deposit(cudaStream_t s, const GridDev& g, const BucketDev& b, cons
 }
 
 static void l_photon_push(cudaStream_t s, const GridDev& g, const PhotonDev& src, const PhotonDev& dst, const StepParams& sp,
-                          opal_migrant* out_l, opal_migrant* out_r, StatusDev* st) {
+                          opal_migrant* out_l, opal_migrant* out_r, StatusDev* st, const PairDev& pairs) {
     int grid = (src.cap + 255) / 256;
     if (grid > 148 * 8) grid = 148 * 8;
     if (grid < 1) grid = 1;
-    k_photon_push<<<grid, 256, 0, s>>>(g, src, dst, sp, out_l, out_r, st);
+    k_photon_push<<<grid, 256, 0, s>>>(g, src, dst, sp, out_l, out_r, st, pairs);
 }
 static void l_photon_insert(cudaStream_t s, const PhotonDev& dst, const opal_migrant* recs, const int* n_recs, int n_max,
                             long long cell_shift, StatusDev* st) {
@@ -1339,6 +1408,10 @@ static void l_qed_sample(cudaStream_t s, int n, const double* tables, const doub
     cudaFuncSetAttribute(k_qed_sample, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);      // per device: see l_emit
     k_qed_sample<<<(n + 127) / 128, 128, smem, s>>>(n, tables, chi, gamma, r1, r2, r3, classical, out3, st);
 }
+static void l_bw_rate(cudaStream_t s, int n, const double* chi, double* out) { k_bw_rate<<<(n + 127) / 128, 128, 0, s>>>(n, chi, out); }
+static void l_bw_sample(cudaStream_t s, int n, const double* chi, const double* r1, const double* r2, double* out) {
+    k_bw_sample<<<(n + 127) / 128, 128, 0, s>>>(n, chi, r1, r2, out);
+}
 static void l_fields_at(cudaStream_t s, const GridDev& g, int n, const long long* cell, const double* xi, double* out6, StatusDev* st) {
     k_fields_at<<<(n + 127) / 128, 128, 0, s>>>(g, n, cell, xi, out6, st);
 }
@@ -1360,7 +1433,7 @@ KernelTable table() {
     t.push = l_push; t.flush = l_flush; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
     t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
-    t.fields_at = l_fields_at; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
+    t.fields_at = l_fields_at; t.bw_rate = l_bw_rate; t.bw_sample = l_bw_sample; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
     return t;
 }
 

@@ -57,6 +57,14 @@ struct PhotonDev {
     double* f[NF_PHOTON];
 };
 
+// Breit-Wheeler pair creation inside the photon push (OPAL_FLAG_PAIR_CREATION): pair k of a call is e_recs[k] + p_recs[k]
+struct PairDev {
+    opal_migrant* e_recs = nullptr; opal_migrant* p_recs = nullptr;
+    int* n = nullptr;            // pairs created by this call (null: pair creation off); may run past cap -- then the photon waits a step
+    int cap = 0;
+    uint64_t seed = 0; unsigned call = 0;
+};
+
 // device-side counters / sticky error bits, mirrored to pinned host memory after each step
 struct StatusDev {
     int n_movers;        // records in the mover buffer
@@ -119,7 +127,7 @@ struct KernelTable {
                     opal_migrant* outbox_l, opal_migrant* outbox_r, int* overflow_idx, StatusDev* st);
     void (*deposit)(cudaStream_t, const GridDev&, const BucketDev&, const StepParams&, StatusDev* st);
     void (*photon_push)(cudaStream_t, const GridDev&, const PhotonDev& src, const PhotonDev& dst, const StepParams&,
-                        opal_migrant* outbox_l, opal_migrant* outbox_r, StatusDev* st);
+                        opal_migrant* outbox_l, opal_migrant* outbox_r, StatusDev* st, const PairDev& pairs);
     void (*photon_insert)(cudaStream_t, const PhotonDev& dst, const opal_migrant* recs, const int* n_recs, int n_max,
                           long long cell_shift, StatusDev* st);
     void (*emit)(cudaStream_t, const GridDev&, const BucketDev& electrons, const PhotonDev& photons, const StepParams&,
@@ -139,6 +147,8 @@ struct KernelTable {
     void (*qed_rate)(cudaStream_t, int n, const double* chi, const double* gamma, double* out);
     void (*qed_sample)(cudaStream_t, int n, const double* qed_tables, const double* chi, const double* gamma, const double* r1,
                        const double* r2, const double* r3, int classical, double* out3, StatusDev* st);
+    void (*bw_rate)(cudaStream_t, int n, const double* chi, double* out);                 // F(chi) of the pair-creation extension
+    void (*bw_sample)(cudaStream_t, int n, const double* chi, const double* r1, const double* r2, double* out);
     void (*fields_at)(cudaStream_t, const GridDev&, int n, const long long* cell, const double* xi, double* out6, StatusDev* st);
     void (*copy_buckets)(cudaStream_t, const BucketDev& src, const BucketDev& dst, bool full);
     // sizing of the mover buffer: out2[0] += particles whose ballistic step x + v_x dt/dx leaves [0,1),

@@ -102,6 +102,11 @@ int run(const Options& opt, Ranks& ranks) {
 
     const bool photon_emission = input.read_bool("qed", "photon_emission");         // main.rs:78-79
     const bool photon_absorption = input.read_bool("qed", "photon_absorption");
+    // EXTENSION (not in the reference's schema; absent == false): qed.pair_creation -- nonlinear Breit-Wheeler pair creation,
+    // OPAL_FLAG_PAIR_CREATION of include/opal_b200.h.  Positrons take the ion slot and are written out as species "positron"
+    // with the electrons' output list; a deck with ions cannot switch it on.
+    bool pair_creation = false;
+    optional_read([&] { pair_creation = input.read_bool("qed", "pair_creation"); });
     double photon_energy_min = 0.0, photon_angle_max = 0.0, max_formation_length = 0.0;
     const bool has_emin = optional_read([&] { photon_energy_min = 1.0e-6 * input.read_f64("qed", "photon_energy_min") / constants::ELEMENTARY_CHARGE; });
     const bool has_amax = optional_read([&] { photon_angle_max = input.read_f64("qed", "photon_angle_max"); });
@@ -141,11 +146,13 @@ int run(const Options& opt, Ranks& ranks) {
     }
     if (opt.lean && !lean_ok) throw std::runtime_error("--lean: this deck needs the full particle state (QED on, deposition off, or r/work/chi outputs)");
     const bool lean = opt.lean || (lean_ok && !opt.full);
-    const uint32_t flags = lean ? OPAL_FLAG_LEAN_STATE : 0u;
+    if (pair_creation && !(photon_emission || photon_absorption)) throw std::runtime_error("qed.pair_creation needs photons (qed.photon_emission or qed.photon_absorption)");
+    const uint32_t flags = (lean ? OPAL_FLAG_LEAN_STATE : 0u) | (pair_creation ? OPAL_FLAG_PAIR_CREATION : 0u);
     opal_ctx* ctx = nullptr;
     const int device = opt.device >= 0 ? opt.device + id : id;
     ck(OPAL_FN(create)(&ctx, device, (int64_t)my_nx, my_xmin, dx, dt, left_bdy, right_bdy, id, np, (uint64_t)id + opt.seed, flags), nullptr, "opal_create");
     ranks.connect(ctx);                                                             // NCCL ring (np > 1)
+    if (pair_creation && np > 1 && ranks.host_staged()) throw std::runtime_error("qed.pair_creation with several ranks needs the library's NCCL exchange");
     const bool staged = ranks.host_staged();                                        // no communicator in the library (ranks.h)
     if (staged && lean) {                                                           // a lean context takes opal_run_steps only
         OPAL_FN(destroy)(ctx);
@@ -168,6 +175,7 @@ int run(const Options& opt, Ranks& ranks) {
     const size_t ipc = input.read_usize("ions", "npc");
     std::vector<std::string> iospec;
     std::string ion_name;
+    if (ipc > 0 && pair_creation) throw std::runtime_error("qed.pair_creation keeps the positrons in the ion slot: set ions.npc to 0");
     if (ipc > 0) {
         iospec = input.read_strings("ions", "output");
         ion_name = input.read_string("ions", "name");
@@ -216,11 +224,13 @@ int run(const Options& opt, Ranks& ranks) {
         write_grid(ctx, output_dir, index, ranks);
         write_population(ctx, OPAL_ELECTRON, "electron", eospec, output_dir, index, ranks);
         if (ipc > 0) write_population(ctx, OPAL_ION, ion_name, iospec, output_dir, index, ranks);
+        if (pair_creation) write_population(ctx, OPAL_ION, "positron", eospec, output_dir, index, ranks);
         if (photons_on) write_population(ctx, OPAL_PHOTON, "photon", pospec, output_dir, index, ranks);
         write_energies(ctx, output_dir, index, ranks);
         if (opt.dump) {
             dump_species(ctx, OPAL_ELECTRON, "electron", output_dir, index, id);
             if (ipc > 0) dump_species(ctx, OPAL_ION, ion_name.c_str(), output_dir, index, id);
+            if (pair_creation) dump_species(ctx, OPAL_ION, "positron", output_dir, index, id);
             if (photons_on) dump_species(ctx, OPAL_PHOTON, "photon", output_dir, index, id);
         }
     };

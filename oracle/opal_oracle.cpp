@@ -1168,6 +1168,7 @@ opal_status opal_ref_particles_upload(opal_ctx* g, int species, int64_t n, const
 }
 opal_status opal_ref_set_ion(opal_ctx* g, double z_star, double a) {
     CHECK_CTX(g);
+    if (g->flags & OPAL_FLAG_PAIR_CREATION) { g->status = OPAL_EINVAL; g->err = "OPAL_FLAG_PAIR_CREATION keeps the positrons in the ion slot"; return OPAL_EINVAL; }
     g->ion_spec.Z_star = z_star; g->ion_spec.A = a;
     for (auto& p : g->ions.store) { p.Z_star = z_star; p.Z = z_star; p.A = a; }   // main.rs:145-147
     return OPAL_OK;
@@ -1227,11 +1228,77 @@ opal_status opal_ref_fields_download(opal_ctx* g, double* cells11) {
     return OPAL_OK;
 }
 
+// ---- EXTENSION (OPAL_FLAG_PAIR_CREATION): nonlinear Breit-Wheeler pair creation ------------------------------------------
+// Nothing in the reference implements it (only the unused Photon.tau, photon.rs:27,126-132): PARITY UNPINNED.  This is a CPU
+// statement of the same published rate the CUDA kernel uses (tables: tools/gen_bw_tables.py), written on its own, so that the
+// two can be compared statistically; single slab only.
+namespace bw {
+#include "../opal_b200/csrc/bw_tables.inc"
+static const double LN_F[BW_NCHI] = BW_LN_F_INIT;
+static const double CDF[BW_NCHI][BW_NF] = BW_CDF_INIT;
+double big_f(double chi) {
+    if (!(chi > 0.0)) return 0.0;
+    const double lc = std::log(chi), lc_max = BW_LN_CHI0 + (BW_NCHI - 1) * BW_DLN_CHI;
+    if (lc < BW_LN_CHI0) return 3.0 * std::sqrt(3.0) / (16.0 * std::sqrt(2.0)) * chi * std::exp(-8.0 / (3.0 * chi));
+    if (lc >= lc_max) return std::exp(LN_F[BW_NCHI - 1] + 2.0 * (lc - lc_max) / 3.0);
+    const double pos = (lc - BW_LN_CHI0) / BW_DLN_CHI;
+    const int i = (int)std::floor(pos);
+    const double w = pos - i;
+    return std::exp(LN_F[i] + w * (LN_F[i + 1] - LN_F[i]));
+}
+double invert(const double* cdf, double r) {            // f in [0, 1/2] with P(f' < f) = r on one chi node
+    int j = 0;
+    for (; j < BW_NF - 2; j++) if (cdf[j + 1] > r) break;
+    const double span = cdf[j + 1] - cdf[j];
+    double frac = span > 0.0 ? (r - cdf[j]) / span : 0.5;
+    frac = std::min(std::max(frac, 0.0), 1.0);
+    return (j + frac) * 0.5 / (BW_NF - 1);
+}
+double sample_f(double chi, double r1, double r2) {
+    double pos = (std::log(chi) - BW_LN_CHI0) / BW_DLN_CHI;
+    pos = std::min(std::max(pos, 0.0), (double)(BW_NCHI - 1) - 1.0e-9);
+    const int i = (int)pos;
+    const double w = pos - i;
+    const double f = (1.0 - w) * invert(CDF[i], r1) + w * invert(CDF[i + 1], r1);
+    return r2 < 0.5 ? f : 1.0 - f;
+}
+}  // namespace bw
+
+static void create_pairs(opal_ctx* g) {
+    if (g->nranks != 1) { if (g->status == OPAL_OK) { g->status = OPAL_EINVAL; g->err = "oracle: pair creation is restated for a single slab only"; } return; }
+    finalize(g, g->electrons); finalize(g, g->ions); finalize(g, g->photons);
+    g->ion_spec.Z_star = 1.0; g->ion_spec.A = ELECTRON_MASS / PROTON_MASS;     // positrons in the ion slot (include/opal_b200.h)
+    std::vector<Photon> keep;
+    keep.reserve(g->photons.store.size());
+    bool any = false;
+    for (Photon& ph : g->photons.store) {
+        const double k0 = std::sqrt(norm_sqr(ph.k));
+        ph.tau[0] -= ALPHA_FINE / COMPTON_TIME * bw::big_f(ph.chi) / k0 * g->dt;
+        if (ph.tau[0] >= 0.0) { keep.push_back(ph); continue; }
+        const double f = bw::sample_f(ph.chi, g->rng.gen(), g->rng.gen());
+        const Vec3 ue = f * ph.k, up = ph.k - ue;
+        Electron e = electron_create(ph.cell, ph.x, ue, ph.weight, g->dx, 0.0);    // dt = 0: prev_x = x (born at rest in the cell frame of this step)
+        e.y = ph.y; e.z = ph.z; e.tau = g->rng.exp1();
+        Ion pos = ion_create(ph.cell, ph.x, up, ph.weight, g->dx, 0.0);
+        pos.Z_star = 1.0; pos.Z = 1.0; pos.A = g->ion_spec.A;
+        g->electrons.store.push_back(e);
+        g->ions.store.push_back(pos);
+        any = true;
+    }
+    if (!any) return;
+    g->photons.store.swap(keep);
+    std::stable_sort(g->electrons.store.begin(), g->electrons.store.end(), [](const Electron& a, const Electron& b) { return a.cell < b.cell; });
+    std::stable_sort(g->ions.store.begin(), g->ions.store.end(), [](const Ion& a, const Ion& b) { return a.cell < b.cell; });
+}
+
 opal_status opal_ref_advance(opal_ctx* g, int species) {
     CHECK_CTX(g);
     if (species == OPAL_ELECTRON) advance(g, g->electrons);
     else if (species == OPAL_ION) advance(g, g->ions);
-    else if (species == OPAL_PHOTON) { if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons); }
+    else if (species == OPAL_PHOTON) {
+        if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons);
+        if (g->flags & OPAL_FLAG_PAIR_CREATION) create_pairs(g);
+    }
     else return OPAL_EINVAL;
     return (opal_status)g->status;
 }
@@ -1351,6 +1418,7 @@ opal_status opal_ref_run_steps(opal_ctx* g, int64_t nsteps, double t0, const dou
         advance(g, g->electrons);
         advance(g, g->ions);
         if (!(g->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) advance(g, g->photons);
+        if (g->flags & OPAL_FLAG_PAIR_CREATION) create_pairs(g);               // extension, off by default
         if (g->absorb_on)                                                       // main.rs:246-248
             absorb(g, t, std::isnan(g->absorb_max_displacement) ? nullptr : &g->absorb_max_displacement,
                    std::isnan(g->absorb_stop_time) ? nullptr : &g->absorb_stop_time);
@@ -1582,6 +1650,22 @@ uint64_t opal_ref_table_checksum(void) {
 }
 uint64_t opal_ref_table_checksum_expected(void) { return OPAL_QED_TABLE_FNV1A; }
 // xoshiro256** stream for tests (seed_from_u64 -> n x gen::<f64>())
+opal_status opal_ref_bw_rate(int64_t n, const double* chi, double* out) {
+    if (n < 0 || (n > 0 && (!chi || !out))) return OPAL_EINVAL;
+    for (int64_t i = 0; i < n; i++) out[i] = bw::big_f(chi[i]);
+    return OPAL_OK;
+}
+opal_status opal_ref_bw_sample(int64_t n, const double* chi, const double* r1, const double* r2, double* out) {
+    if (n < 0 || (n > 0 && (!chi || !r1 || !r2 || !out))) return OPAL_EINVAL;
+    for (int64_t i = 0; i < n; i++) out[i] = bw::sample_f(chi[i], r1[i], r2[i]);
+    return OPAL_OK;
+}
+opal_status opal_ref_pairs_created(opal_ctx* g, int64_t* n) {
+    if (!g || !n) return OPAL_EINVAL;
+    *n = 0;
+    for (const Ion& p : g->ions.store) if (p.A < 0.01) (*n)++;          // positrons: the only "ions" lighter than a proton
+    return OPAL_OK;
+}
 void opal_ref_rng_stream(uint64_t seed, int64_t n, double* out) {
     Xoshiro r; r.seed_from_u64(seed);
     for (int64_t i = 0; i < n; i++) out[i] = r.gen();
