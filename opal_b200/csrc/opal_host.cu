@@ -138,6 +138,7 @@ struct opal_ctx {
                                      // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
+    unsigned* d_gridbar = nullptr;   // k_grid_step's grid-wide barrier: arrival count, generation
     double* d_qed_tables = nullptr;
     int64_t last_gone[3][2] = {{0, 0}, {0, 0}, {0, 0}};
     uint64_t emit_calls = 0;
@@ -908,12 +909,14 @@ struct StepCfg {
 };
 enum { PH_ELECTRONS = 0, PH_IONS = 1, PH_PHOTONS = 2, PH_ABSORB = 3, PH_EMIT_ROOM = 4, PH_EMIT = 5, PH_DEPOSIT = 6, PH_GRID = 7 };
 
-void enqueue_species(opal_ctx* c, int sp, bool fused) {     // advance_charged without the host in the loop (local slab)
+// begin_marked: the kernel before (k_clear) has zeroed the per-advance counters already; defer_check: the kernel after
+// (k_grid_step) looks at the overflow / error state itself
+int enqueue_species(opal_ctx* c, int sp, bool fused, bool begin_marked, bool defer_check) {     // advance_charged without the host in the loop (local slab)
     Buckets& B = c->bk[sp];
-    if (!B.allocated) return;
+    if (!B.allocated) return 0;
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
-    c->k.burst_mark(c->stream, c->d_status, 0, sp);
+    if (!begin_marked) c->k.burst_mark(c->stream, c->d_status, 0, sp);
     if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->d_eq_n);
     opal_ctx::Lean& L = c->lean[sp];
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
@@ -922,13 +925,19 @@ void enqueue_species(opal_ctx* c, int sp, bool fused) {     // advance_charged w
     if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
     c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status);
-    c->k.burst_mark(c->stream, c->d_status, 1, sp);
+    if (!defer_check) c->k.burst_mark(c->stream, c->d_status, 1, sp);
+    return 2 + (begin_marked ? 0 : 1) + (defer_check ? 0 : 1);
 }
 
 int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // one iteration of main.rs:238-267; returns the launch count
     int n = 0;
-    if (cfg.dep) { c->k.clear(c->stream, c->g); n++; }
-    for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { enqueue_species(c, sp, cfg.fused()); n += 4; }
+    const int first_sp = c->bk[0].allocated ? 0 : (c->bk[1].allocated ? 1 : -1), last_sp = c->bk[1].allocated ? 1 : (c->bk[0].allocated ? 0 : -1);
+    const bool photons_move = c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS);
+    // nothing between the last particle advance and the grid's share of the step: one launch does its check, halo + BCs, the
+    // field update and the step counter (k_grid_step)
+    const bool one_grid_launch = cfg.fused() && !photons_move && !cfg.emit && last_sp >= 0 && env_ll("OPAL_GRID_FUSED", 1) != 0;
+    if (cfg.dep) { c->k.clear(c->stream, c->g, first_sp >= 0 ? c->d_status : nullptr); n++; }
+    for (int sp = 0; sp < 2; sp++) n += enqueue_species(c, sp, cfg.fused(), cfg.dep && sp == first_sp, one_grid_launch && sp == last_sp);
     if (c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) {
         const int src = c->ph_cur, dst = 1 - src;
         k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n);
@@ -948,6 +957,14 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
     }
     if (cfg.dep && !cfg.fused()) {
         for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { c->k.deposit(c->stream, c->g, bdev(c, sp), sparams(c, sp), c->d_status); n++; }
+    }
+    if (one_grid_launch) {
+        GridDev nxt = c->g;
+        nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
+        c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar);
+        c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
+        c->g = nxt;
+        return n + 1;
     }
     c->k.sync_bc(c->stream, c->g, nullptr, 0.0, 0.0, nullptr);
     do_field(c);
@@ -1063,6 +1080,8 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     CU(cudaMalloc(&c->d_energy, 8 * sizeof(double)));
     CU(cudaMallocHost(&c->h_energy, 8 * sizeof(double)));
     CU(cudaMalloc(&c->d_tmp_int, 8 * sizeof(int)));
+    CU(cudaMalloc(&c->d_gridbar, 2 * sizeof(unsigned)));
+    CU(cudaMemsetAsync(c->d_gridbar, 0, 2 * sizeof(unsigned), c->stream));
     c->out_cap = c->in_cap = (int)env_ll("OPAL_EXCHANGE_CAP", 4096);      // initial sizes: both grow on demand
     for (int s = 0; s < 2; s++) {
         CU(cudaMalloc(&c->d_out[s], (size_t)(c->out_cap + 1) * sizeof(opal_migrant)));
@@ -1094,7 +1113,7 @@ opal_status opal_destroy(opal_ctx* c) {
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
     void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
-                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n, c->d_pair[0], c->d_pair[1], c->d_pair_n};
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n, c->d_pair[0], c->d_pair[1], c->d_pair_n, c->d_gridbar};
     for (void* p : frees) if (p) cudaFree(p);
     for (int sp = 0; sp < 2; sp++) {
         for (int k = 0; k < 2; k++) { if (c->lean[sp].d_strips[k]) cudaFree(c->lean[sp].d_strips[k]); if (c->lean[sp].d_scount[k]) cudaFree(c->lean[sp].d_scount[k]); }
@@ -1485,7 +1504,7 @@ opal_status opal_photon_pair_depths(opal_ctx* c, int set, int64_t n, double* tau
 
 opal_status opal_clear(opal_ctx* c) {
     CHECK_CTX(c);
-    c->k.clear(c->stream, c->g); c->launches++;
+    c->k.clear(c->stream, c->g, nullptr); c->launches++;
     return OPAL_OK;
 }
 
@@ -1543,7 +1562,7 @@ opal_status opal_field_advance(opal_ctx* c) {
 static bool run_phases(opal_ctx* c, const StepCfg& cfg, int from, double t, double ly, double lz, bool want_ke) {
     const bool fused = cfg.fused() && !c->absorb_on && !(c->flags & OPAL_FLAG_PAIR_CREATION);   // (leptons born mid-step are deposited by the separate pass)
     if (from <= PH_ELECTRONS) {
-        if (cfg.dep) { c->k.clear(c->stream, c->g); c->launches++; }
+        if (cfg.dep) { c->k.clear(c->stream, c->g, nullptr); c->launches++; }
         if (!advance_charged(c, OPAL_ELECTRON, fused, true, want_ke)) return false;
     }
     if (from <= PH_IONS && !advance_charged(c, OPAL_ION, fused, true)) return false;

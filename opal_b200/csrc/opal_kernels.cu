@@ -894,9 +894,8 @@ __global__ void k_fields_at(GridDev g, int n, const long long* cell, const doubl
 __device__ __forceinline__ double cell_x(const GridDev& g, int c) { return g.xmin + ((double)c - (double)g.left) * g.dx; }   // yee.rs:296
 
 // one block.  halo_recv: [2][8][11] cells received from the left / right neighbour (remote case).
-__global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __restrict__ halo_recv, double laser_y, double laser_z,
-                                                  const double* __restrict__ laser_dev) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+__device__ __forceinline__ void sync_bc_body(const GridDev& g, const double* __restrict__ halo_recv, double laser_y, double laser_z,
+                                             const double* __restrict__ laser_dev) {       // one block of 256 threads
     __shared__ double s_send[2][OPAL_HALO_CELLS][10];   // copies of my first / last 8 cells (yee.rs:353-354)
     const int G = OPAL_GHOST_SIZE;
     double* arr[10] = {g.rho, g.jx, g.jy, g.jz, g.ex, g.ey, g.ez, g.bx, g.by, g.bz};
@@ -955,16 +954,20 @@ __global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __rest
 
 // Conducting mirror reads cell[start].{ey,ez,bx} (i = 1) which thread 0 does not modify, and
 // cell[start - i] for i >= 1 which nobody writes: no intra-kernel hazard.
+__global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __restrict__ halo_recv, double laser_y, double laser_z,
+                                                  const double* __restrict__ laser_dev) {
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    sync_bc_body(g, halo_recv, laser_y, laser_z, laser_dev);
+}
 
 constexpr int FT = 256;   // field tile
 // B += dt/2, E += dt (Silver-Mueller on cell 0), B += dt/2 in ONE pass: each block recomputes the
 // one-cell halo it needs (identical arithmetic to the owning block) and writes its tile to the
 // other buffer of the E/B ping-pong, so no block ever reads a value another block has updated.
-__global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+__device__ __forceinline__ void field_tile(const GridDev& g, const GridDev& o, const int t0) {     // FT threads
     __shared__ double s_ey[FT + 3], s_ez[FT + 3], s_by[FT + 2], s_bz[FT + 2];
-    const int t0 = blockIdx.x * FT;
     const int tid = threadIdx.x;
+    __syncthreads();                                      // (a block that walks several tiles re-uses the staging arrays)
     const int len = g.len;
     const double hdt = 0.5 * g.dt;
     // stage E (t0-1 .. t0+FT+1) and B (t0-1 .. t0+FT)
@@ -1021,10 +1024,49 @@ __global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
         }
     }
 }
-
-__global__ void k_clear(GridDev g) {   // yee.rs:543-549
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.len; i += gridDim.x * blockDim.x) {
+__global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
     if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    field_tile(g, o, blockIdx.x * FT);
+}
+
+// The grid's share of a step in ONE launch (graph-replayed bursts on a single slab): the check of the
+// last particle advance (bucket overflow / assert -> halt), halo overlay + boundary conditions (yee.rs:351-496, block 0),
+// a grid-wide barrier, B/2 - E - B/2 (yee.rs:345-349) over the tiles, and the step counter.  At most 148 blocks of FT
+// threads with < 9 KB of shared memory each: all resident at once, so the spin barrier cannot starve (it still gives up
+// after ~1 s and raises ERR_INDEX rather than hang the device).
+__global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDev* st, int last_species, unsigned* bar /* count, generation */) {
+    if (*(volatile const int*)&st->halt) return;
+    if (st->n_overflow > 0 || st->err) {                  // the same for every block: nobody advances the fields
+        if (blockIdx.x == 0 && threadIdx.x == 0) { st->halt_species = last_species; __threadfence(); st->halt = 1; }
+        return;
+    }
+    if (blockIdx.x == 0) { sync_bc_body(g, nullptr, 0.0, 0.0, nullptr); __threadfence(); }
+    __syncthreads();
+    if (gridDim.x > 1) {
+        if (threadIdx.x == 0) {
+            const unsigned gen = *(volatile unsigned*)(bar + 1);
+            if (atomicAdd(bar, 1u) == gridDim.x - 1) { *(volatile unsigned*)bar = 0u; __threadfence(); atomicAdd(bar + 1, 1u); }
+            else {
+                long long spins = 0;
+                while (*(volatile unsigned*)(bar + 1) == gen) if (++spins > (1ll << 28)) { atomicOr(&st->err, ERR_INDEX); break; }
+            }
+            __threadfence();
+        }
+        __syncthreads();
+    }
+    for (int t0 = blockIdx.x * FT; t0 < g.len; t0 += gridDim.x * FT) field_tile(g, o, t0);
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->step = st->step + 1;     // (read only by the kernels of the next step)
+}
+
+// st != null (bursts): also the begin-mark of the species advance that follows (per-advance counters, mover segment counters)
+__global__ void k_clear(GridDev g, StatusDev* st) {   // yee.rs:543-549
+    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (st && blockIdx.x == 0) {
+        int* seg = reinterpret_cast<int*>(st + 1);
+        for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) seg[i] = 0;
+        if (threadIdx.x == 0) { st->n_movers = 0; st->n_overflow = 0; st->n_out[0] = st->n_out[1] = 0; st->gone[0] = st->gone[1] = 0; st->n_new_photons = 0; }
+    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.len; i += gridDim.x * blockDim.x) {
         g.rho[i] = 0.0; g.jx[i] = 0.0; g.jy[i] = 0.0; g.jz[i] = 0.0;
     }
 }
@@ -1358,10 +1400,15 @@ static void l_sync_bc(cudaStream_t s, const GridDev& g, const double* halo_recv,
 static void l_field(cudaStream_t s, const GridDev& cur, const GridDev& nxt, bool) {
     k_field<<<(cur.len + FT - 1) / FT, FT, 0, s>>>(cur, nxt);
 }
-static void l_clear(cudaStream_t s, const GridDev& g) {
+static void l_clear(cudaStream_t s, const GridDev& g, StatusDev* st_begin_mark) {
     int grid = (g.len + 255) / 256;
     if (grid > 148 * 8) grid = 148 * 8;
-    k_clear<<<grid, 256, 0, s>>>(g);
+    k_clear<<<grid, 256, 0, s>>>(g, st_begin_mark);
+}
+static void l_grid_step(cudaStream_t s, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* bar) {
+    int grid = (cur.len + FT - 1) / FT;
+    if (grid > 148) grid = 148;
+    k_grid_step<<<grid, FT, 0, s>>>(cur, nxt, st, last_species, bar);
 }
 static void l_halo_pack(cudaStream_t s, const GridDev& g, double* out) { k_halo_pack<<<1, 192, 0, s>>>(g, out); }
 
@@ -1431,7 +1478,7 @@ KernelTable table() {
     KernelTable t;
     t.crossing_estimate = l_crossing_estimate;
     t.push = l_push; t.flush = l_flush; t.scatter = l_scatter; t.deposit = l_deposit; t.photon_push = l_photon_push; t.photon_insert = l_photon_insert;
-    t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
+    t.emit = l_emit; t.sync_bc = l_sync_bc; t.field = l_field; t.grid_step = l_grid_step; t.clear = l_clear; t.halo_pack = l_halo_pack; t.energy = l_energy;
     t.generate = l_generate; t.gather_out = l_gather_out; t.qed_rate = l_qed_rate; t.qed_sample = l_qed_sample;
     t.fields_at = l_fields_at; t.bw_rate = l_bw_rate; t.bw_sample = l_bw_sample; t.copy_buckets = l_copy_buckets; t.compact_cells = l_compact_cells; t.burst_mark = l_burst_mark;
     return t;

@@ -136,7 +136,9 @@ struct KernelTable {
     void (*sync_bc)(cudaStream_t, const GridDev&, const double* halo_recv /*2 x 8 x 11 or null*/, double laser_y, double laser_z,
                     const double* laser_dev /*2 doubles or null*/);
     void (*field)(cudaStream_t, const GridDev& cur, const GridDev& nxt, bool zero_next_j);
-    void (*clear)(cudaStream_t, const GridDev&);
+    void (*clear)(cudaStream_t, const GridDev&, StatusDev* begin_mark /* bursts: also zero the per-advance counters; else null */);
+    // bursts on one slab: check of the last advance + halo/BC + field update + step counter in one launch (k_grid_step)
+    void (*grid_step)(cudaStream_t, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* barrier2);
     void (*halo_pack)(cudaStream_t, const GridDev&, double* out2x8x11);
     void (*energy)(cudaStream_t, const GridDev&, const BucketDev* electrons, const BucketDev* ions, const PhotonDev* photons,
                    bool full, double* out4);
