@@ -916,7 +916,7 @@ int enqueue_species(opal_ctx* c, int sp, bool fused, bool begin_marked, bool def
     if (!B.allocated) return 0;
     c->adv_calls[sp]++;
     StepParams p = sparams(c, sp);
-    if (!begin_marked) c->k.burst_mark(c->stream, c->d_status, 0, sp);
+    if (!begin_marked) c->k.burst_mark(c->stream, c->d_status, 0, sp, c->mover_seg_cap);
     if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->d_eq_n);
     opal_ctx::Lean& L = c->lean[sp];
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
@@ -925,7 +925,7 @@ int enqueue_species(opal_ctx* c, int sp, bool fused, bool begin_marked, bool def
     if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
     c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                  reinterpret_cast<int*>(c->d_overflow), c->d_status);
-    if (!defer_check) c->k.burst_mark(c->stream, c->d_status, 1, sp);
+    if (!defer_check) c->k.burst_mark(c->stream, c->d_status, 1, sp, c->mover_seg_cap);
     return 2 + (begin_marked ? 0 : 1) + (defer_check ? 0 : 1);
 }
 
@@ -942,7 +942,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
         const int src = c->ph_cur, dst = 1 - src;
         k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n);
         c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status, PairDev());
-        c->k.burst_mark(c->stream, c->d_status, 1, PH_PHOTONS);
+        c->k.burst_mark(c->stream, c->d_status, 1, PH_PHOTONS, 1 << 30);
         c->ph_cur = dst;
         n += 3;
     }
@@ -952,7 +952,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
         // t and the call index of step k come from the device-side step counter (GridDev::step / laser_arr[3k + 2])
         c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, 0.0, cfg.f3[0], cfg.f3[1], cfg.f3[2],
                   c->seed, emit_call0, c->d_status);
-        c->k.burst_mark(c->stream, c->d_status, 1, PH_EMIT);
+        c->k.burst_mark(c->stream, c->d_status, 1, PH_EMIT, 1 << 30);
         n += 3;
     }
     if (cfg.dep && !cfg.fused()) {
@@ -961,7 +961,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
     if (one_grid_launch) {
         GridDev nxt = c->g;
         nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
-        c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar);
+        c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar, c->mover_seg_cap);
         c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
         c->g = nxt;
         return n + 1;
@@ -969,7 +969,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // on
     c->k.sync_bc(c->stream, c->g, nullptr, 0.0, 0.0, nullptr);
     do_field(c);
     c->launches--;                               // (do_field counted itself; the burst accounts launches per replay)
-    c->k.burst_mark(c->stream, c->d_status, 2, 0);
+    c->k.burst_mark(c->stream, c->d_status, 2, 0, 0);
     return n + 3;
 }
 
@@ -1014,7 +1014,7 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
         }
         if (!ok) break;
         c->launches += batch * per_step;
-        if (cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
+        if (cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
             cudaStreamSynchronize(c->stream) != cudaSuccess) { ok = fail(c, OPAL_ECUDA, "burst status read-back failed"); break; }
         *done = c->h_status->step;
         if (c->h_status->halt) { *halted = true; break; }
@@ -1623,6 +1623,7 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
         if (hphase == PH_ELECTRONS || hphase == PH_IONS) {        // a bucket overflowed: re-lay out, re-insert the parked movers
             c->last_gone[hphase][0] = c->h_status->gone[0]; c->last_gone[hphase][1] = c->h_status->gone[1];
             if (!handle_overflow(c, hphase, cfg.fused())) break;
+            if (!grow_movers_after(c)) break;                     // (a mover segment more than half full halts a burst too)
         } else if (hphase == PH_EMIT_ROOM) {                      // the photon store is full: do_emit (the next phase) grows it
             resume = PH_EMIT;
         }

@@ -1029,14 +1029,24 @@ __global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
     field_tile(g, o, blockIdx.x * FT);
 }
 
+// bursts: is a mover segment more than half full?  (block-wide; every thread of the block must call it)
+__device__ __forceinline__ bool segments_filling(const StatusDev* st, int mover_cap, int tid, int nthreads) {
+    const int* seg = reinterpret_cast<const int*>(st + 1);
+    bool any = false;
+    for (int i = tid; i < OPAL_MOVER_SEGMENTS; i += nthreads) any |= 2 * seg[i] > mover_cap;
+    return __syncthreads_or(any);
+}
+
 // The grid's share of a step in ONE launch (graph-replayed bursts on a single slab): the check of the
 // last particle advance (bucket overflow / assert -> halt), halo overlay + boundary conditions (yee.rs:351-496, block 0),
 // a grid-wide barrier, B/2 - E - B/2 (yee.rs:345-349) over the tiles, and the step counter.  At most 148 blocks of FT
 // threads with < 9 KB of shared memory each: all resident at once, so the spin barrier cannot starve (it still gives up
 // after ~1 s and raises ERR_INDEX rather than hang the device).
-__global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDev* st, int last_species, unsigned* bar /* count, generation */) {
+__global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDev* st, int last_species, unsigned* bar /* count, generation */,
+                                                  int mover_cap) {
     if (*(volatile const int*)&st->halt) return;
-    if (st->n_overflow > 0 || st->err) {                  // the same for every block: nobody advances the fields
+    const bool filling = segments_filling(st, mover_cap, threadIdx.x, blockDim.x);
+    if (st->n_overflow > 0 || st->err || filling) {       // the same for every block: nobody advances the fields
         if (blockIdx.x == 0 && threadIdx.x == 0) { st->halt_species = last_species; __threadfence(); st->halt = 1; }
         return;
     }
@@ -1380,19 +1390,22 @@ static void l_emit(cudaStream_t s, const GridDev& g, const BucketDev& e, const P
 
 // burst-mode bookkeeping (one block): what == 0 zero the per-advance counters and the mover segment counters,
 // 1 raise halt when the advance of `species` parked movers or tripped an assert, 2 count the completed step
-__global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, int species) {
+// (mover_cap: room per mover segment.  A segment more than half full also halts the burst -- without an error -- so that the
+//  host doubles the buffer before a later step overflows it, as the ordinary path does after every advance)
+__global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, int species, int mover_cap) {
     if (*(volatile int*)&st->halt) return;
     if (what == 0) {
         int* seg = reinterpret_cast<int*>(st + 1);
         for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) seg[i] = 0;
         if (threadIdx.x == 0) { st->n_movers = 0; st->n_overflow = 0; st->n_out[0] = st->n_out[1] = 0; st->gone[0] = st->gone[1] = 0; st->n_new_photons = 0; }
     } else if (what == 1) {
-        if (threadIdx.x == 0 && (st->n_overflow > 0 || st->err)) { st->halt_species = species; __threadfence(); st->halt = 1; }
+        const bool filling = segments_filling(st, mover_cap, threadIdx.x, blockDim.x);
+        if (threadIdx.x == 0 && (st->n_overflow > 0 || st->err || filling)) { st->halt_species = species; __threadfence(); st->halt = 1; }
     } else if (threadIdx.x == 0) {
         st->step = st->step + 1;
     }
 }
-static void l_burst_mark(cudaStream_t s, StatusDev* st, int what, int species) { k_burst_mark<<<1, what == 0 ? 1024 : 32, 0, s>>>(st, what, species); }
+static void l_burst_mark(cudaStream_t s, StatusDev* st, int what, int species, int mover_cap) { k_burst_mark<<<1, what == 2 ? 32 : 1024, 0, s>>>(st, what, species, mover_cap); }
 
 static void l_sync_bc(cudaStream_t s, const GridDev& g, const double* halo_recv, double ly, double lz, const double* laser_dev) {
     k_sync_bc<<<1, 256, 0, s>>>(g, halo_recv, ly, lz, laser_dev);
@@ -1405,10 +1418,10 @@ static void l_clear(cudaStream_t s, const GridDev& g, StatusDev* st_begin_mark) 
     if (grid > 148 * 8) grid = 148 * 8;
     k_clear<<<grid, 256, 0, s>>>(g, st_begin_mark);
 }
-static void l_grid_step(cudaStream_t s, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* bar) {
+static void l_grid_step(cudaStream_t s, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* bar, int mover_cap) {
     int grid = (cur.len + FT - 1) / FT;
     if (grid > 148) grid = 148;
-    k_grid_step<<<grid, FT, 0, s>>>(cur, nxt, st, last_species, bar);
+    k_grid_step<<<grid, FT, 0, s>>>(cur, nxt, st, last_species, bar, mover_cap);
 }
 static void l_halo_pack(cudaStream_t s, const GridDev& g, double* out) { k_halo_pack<<<1, 192, 0, s>>>(g, out); }
 

@@ -138,7 +138,7 @@ struct KernelTable {
     void (*field)(cudaStream_t, const GridDev& cur, const GridDev& nxt, bool zero_next_j);
     void (*clear)(cudaStream_t, const GridDev&, StatusDev* begin_mark /* bursts: also zero the per-advance counters; else null */);
     // bursts on one slab: check of the last advance + halo/BC + field update + step counter in one launch (k_grid_step)
-    void (*grid_step)(cudaStream_t, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* barrier2);
+    void (*grid_step)(cudaStream_t, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* barrier2, int mover_cap);
     void (*halo_pack)(cudaStream_t, const GridDev&, double* out2x8x11);
     void (*energy)(cudaStream_t, const GridDev&, const BucketDev* electrons, const BucketDev* ions, const PhotonDev* photons,
                    bool full, double* out4);
@@ -159,7 +159,7 @@ struct KernelTable {
     // lean layout: close the free slots the strip kernel leaves inside the buckets
     void (*compact_cells)(cudaStream_t, const BucketDev&, int* hcount);
     // burst mode bookkeeping kernels: 0 begin (zero the per-advance counters), 1 check (raise halt on overflow / error), 2 end (step++)
-    void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species);
+    void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species, int mover_cap);
 };
 
 namespace fast { KernelTable table(); }

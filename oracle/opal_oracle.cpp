@@ -420,7 +420,7 @@ void qed_sample(double chi, double gamma, double rand1, double rand2, double ran
 
 // ---- Airy Ai for x >= 0 (qed/special_functions/airy.rs:19-69, Series::evaluate_up_to mod.rs:29-35) -----
 // Pinned by the reference's known answers Ai(0), Ai(2), Ai(17), Ai(20) at 1e-12 and None beyond 50 (airy.rs:77-112).
-#include "airy_tables.h"
+#include "../opal_b200/csrc/airy_tables.h"   // generated data (tools/gen_airy_tables.py): one copy, shared like qed_tables.inc
 constexpr double CLASSICAL_ELECTRON_RADIUS = 2.817940e-15;   // constants.rs:28
 constexpr double AIRY_SCALE = 0.262183997088323;             // the 15-digit literal of airy.rs:40
 inline double powi(double a, int b) {     // f64::powi = llvm.powi = compiler-rt's __powidf2: square-and-multiply from the low bit
