@@ -549,13 +549,6 @@ __global__ void k_header_to_int(const opal_migrant* in, int* n) { if (threadIdx.
 __global__ void k_burst_zero_int(const StatusDev* st, int* p) {
     if (threadIdx.x == 0 && !*(volatile const int*)&st->halt) *p = 0;
 }
-// burst mode: before k_emit, is there room for one photon per electron (electron.rs:208-251)?  If not: halt, the host grows the store
-// (eq_n: the emitter list's count when the push kept one -- then the exact number of photons this step can add)
-__global__ void k_burst_photon_room(StatusDev* st, const int* ph_n, int cap, long long need, const int* eq_n, int eq_cap, int phase) {
-    if (threadIdx.x != 0 || *(volatile int*)&st->halt) return;
-    if (eq_n) { const int q = *eq_n; if (q >= 0 && q <= eq_cap) need = q; }
-    if ((long long)*ph_n + need > (long long)cap) { st->halt_species = phase; __threadfence(); st->halt = 1; }
-}
 // live particles of a species: sum of count[] (out must be zeroed)
 __global__ void __launch_bounds__(256) k_total_count(const int* __restrict__ count, int ncell, unsigned long long* out) {
     unsigned long long acc = 0;
@@ -829,7 +822,7 @@ bool do_emit(opal_ctx* c, double t, double min_e, double max_a, double max_fl) {
     E.n_hint = (long long)live;
     if (!ensure_photons(c, (long long)nph + (long long)live + c->out_cap)) return false;
     c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, t, min_e, max_a, max_fl,
-              c->seed, c->emit_calls++, c->d_status);
+              c->seed, c->emit_calls++, c->d_status, 0, 0);
     c->launches++;
     CUB(cudaGetLastError());
     return fetch_status(c);
@@ -909,68 +902,76 @@ struct StepCfg {
 };
 enum { PH_ELECTRONS = 0, PH_IONS = 1, PH_PHOTONS = 2, PH_ABSORB = 3, PH_EMIT_ROOM = 4, PH_EMIT = 5, PH_DEPOSIT = 6, PH_GRID = 7 };
 
-// begin_marked: the kernel before (k_clear) has zeroed the per-advance counters already; defer_check: the kernel after
-// (k_grid_step) looks at the overflow / error state itself
-int enqueue_species(opal_ctx* c, int sp, bool fused, bool begin_marked, bool defer_check) {     // advance_charged without the host in the loop (local slab)
-    Buckets& B = c->bk[sp];
-    if (!B.allocated) return 0;
-    c->adv_calls[sp]++;
-    StepParams p = sparams(c, sp);
-    if (!begin_marked) c->k.burst_mark(c->stream, c->d_status, 0, sp, c->mover_seg_cap);
-    if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->d_eq_n);
-    opal_ctx::Lean& L = c->lean[sp];
-    LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
-    const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
-                                  c->d_overflow, c->d_status, nullptr);
-    if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
-    c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, fused, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
-                 reinterpret_cast<int*>(c->d_overflow), c->d_status);
-    if (!defer_check) c->k.burst_mark(c->stream, c->d_status, 1, sp, c->mover_seg_cap);
-    return 2 + (begin_marked ? 0 : 1) + (defer_check ? 0 : 1);
-}
-
-int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {   // one iteration of main.rs:238-267; returns the launch count
+// One iteration of main.rs:238-267 without the host in the loop (one slab), as few launches as the phases allow: the check
+// of an advance (parked movers, asserts, mover segments filling up) rides on the next kernel of the step (GridDev::prev_phase)
+// or shares a launch with the next species' begin-mark (burst_mark 3); the begin-mark of the first species rides on k_clear.
+// Returns the launch count.
+int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
     int n = 0;
-    const int first_sp = c->bk[0].allocated ? 0 : (c->bk[1].allocated ? 1 : -1), last_sp = c->bk[1].allocated ? 1 : (c->bk[0].allocated ? 0 : -1);
+    int pend = -1;                                   // the phase whose check has not been done yet
+    const int last_sp = c->bk[1].allocated ? 1 : (c->bk[0].allocated ? 0 : -1);
     const bool photons_move = c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS);
+    const bool emit = cfg.emit && c->bk[OPAL_ELECTRON].allocated;
     // nothing between the last particle advance and the grid's share of the step: one launch does its check, halo + BCs, the
     // field update and the step counter (k_grid_step)
-    const bool one_grid_launch = cfg.fused() && !photons_move && !cfg.emit && last_sp >= 0 && env_ll("OPAL_GRID_FUSED", 1) != 0;
-    if (cfg.dep) { c->k.clear(c->stream, c->g, first_sp >= 0 ? c->d_status : nullptr); n++; }
-    for (int sp = 0; sp < 2; sp++) n += enqueue_species(c, sp, cfg.fused(), cfg.dep && sp == first_sp, one_grid_launch && sp == last_sp);
-    if (c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS)) {
-        const int src = c->ph_cur, dst = 1 - src;
-        k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n);
-        c->k.photon_push(c->stream, c->g, pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status, PairDev());
-        c->k.burst_mark(c->stream, c->d_status, 1, PH_PHOTONS, 1 << 30);
-        c->ph_cur = dst;
-        n += 3;
+    const bool one_grid_launch = cfg.fused() && !photons_move && !emit && last_sp >= 0 && env_ll("OPAL_GRID_FUSED", 1) != 0;
+    int* const eq_n = (c->eq_on && c->d_eq_n) ? c->d_eq_n : nullptr;
+    int* ph_dst_n = photons_move ? c->ph[1 - c->ph_cur].d_n : nullptr;      // emptied by the first begin-mark of the step
+    auto gdev = [&](int prev_phase, int count_step) { GridDev g = c->g; g.prev_phase = prev_phase; g.count_step = count_step; g.seg_cap = c->mover_seg_cap; return g; };
+    bool cleared_with_mark = false;
+    if (cfg.dep) { c->k.clear(c->stream, c->g, last_sp >= 0 ? c->d_status : nullptr); n++; cleared_with_mark = last_sp >= 0; }
+    for (int sp = 0; sp < 2; sp++) {
+        Buckets& B = c->bk[sp];
+        if (!B.allocated) continue;
+        c->adv_calls[sp]++;
+        StepParams p = sparams(c, sp);
+        int* za = sp == OPAL_ELECTRON ? eq_n : nullptr;
+        if (pend >= 0) { c->k.burst_mark(c->stream, c->d_status, 3, pend, c->mover_seg_cap, za, ph_dst_n); ph_dst_n = nullptr; n++; }
+        else if (cleared_with_mark) {
+            cleared_with_mark = false;
+            if (za) { k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, za); n++; }
+        } else { c->k.burst_mark(c->stream, c->d_status, 0, sp, c->mover_seg_cap, za, ph_dst_n); ph_dst_n = nullptr; n++; }
+        opal_ctx::Lean& L = c->lean[sp];
+        LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
+        const bool strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, cfg.fused(), c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                                      c->d_overflow, c->d_status, nullptr);
+        if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }
+        c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, cfg.fused(), c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
+                     reinterpret_cast<int*>(c->d_overflow), c->d_status);
+        n += 2;
+        pend = sp;
     }
-    if (cfg.emit && c->bk[OPAL_ELECTRON].allocated) {
-        k_burst_photon_room<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[c->ph_cur].d_n, c->ph[c->ph_cur].cap, c->bk[OPAL_ELECTRON].n_hint,
-                                                     c->eq_on ? c->d_eq_n : nullptr, c->eq_cap, PH_EMIT_ROOM);
+    if (photons_move) {
+        const int src = c->ph_cur, dst = 1 - src;
+        if (ph_dst_n) { k_burst_zero_int<<<1, 32, 0, c->stream>>>(c->d_status, c->ph[dst].d_n); n++; }      // (no begin-mark took it along)
+        c->k.photon_push(c->stream, gdev(pend, 0), pdev(c, src), pdev(c, dst), sparams(c, OPAL_PHOTON), c->d_out[0] + 1, c->d_out[1] + 1, c->d_status, PairDev());
+        c->ph_cur = dst;
+        n++;
+        pend = PH_PHOTONS;
+    }
+    if (emit) {
         // t and the call index of step k come from the device-side step counter (GridDev::step / laser_arr[3k + 2])
-        c->k.emit(c->stream, c->g, bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, 0.0, cfg.f3[0], cfg.f3[1], cfg.f3[2],
-                  c->seed, emit_call0, c->d_status);
-        c->k.burst_mark(c->stream, c->d_status, 1, PH_EMIT, 1 << 30);
-        n += 3;
+        c->k.emit(c->stream, gdev(pend, 0), bdev(c, OPAL_ELECTRON), pdev(c, c->ph_cur), sparams(c, OPAL_ELECTRON), c->d_qed_tables, 0.0, cfg.f3[0], cfg.f3[1], cfg.f3[2],
+                  c->seed, emit_call0, c->d_status, std::max<long long>(c->bk[OPAL_ELECTRON].n_hint, 1), PH_EMIT_ROOM);
+        n++;
+        pend = PH_EMIT;
     }
     if (cfg.dep && !cfg.fused()) {
-        for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { c->k.deposit(c->stream, c->g, bdev(c, sp), sparams(c, sp), c->d_status); n++; }
+        for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated) { c->k.deposit(c->stream, gdev(pend, 0), bdev(c, sp), sparams(c, sp), c->d_status); pend = -1; n++; }
     }
+    GridDev nxt = c->g;
+    nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
     if (one_grid_launch) {
-        GridDev nxt = c->g;
-        nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
         c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar, c->mover_seg_cap);
-        c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
-        c->g = nxt;
-        return n + 1;
+        n++;
+    } else {
+        c->k.sync_bc(c->stream, gdev(pend, 0), nullptr, 0.0, 0.0, nullptr);
+        c->k.field(c->stream, gdev(-1, 1), nxt, false);
+        n += 2;
     }
-    c->k.sync_bc(c->stream, c->g, nullptr, 0.0, 0.0, nullptr);
-    do_field(c);
-    c->launches--;                               // (do_field counted itself; the burst accounts launches per replay)
-    c->k.burst_mark(c->stream, c->d_status, 2, 0, 0);
-    return n + 3;
+    c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
+    c->g = nxt;
+    return n;
 }
 
 // Runs up to n (even) steps from laser_y/z[0..n) as graph replays.  *done = steps completed; *halted tells whether the
@@ -989,8 +990,8 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     CUB(cudaMemcpyAsync(c->d_laser, lh.data(), lh.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CUB(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
     CUB(cudaStreamSynchronize(c->stream));
-    c->g.halt = &c->d_status->halt; c->g.step = &c->d_status->step; c->g.laser_arr = c->d_laser;
-    auto leave = [&]() { c->g.halt = nullptr; c->g.step = nullptr; c->g.laser_arr = nullptr; };
+    c->g.halt = &c->d_status->halt; c->g.step = &c->d_status->step; c->g.laser_arr = c->d_laser; c->g.bst = c->d_status;
+    auto leave = [&]() { c->g.halt = nullptr; c->g.step = nullptr; c->g.laser_arr = nullptr; c->g.bst = nullptr; c->g.prev_phase = -1; c->g.count_step = 0; };
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int per_step = 0;
@@ -1059,6 +1060,7 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     GridDev& g = c->g;
     g.nx = (int)nx; g.xmin = xmin; g.dx = dx; g.dt = dt; g.self_nbr = nranks == 1;
+    g.halt = nullptr; g.step = nullptr; g.laser_arr = nullptr; g.bst = nullptr; g.prev_phase = -1; g.count_step = 0; g.seg_cap = 0;
     // yee.rs:278-292
     if (rank == 0 && left == OPAL_BDY_LASER) { g.left_bdy = OPAL_BDY_LASER; g.left = OPAL_LASER_BDY_SIZE; }
     else { g.left_bdy = OPAL_BDY_INTERNAL; g.left = OPAL_GHOST_SIZE; }

@@ -37,6 +37,29 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
+// Bursts (graph-replayed steps): may this kernel run?  No if an earlier kernel raised the halt; no, too, if the advance of
+// phase g.prev_phase parked movers or tripped an assert -- then this kernel raises the halt in that phase's name (what a
+// k_burst_mark launch of its own used to do).  Every thread gets the same answer: n_overflow is written by the charged
+// species' push / scatter only, and an assert is fatal anyway.
+__device__ __forceinline__ bool burst_blocked(const GridDev& g) {
+    if (!g.halt) return false;
+    if (*(volatile const int*)g.halt) return true;
+    StatusDev* const st = g.bst;
+    if (st && g.prev_phase >= 0) {
+        bool filling = false;                                      // a mover segment more than half full (block-wide vote)
+        if (g.prev_phase <= 1) {                                   // (only a charged species' advance fills segments)
+            const int* seg = reinterpret_cast<const int*>(st + 1);
+            for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) filling |= 2 * seg[i] > g.seg_cap;
+            filling = __syncthreads_or(filling);
+        }
+        if (st->n_overflow > 0 || st->err || filling) {
+            if (blockIdx.x == 0 && threadIdx.x == 0) { st->halt_species = g.prev_phase; __threadfence(); *(volatile int*)&st->halt = 1; }
+            return true;
+        }
+    }
+    return false;
+}
+
 __device__ __forceinline__ void load_cell_fields(const GridDev& g, int j, CellFields& f) {
     // j = c + left_bdy_size; cells j-1 .. j+2 always exist (>= 4 ghost cells each side)
 #pragma unroll
@@ -289,7 +312,7 @@ __global__ void __launch_bounds__(256) k_scatter(GridDev g, BucketDev b, StepPar
 // ============================================================================================
 template <int SP>
 __global__ void __launch_bounds__(BLOCK) k_deposit(GridDev g, BucketDev b) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (burst_blocked(g)) return;                         // burst mode: an earlier kernel needs the host first
     const int lane = threadIdx.x & 31;
     const int warps_total = gridDim.x * WARPS_PER_BLOCK;
     const double q = species_charge(SP, b.z_star);
@@ -379,7 +402,7 @@ __global__ void k_bw_sample(int n, const double* chi, const double* r1, const do
 __global__ void __launch_bounds__(256) k_photon_push(GridDev g, PhotonDev src, PhotonDev dst, StepParams sp,
                                                       opal_migrant* __restrict__ out_l, opal_migrant* __restrict__ out_r,
                                                       StatusDev* __restrict__ st, PairDev pr) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (burst_blocked(g)) return;                         // burst mode: an earlier kernel needs the host first
     const int n = *src.n;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -784,13 +807,25 @@ constexpr int EMIT_QCAP = OPAL_EMIT_QCAP;
 // change its random numbers (keyed by slot); the order of the photon store is arbitrary as before.
 __global__ void __launch_bounds__(BLOCK, OPAL_EMIT_MB) k_emit(GridDev g, BucketDev b, PhotonDev ph, StepParams sp, const double* __restrict__ tables_g,
                                                     double t, double min_energy, double max_angle, double max_fl,
-                                                    uint64_t seed, uint64_t call_index, StatusDev* __restrict__ st) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+                                                    uint64_t seed, uint64_t call_index, StatusDev* __restrict__ st, long long room_need, int room_phase) {
+    if (burst_blocked(g)) return;                         // burst mode: an earlier kernel needs the host first
+    if (room_need > 0) {
+        // room for one photon per emitter (electron.rs:208-251)?  The emitter list, when valid, says exactly how many.
+        long long need = room_need;
+        if (b.eq_n) { const int q = *b.eq_n; if (q >= 0 && q <= b.eq_cap) need = q; }
+        if ((long long)*ph.n + need > (long long)ph.cap) {                                  // the same in every thread: k_emit has not appended yet
+            if (blockIdx.x == 0 && threadIdx.x == 0) { st->halt_species = room_phase; __threadfence(); *(volatile int*)&st->halt = 1; }
+            return;
+        }
+    }
     if (g.step) {                                         // burst mode: step k of the burst -> its time and its random-number call index
         const int k = *(volatile const int*)g.step;
         t = g.laser_arr[3 * k + 2];
         call_index += (uint64_t)k;
     }
+    const int qn = b.eq_n ? *b.eq_n : -1;
+    const bool listed = qn >= 0 && qn <= b.eq_cap;        // the push and the scatter of this step listed the emitters
+    if (listed && (long long)blockIdx.x * blockDim.x >= qn) return;      // nothing for this block (before the beam meets the pulse: for any block)
     extern __shared__ double s_tab[];
     long long* s_qs = reinterpret_cast<long long*>(s_tab + QED_TABLE_DOUBLES);
     int* s_qc = reinterpret_cast<int*>(s_qs + EMIT_QCAP);
@@ -802,9 +837,8 @@ __global__ void __launch_bounds__(BLOCK, OPAL_EMIT_MB) k_emit(GridDev g, BucketD
     const unsigned lt_mask = (1u << lane) - 1u;
     const int warps_total = gridDim.x * WARPS_PER_BLOCK;
     bool chi_err = false;
-    const int qn = b.eq_n ? *b.eq_n : -1;
-    if (qn >= 0 && qn <= b.eq_cap) {
-        // the push and the scatter of this step listed the emitters: sample exactly those, every lane busy
+    if (listed) {
+        // sample exactly the listed electrons, every lane busy
         const int n_round = (qn + 31) & ~31;
         for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n_round; j += gridDim.x * blockDim.x) {      // whole warps: emit_append votes
             bool store_photon = false;
@@ -956,7 +990,7 @@ __device__ __forceinline__ void sync_bc_body(const GridDev& g, const double* __r
 // cell[start - i] for i >= 1 which nobody writes: no intra-kernel hazard.
 __global__ void __launch_bounds__(256) k_sync_bc(GridDev g, const double* __restrict__ halo_recv, double laser_y, double laser_z,
                                                   const double* __restrict__ laser_dev) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (burst_blocked(g)) return;                         // burst mode: an earlier kernel needs the host first
     sync_bc_body(g, halo_recv, laser_y, laser_z, laser_dev);
 }
 
@@ -1025,8 +1059,9 @@ __device__ __forceinline__ void field_tile(const GridDev& g, const GridDev& o, c
     }
 }
 __global__ void __launch_bounds__(FT) k_field(GridDev g, GridDev o) {
-    if (g.halt && *(volatile const int*)g.halt) return;   // burst mode: an earlier kernel needs the host first
+    if (burst_blocked(g)) return;                         // burst mode: an earlier kernel needs the host first
     field_tile(g, o, blockIdx.x * FT);
+    if (g.bst && g.count_step && blockIdx.x == 0 && threadIdx.x == 0) g.bst->step = g.bst->step + 1;   // (read by the NEXT step's kernels only)
 }
 
 // bursts: is a mover segment more than half full?  (block-wide; every thread of the block must call it)
@@ -1379,22 +1414,33 @@ static void l_photon_insert(cudaStream_t s, const PhotonDev& dst, const opal_mig
 
 static void l_emit(cudaStream_t s, const GridDev& g, const BucketDev& e, const PhotonDev& ph, const StepParams& sp,
                    const double* tables, double t, double min_energy, double max_angle, double max_fl, uint64_t seed,
-                   uint64_t call_index, StatusDev* st) {
+                   uint64_t call_index, StatusDev* st, long long burst_room_need, int room_phase) {
     const int smem = QED_TABLE_DOUBLES * (int)sizeof(double) + EMIT_QCAP * (int)(sizeof(long long) + sizeof(int));
     // per DEVICE, and contexts may live on several devices of one process: set it on every launch (a cheap host-side call)
     cudaFuncSetAttribute(k_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     int grid = cell_grid(e.ncell);
     if (grid > 148 * OPAL_EMIT_MB) grid = 148 * OPAL_EMIT_MB;
-    k_emit<<<grid, BLOCK, smem, s>>>(g, e, ph, sp, tables, t, min_energy, max_angle, max_fl, seed, call_index, st);
+    k_emit<<<grid, BLOCK, smem, s>>>(g, e, ph, sp, tables, t, min_energy, max_angle, max_fl, seed, call_index, st, burst_room_need, room_phase);
 }
 
 // burst-mode bookkeeping (one block): what == 0 zero the per-advance counters and the mover segment counters,
 // 1 raise halt when the advance of `species` parked movers or tripped an assert, 2 count the completed step
 // (mover_cap: room per mover segment.  A segment more than half full also halts the burst -- without an error -- so that the
 //  host doubles the buffer before a later step overflows it, as the ordinary path does after every advance)
-__global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, int species, int mover_cap) {
+// what == 3: the check of `species` followed by the begin-mark of the next one, in one launch
+__global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, int species, int mover_cap, int* zero_a, int* zero_b) {
     if (*(volatile int*)&st->halt) return;
+    if (what == 3) {
+        const bool filling = segments_filling(st, mover_cap, threadIdx.x, blockDim.x);
+        if (st->n_overflow > 0 || st->err || filling) {
+            if (threadIdx.x == 0) { st->halt_species = species; __threadfence(); st->halt = 1; }
+            return;
+        }
+        __syncthreads();
+        what = 0;
+    }
     if (what == 0) {
+        if (threadIdx.x == 0) { if (zero_a) *zero_a = 0; if (zero_b) *zero_b = 0; }
         int* seg = reinterpret_cast<int*>(st + 1);
         for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) seg[i] = 0;
         if (threadIdx.x == 0) { st->n_movers = 0; st->n_overflow = 0; st->n_out[0] = st->n_out[1] = 0; st->gone[0] = st->gone[1] = 0; st->n_new_photons = 0; }
@@ -1405,7 +1451,9 @@ __global__ void __launch_bounds__(1024) k_burst_mark(StatusDev* st, int what, in
         st->step = st->step + 1;
     }
 }
-static void l_burst_mark(cudaStream_t s, StatusDev* st, int what, int species, int mover_cap) { k_burst_mark<<<1, what == 2 ? 32 : 1024, 0, s>>>(st, what, species, mover_cap); }
+static void l_burst_mark(cudaStream_t s, StatusDev* st, int what, int species, int mover_cap, int* zero_a, int* zero_b) {
+    k_burst_mark<<<1, what == 2 ? 32 : 1024, 0, s>>>(st, what, species, mover_cap, zero_a, zero_b);
+}
 
 static void l_sync_bc(cudaStream_t s, const GridDev& g, const double* halo_recv, double ly, double lz, const double* laser_dev) {
     k_sync_bc<<<1, 256, 0, s>>>(g, halo_recv, ly, lz, laser_dev);

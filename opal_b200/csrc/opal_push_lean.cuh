@@ -7,18 +7,21 @@
 //       Boris ion.rs:168-214) and written back TO THE SLOT THEY CAME FROM: x, u only -- w is never rewritten
 //       (72 B per particle-step: read 40, write 32; the cell index is implicit);
 //   (2) a resident that leaves the cell (|dxi| < 1 => cell +-1, electron.rs:313) is handed to this step's left / right
-//       mover strip of the cell (40-B records), its slot is marked free (x := NaN) and remembered in a free list;
+//       mover strip of the cell (48-B records: new offset, old offset, u, w), its slot is marked free (x := -1) and
+//       remembered in a free list;
 //   (3) the ARRIVALS -- the movers the two neighbour cells left in LAST step's strips -- are pushed by the same code
 //       and dropped into the free slots (the rest is appended behind the bucket): the cell hand-over of
 //       Population::advance (mod.rs:288-373) costs no separate pass over the buckets, and no kernel of its own;
-//   (4) deposit (yee.rs:551-641): stayers accumulate in registers (13 sums), movers -- a few per cent -- add the terms
-//       of their trajectory, in the frame of the cell they leave, to the same sums plus 8 private shared-memory columns; one shuffle
-//       reduction and <= 21 global atomics per CELL.
+//   (4) deposit (yee.rs:551-641): stayers accumulate in registers (13 sums) as they are pushed; the movers -- a few per
+//       cent -- are deposited at the end of the cell FROM THE STRIP JUST WRITTEN, every lane busy, in the frame of the
+//       cell they leave (8 more sums); one transposing shuffle reduction and <= 21 global atomics per CELL.
 // Strips are double-buffered by step parity (read last step's, write this step's).  Between steps a bucket holds its
 // residents plus a few free slots (count[c] counts slots in use; hcount[c] the free ones among them); the arrivals of
 // the last step wait in the strips.  Anything other than this kernel sees the buckets only after k_strip_flush +
-// k_compact_cells (host: ensure_settled).  A cell whose free slots exceed OPAL_HOLE_MAX shifts its live particles down
+// k_compact_cells (host: settle).  A cell whose free slots exceed OPAL_HOLE_MAX shifts its live particles down
 // itself (rare: arrivals fill the slots departures open; the excess random-walks).
+// At a slab edge: a leaver through an open boundary is dropped (mod.rs:372-373); towards a neighbour slab it goes
+// straight into the outbox (the receiver deposits it in its own frame); on a periodic single slab it is an ordinary mover.
 //
 // Arithmetic: the order-2 spline is evaluated through R(d), the fraction of the particle's triangle to the right of a
 // face at displacement d: W(node j) = R(j-1/2-x) - R(j+1/2-x), Cell::flux(x_i, x_f) = R(x_f) - R(x_i) (3e-16 against
@@ -26,11 +29,14 @@
 // q/dx are applied once per cell.  Results differ from the literal formulas by re-association only (<= 1e-15), far inside
 // the 1e-10 parity tolerance; the strict build keeps the literal code (k_push).
 //
-// Measured history (B200, 1e9 electrons / 1e6 cells, per step): round 1 shifted the stayers down over the movers' slots
-// (w rewritten behind a cell's first mover: 80.2 B/particle DRAM) and appended the arrivals in a second kernel (k_pull,
-// 0.56-1.0 ms); two hole-list variants built then lost to it (scattered read-modify-writes of the arrivals long after
-// the cell's sectors had left L2).  Consuming the strips inside the NEXT push, while the sectors stream through L2,
-// is what this file does; numbers in DESIGN.md section 4 and profiles/.
+// Measured history (B200, 1e9 electrons / 1e6 cells, per step; DESIGN.md section 4, profiles/): round 1 shifted the
+// stayers down over the movers' slots (w rewritten behind a cell's first mover: 80.2 B/particle DRAM) and appended the
+// arrivals in a second kernel (k_pull, 0.56-1.0 ms): 15.7 + 0.6 ms.  This kernel: 77.9 B/particle, 324 instructions per
+// 32 particles, 15.6 ms under the 1 kW power cap (1.6 GHz), 13.1 ms for one launch alone at the boost clock.  On the way:
+// movers deposited inside the divergent branch through atomicAdd(double) on shared memory (CAS spin loops in SASS): 25 ms;
+// through private shared-memory columns: 19.5 ms; an `if (live)` around the arithmetic instead of finite free-slot marks
+// and a masked weight: +40 instructions; 16 warps per SM at 124 registers instead of 18 at 94: 17.0 ms; bulk copies of
+// 256 B / 512 B / 768 B / 1 KB per stream and 2 to 6 ring stages: equal within noise beyond 3 stages.
 #pragma once
 
 #ifndef OPAL_PUSH_STAGES

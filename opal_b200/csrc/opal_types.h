@@ -19,6 +19,7 @@ enum { P_X = 0, P_PREVX, P_KX, P_KY, P_KZ, P_W, P_CHI, P_TAU, P_Y, P_Z, P_BIRTH,
        NF_PHOTON };
 
 // device-side view of the Yee grid: SoA over `len` cells (ghost/boundary zones included).
+struct StatusDev;
 struct GridDev {
     int len, left, right, nx;       // total cells, zone sizes, interior cells
     int left_bdy, right_bdy;        // resolved opal_boundary of this slab
@@ -32,6 +33,12 @@ struct GridDev {
     const int* halt;
     const int* step;
     const double* laser_arr;
+    // ... and, to keep a replayed step at a handful of launches, two chores ride on the step kernels themselves:
+    StatusDev* bst;                 // the status block (null outside a burst)
+    int prev_phase;                 // >= 0: before doing anything, look at what the advance of that phase left behind (parked movers, an
+                                    // assert) and raise the halt in its name -- the check a separate k_burst_mark launch would do
+    int count_step;                 // k_field: the step is complete, count it
+    int seg_cap;                    // room per mover segment: a segment more than half full is a reason to halt, too (the host doubles it)
 };
 
 // Cell-major gapped buckets: cell c owns slots [start[c], start[c+1]) of which the first
@@ -130,9 +137,11 @@ struct KernelTable {
                         opal_migrant* outbox_l, opal_migrant* outbox_r, StatusDev* st, const PairDev& pairs);
     void (*photon_insert)(cudaStream_t, const PhotonDev& dst, const opal_migrant* recs, const int* n_recs, int n_max,
                           long long cell_shift, StatusDev* st);
+    // burst_room_need > 0 (bursts): first make sure the photon store has room for that many more photons -- or, when the
+    // emitter list is valid, for as many as it lists -- else raise the halt in the name of `room_phase` and do nothing
     void (*emit)(cudaStream_t, const GridDev&, const BucketDev& electrons, const PhotonDev& photons, const StepParams&,
                  const double* qed_tables, double t, double min_energy, double max_angle, double max_fl,
-                 uint64_t seed, uint64_t call_index, StatusDev* st);
+                 uint64_t seed, uint64_t call_index, StatusDev* st, long long burst_room_need, int room_phase);
     void (*sync_bc)(cudaStream_t, const GridDev&, const double* halo_recv /*2 x 8 x 11 or null*/, double laser_y, double laser_z,
                     const double* laser_dev /*2 doubles or null*/);
     void (*field)(cudaStream_t, const GridDev& cur, const GridDev& nxt, bool zero_next_j);
@@ -159,7 +168,8 @@ struct KernelTable {
     // lean layout: close the free slots the strip kernel leaves inside the buckets
     void (*compact_cells)(cudaStream_t, const BucketDev&, int* hcount);
     // burst mode bookkeeping kernels: 0 begin (zero the per-advance counters), 1 check (raise halt on overflow / error), 2 end (step++)
-    void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species, int mover_cap);
+    // 3 the check of `species` + the begin-mark of the next advance; zero_a / zero_b: ints the begin-mark also zeroes (may be null)
+    void (*burst_mark)(cudaStream_t, StatusDev*, int what, int species, int mover_cap, int* zero_a, int* zero_b);
 };
 
 namespace fast { KernelTable table(); }
