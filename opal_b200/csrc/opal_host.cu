@@ -148,6 +148,7 @@ struct opal_ctx {
     // emitter queue (BucketDev::eq_slot): filled by the electrons' push + scatter of a step of opal_run_steps with emission on
     long long* d_eq_slot = nullptr; int* d_eq_cell = nullptr; int* d_eq_n = nullptr; int eq_cap = 0; bool eq_on = false;
     int64_t launches = 0;
+    int64_t n_regrids = 0, n_halts = 0, n_bursts = 0;   // OPAL_STATS=1: printed by opal_destroy
     ncclComm_t comm = nullptr;
     // optional per-kernel timing (opal_timing): event pairs per category
     bool timing = false;
@@ -460,6 +461,7 @@ bool settle(opal_ctx* c, int sp) {
 // Re-lay the buckets of species `sp` out for the demand recorded in count[] (which includes the
 // movers parked in d_overflow), then scatter the parked movers.
 bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
+    c->n_regrids++;
     Buckets& B = c->bk[sp];
     const int ncell = c->g.nx;
     std::vector<int> cnt(ncell);
@@ -978,6 +980,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
 // step after them stopped half-way (c->h_status then holds the counters and halt_species of that moment).
 bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const double* ly, const double* lz, int64_t* done, bool* halted) {
     *done = 0; *halted = false;
+    c->n_bursts++;
     if (c->laser_cap < 3 * n) {
         if (c->d_laser) cudaFree(c->d_laser);
         c->d_laser = nullptr; c->laser_cap = 0;
@@ -1018,7 +1021,7 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
         if (cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
             cudaStreamSynchronize(c->stream) != cudaSuccess) { ok = fail(c, OPAL_ECUDA, "burst status read-back failed"); break; }
         *done = c->h_status->step;
-        if (c->h_status->halt) { *halted = true; break; }
+        if (c->h_status->halt) { *halted = true; c->n_halts++; break; }
         s += batch;
     }
     cudaGraphExecDestroy(exec);
@@ -1103,6 +1106,9 @@ opal_status opal_destroy(opal_ctx* c) {
     if (!c) return OPAL_EINVAL;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (const char* e = getenv("OPAL_STATS")) if (e[0] == '1')
+        fprintf(stderr, "opal_b200 stats: launches %lld, burst steps %lld in %lld bursts, %lld halts, %lld re-layouts\n", (long long)c->launches,
+                (long long)c->burst_steps, (long long)c->n_bursts, (long long)c->n_halts, (long long)c->n_regrids);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (int k = 0; k < 3; k++) for (auto& p : c->ev[k]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     for (int s = 0; s < 2; s++) free_buckets(c->bk[s]);
