@@ -230,6 +230,21 @@ opal_status OPAL_FN(hgram_minmax)(opal_ctx*, int species, int ndim, const int* q
 opal_status OPAL_FN(hgram_bin)(opal_ctx*, int species, int ndim, const int* quantity, const int* log_scaled,
                                const double* gmin, const double* bin_sz, const int64_t* nbins, int weight_kind,
                                int log_density_adjust, double* counts, double* total);
+/* opal_hgram_bin for callers that may not allocate device memory (code under CUDA graph capture, tight
+   serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+   Same arguments and results as opal_hgram_bin, but the device-side bin counters live
+   in a static device array of OPAL_HGRAM_STATIC_MAX_BINS + 1 doubles (512 KiB, held by every GPU that loads
+   the library until exit) instead of a cudaMalloc per call; the call makes no cudaMalloc / cudaFree.
+   nbins[0]*nbins[1] > OPAL_HGRAM_STATIC_MAX_BINS returns OPAL_ECAPACITY (message in opal_last_error; the
+   context stays usable).  A lean-layout species whose cell hand-over is still pending (the step just run
+   left movers in the strips; settling them may re-lay the buckets out, which allocates) returns
+   OPAL_EINVAL: call any reader (opal_particles_count) once after the steps, then this.  All calls on one
+   GPU share the array: it is cleared at the start of every call, and calls that overlap on the GPU (two
+   contexts, two host threads) race on it.                                                          */
+#define OPAL_HGRAM_STATIC_MAX_BINS 65536
+opal_status OPAL_FN(hgram_bin_static)(opal_ctx*, int species, int ndim, const int* quantity, const int* log_scaled,
+                                      const double* gmin, const double* bin_sz, const int64_t* nbins, int weight_kind,
+                                      int log_density_adjust, double* counts, double* total);
 
 /* ---- multi-GPU: NCCL ring of slabs (replaces rsmpi p2p) -------------------- */
 opal_status OPAL_FN(comm_unique_id)(void* id128);                 /* ncclGetUniqueId; 128 bytes */

@@ -67,6 +67,7 @@ SIGNATURES = {
     "energy": [_vp, _pf64, _pf64, _pf64, _pf64],
     "hgram_minmax": [_vp, _int, _int, _vp, _vp, _vp, _vp, _pi64],
     "hgram_bin": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _int, _int, _vp, _pf64],
+    "hgram_bin_static": [_vp, _int, _int, _vp, _vp, _vp, _vp, _vp, _int, _int, _vp, _pf64],
     "comm_unique_id": [_vp],
     "comm_init": [_vp, _vp],
     "stream": [_vp, C.POINTER(_vp)],
@@ -180,6 +181,7 @@ QUANTITIES = ("x", "r", "energy", "px", "py", "pz", "p_perp", "theta", "phi", "l
 QUANTITY_UNITS = {"x": "m", "r": "m", "energy": "MeV", "px": "MeV/c", "py": "MeV/c", "pz": "MeV/c", "p_perp": "MeV/c", "theta": "rad",
                   "phi": "rad", "longitude": "rad", "latitude": "rad", "work": "J", "chi": "1"}
 W_WEIGHT, W_ENERGY = 0, 1
+HGRAM_STATIC_MAX_BINS = 65536      # OPAL_HGRAM_STATIC_MAX_BINS
 
 PARTICLE_FIELDS = ("cell", "x", "prev_x", "ux", "uy", "uz", "weight", "gamma", "chi", "tau", "work", "y", "z", "birth_time")
 
@@ -362,8 +364,9 @@ class Slab:
         self._ck(self.abi.hgram_minmax(self._h, species, nd, _ptr(q), _ptr(lg), _ptr(mn), _ptr(mx), C.byref(n)), "hgram_minmax")
         return mn[:nd].copy(), mx[:nd].copy(), n.value
 
-    def hgram_bin(self, species, quantities, gmin, bin_sz, nbins, log_scaled=None, weight=W_WEIGHT, log_density_adjust=True):
-        """pass 2 (hgram.rs:222-258 / 333-366): (weighted counts of this slab before /bin volume, flat; total weight)"""
+    def hgram_bin(self, species, quantities, gmin, bin_sz, nbins, log_scaled=None, weight=W_WEIGHT, log_density_adjust=True, static=False):
+        """pass 2 (hgram.rs:222-258 / 333-366): (weighted counts of this slab before /bin volume, flat; total weight).
+        static=True goes through opal_hgram_bin_static (no device allocation; at most HGRAM_STATIC_MAX_BINS bins)"""
         nd = len(quantities)
         q = np.array([QUANTITIES.index(v) if isinstance(v, str) else int(v) for v in quantities], dtype=np.int32)
         lg = np.array([int(bool(v)) for v in (log_scaled or [0] * nd)], dtype=np.int32)
@@ -371,8 +374,9 @@ class Slab:
         nb = np.ascontiguousarray(np.atleast_1d(nbins), dtype=np.int64)
         counts = np.zeros(int(np.prod(nb)))
         total = C.c_double(0.0)
-        self._ck(self.abi.hgram_bin(self._h, species, nd, _ptr(q), _ptr(lg), _ptr(gmin), _ptr(bin_sz), _ptr(nb), int(weight),
-                                    int(bool(log_density_adjust)), _ptr(counts), C.byref(total)), "hgram_bin")
+        fn, what = (self.abi.hgram_bin_static, "hgram_bin_static") if static else (self.abi.hgram_bin, "hgram_bin")
+        self._ck(fn(self._h, species, nd, _ptr(q), _ptr(lg), _ptr(gmin), _ptr(bin_sz), _ptr(nb), int(weight),
+                    int(bool(log_density_adjust)), _ptr(counts), C.byref(total)), what)
         return counts, total.value
 
     def fields_at(self, cell, xi):

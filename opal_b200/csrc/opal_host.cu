@@ -1713,6 +1713,74 @@ opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, con
     return OPAL_OK;
 }
 
+// ---- opal_hgram_bin_static: opal_hgram_bin for callers that may not allocate (no counterpart in the reference).
+// The bin counters -- what opal_hgram_bin cudaMallocs per call -- live in a file-scope device
+// array that every GPU loading the library holds until exit.  Its NAME is a host-side stand-in in this host code, not a device
+// address: the device address is looked up once per device with cudaGetSymbolAddress (that device current) and passed to the
+// kernels like any other pointer.  All calls share the array (it keeps the last call's counts: cleared on the stream before
+// each use); calls that overlap on one GPU -- two contexts, two host threads -- race on it.
+static __device__ __align__(256) double g_hgram_static_counts[OPAL_HGRAM_STATIC_MAX_BINS + 1];   // [bins][total]
+
+namespace {
+constexpr int HGRAM_STATIC_MAX_DEVICES = 64;
+double* g_hgram_static_ptr[HGRAM_STATIC_MAX_DEVICES] = {nullptr};
+
+// the device address of g_hgram_static_counts on the context's device (current: CHECK_CTX), nullptr + error state on failure
+double* hgram_static_scratch(opal_ctx* c) {
+    if (c->device < 0 || c->device >= HGRAM_STATIC_MAX_DEVICES) { fail(c, OPAL_EINVAL, "opal_hgram_bin_static: device ordinal out of range"); return nullptr; }
+    if (!g_hgram_static_ptr[c->device]) {
+        double* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_hgram_static_counts);
+        if (e != cudaSuccess || !p) {
+            fail(c, OPAL_ECUDA, std::string("opal_hgram_bin_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_hgram_static_ptr[c->device] = p;
+    }
+    return g_hgram_static_ptr[c->device];
+}
+}  // namespace
+
+opal_status opal_hgram_bin_static(opal_ctx* c, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
+                                  const int64_t* nbins, int weight_kind, int log_density_adjust, double* counts, double* total) {
+    CHECK_CTX(c);
+    if (!hgram_args_ok(species, ndim, q) || !gmin || !bin_sz || !nbins || !counts || !total) return OPAL_EINVAL;
+    if (weight_kind != OPAL_W_WEIGHT && weight_kind != OPAL_W_ENERGY) return OPAL_EINVAL;
+    long long nb[2] = {1, 1};
+    unsigned long long len = 1;
+    for (int d = 0; d < ndim; d++) {
+        if (nbins[d] < 1 || nbins[d] > (1ll << 28)) return OPAL_EINVAL;
+        nb[d] = nbins[d];
+        len *= (unsigned long long)nbins[d];
+    }
+    if (len > (unsigned long long)OPAL_HGRAM_STATIC_MAX_BINS) {
+        // not a sticky error: the context stays usable, the message is left for opal_last_error
+        c->err = "opal_hgram_bin_static: " + std::to_string(len) + " bins exceed the static scratch of " + std::to_string((long long)OPAL_HGRAM_STATIC_MAX_BINS) +
+                 " bins (use opal_hgram_bin)";
+        return OPAL_ECAPACITY;
+    }
+    if (species != OPAL_PHOTON && (c->lean[species].pending || c->lean[species].holes)) {
+        // settling the lean layout's mover strips may have to re-lay the buckets out, which allocates
+        c->err = "opal_hgram_bin_static: the cell hand-over of the last step is still pending; call any reader (opal_particles_count) first";
+        return OPAL_EINVAL;
+    }
+    for (unsigned long long i = 0; i < len; i++) counts[i] = 0.0;
+    *total = 0.0;
+    const bool present = species == OPAL_PHOTON ? c->ph[0].cap > 0 : c->bk[species].allocated;
+    if (!present) return OPAL_OK;
+    double* d_counts = hgram_static_scratch(c);
+    if (!d_counts) return (opal_status)c->status;
+    CU(cudaMemsetAsync(d_counts, 0, (len + 1) * sizeof(double), c->stream));
+    if (species == OPAL_PHOTON) hgram_bin_photon(c->stream, c->g, pdev(c, c->ph_cur), ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust, d_counts, d_counts + len);
+    else hgram_bin_charged(c->stream, c->g, bdev(c, species), species, c->bk[species].full, ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust,
+                           d_counts, d_counts + len);
+    c->launches++;
+    CU(cudaMemcpyAsync(counts, d_counts, len * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(total, d_counts + len, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return OPAL_OK;
+}
+
 opal_status opal_energy(opal_ctx* c, double* em, double* ke_e, double* ke_i, double* ke_ph) {
     CHECK_CTX(c);
     BucketDev be, bi;

@@ -1567,6 +1567,19 @@ opal_status opal_ref_hgram_bin(opal_ctx* g, int species, int ndim, const int* q,
     return OPAL_OK;
 }
 
+// The product's no-allocation variant (include/opal_b200.h; no counterpart in the reference): on the CPU there is no device
+// scratch to avoid, so this is opal_ref_hgram_bin behind the same size limit -- it exists so that the two libraries export
+// the same symbols and the limit can be tested without a GPU.
+opal_status opal_ref_hgram_bin_static(opal_ctx* g, int species, int ndim, const int* q, const int* lg, const double* gmin, const double* bin_sz,
+                                      const int64_t* nbins, int weight_kind, int adjust, double* counts, double* total) {
+    CHECK_CTX(g);
+    if ((ndim != 1 && ndim != 2) || !nbins) return OPAL_EINVAL;
+    unsigned long long len = 1;
+    for (int d = 0; d < ndim; d++) { if (nbins[d] < 1 || nbins[d] > (1ll << 28)) return OPAL_EINVAL; len *= (unsigned long long)nbins[d]; }
+    if (len > (unsigned long long)OPAL_HGRAM_STATIC_MAX_BINS) return OPAL_ECAPACITY;
+    return opal_ref_hgram_bin(g, species, ndim, q, lg, gmin, bin_sz, nbins, weight_kind, adjust, counts, total);
+}
+
 opal_status opal_ref_comm_unique_id(void*) { return OPAL_ENCCL; }
 opal_status opal_ref_comm_init(opal_ctx*, const void*) { return OPAL_ENCCL; }
 opal_status opal_ref_stream(opal_ctx*, void** s) { if (s) *s = nullptr; return OPAL_OK; }
