@@ -37,6 +37,9 @@
 // through private shared-memory columns: 19.5 ms; an `if (live)` around the arithmetic instead of finite free-slot marks
 // and a masked weight: +40 instructions; 16 warps per SM at 124 registers instead of 18 at 94: 17.0 ms; bulk copies of
 // 256 B / 512 B / 768 B / 1 KB per stream and 2 to 6 ring stages: equal within noise beyond 3 stages.
+// Also equal within noise (15.4-15.5 ms, power-capped): the five sign / zero tests and floor() moved from the FP64 pipe to integer
+// compares on the high words (DSETP 26 -> 3 in SASS); the two chunks of a ring stage pushed side by side for instruction-level
+// parallelism at 18 / 16 / 14 / 12 blocks per SM (96 + spills / 124 / 128 / 148 registers: 17.1 / 15.7 / 15.7 / 16.7 ms).
 #pragma once
 
 #ifndef OPAL_PUSH_STAGES
