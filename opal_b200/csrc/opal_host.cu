@@ -4,6 +4,8 @@
 // main.rs:240 and main.rs:266 stays on the device; the host contributes the two laser scalars
 // per step and reads back a 44-byte status block.  There is no CPU compute path in this file.
 #include <algorithm>
+#include <chrono>
+#include <climits>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -56,7 +58,8 @@ constexpr int NCCL_CHAR = 0;   // ncclInt8 / ncclChar
 struct Buckets {
     bool allocated = false;
     bool full = false;
-    long long slots = 0;
+    long long slots = 0;              // slots the layout uses (h_start[ncell]) ...
+    long long cap_slots = 0;          // ... of the cap_slots each field array holds
     std::vector<long long> h_start;   // ncell + 1
     long long* d_start = nullptr;
     int* d_count = nullptr;
@@ -101,6 +104,7 @@ struct opal_ctx {
     double* eb_alt[6] = {nullptr};   // the other half of the E/B ping-pong
     double* grid_block = nullptr;    // one allocation for all grid arrays
     Buckets bk[2];          // electrons, ions
+    Buckets spare[2];       // the arrays the last re-layout of each moved out of: the next one moves into them (alloc_buckets)
     double z_star = 1.0, mass_number = 1.0;
     Photons ph[2];          // ping-pong
     int ph_cur = 0;
@@ -119,6 +123,8 @@ struct opal_ctx {
         int parity = 0;           // the buffer the NEXT push reads
         bool pending = false;     // movers of the last push wait in d_strips[parity] (not yet in the buckets)
         bool holes = false;       // the buckets carry free slots (count[] counts slots in use)
+        int mc_floor = 0;         // strips at least this wide: raised when movers keep finding them full (maybe_widen_strips)
+        long long spill = 0, spill_adv = 0;   // movers that did, and the advances they were counted over
     } lean[2];
     opal_migrant* d_out[2] = {nullptr, nullptr};   // each: [header record][out_cap records]
     opal_migrant* d_in[2] = {nullptr, nullptr};
@@ -148,7 +154,12 @@ struct opal_ctx {
     // emitter queue (BucketDev::eq_slot): filled by the electrons' push + scatter of a step of opal_run_steps with emission on
     long long* d_eq_slot = nullptr; int* d_eq_cell = nullptr; int* d_eq_n = nullptr; int eq_cap = 0; bool eq_on = false;
     int64_t launches = 0;
-    int64_t n_regrids = 0, n_halts = 0, n_bursts = 0;   // OPAL_STATS=1: printed by opal_destroy
+    // lean strip kernel: cells above heavy_min particles go to the block-per-cell launch (opal_push_lean.cuh).  Switched on when a
+    // push reports such a cell (StatusDev::heavy_seen), off again after heavy_quiet status reads in a row without one.
+    bool widen_strips = true, pool_buckets = true;     // OPAL_STRIP_WIDEN=0 / OPAL_BUCKET_POOL=0 switch them off (diagnosis)
+    bool heavy_on = false, heavy_forced = false; int heavy_quiet = 0; int heavy_min = 4096; double heavy_factor = 8.0; int64_t n_heavy_launches = 0;
+    int64_t n_regrids = 0, n_halts = 0, n_bursts = 0, n_wasted = 0, n_widened = 0;   // OPAL_STATS=1: printed by opal_destroy
+    double t_regrid = 0.0, t_graph = 0.0, t_replay = 0.0, t_rg[5] = {0, 0, 0, 0, 0};   // host wall-clock seconds in re-layouts / graph capture + instantiation / replays + read-backs
     ncclComm_t comm = nullptr;
     // optional per-kernel timing (opal_timing): event pairs per category
     bool timing = false;
@@ -170,6 +181,9 @@ struct opal_ctx {
 };
 
 namespace {
+
+double wall_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+struct WallTimer { double& acc; double t0; explicit WallTimer(double& a) : acc(a), t0(wall_now()) {} ~WallTimer() { acc += wall_now() - t0; } };
 
 bool fail(opal_ctx* c, int st, const std::string& msg) {
     if (c && c->status == OPAL_OK) { c->status = st; c->err = msg; }
@@ -220,6 +234,14 @@ StepParams sparams(opal_ctx* c, int species) {
     sp.route_right = c->has_right() ? (c->self_nbr() ? 1 : 2) : 0;
     sp.mover_cap = c->mover_seg_cap; sp.out_cap = c->out_cap; sp.overflow_cap = c->overflow_cap;
     sp.cell_mover_cap = (species == OPAL_ELECTRON || species == OPAL_ION) ? c->lean[species].mc : 0;
+    // "heavy": far above the species' average population per cell (a uniform plasma of 1000 per cell has a million cells to keep
+    // the GPU busy with; a compressed layer of a few dozen cells with thousands each has not) and above heavy_min in any case
+    long long hm = c->heavy_min;
+    if (species == OPAL_ELECTRON || species == OPAL_ION)
+        hm = std::max<long long>(hm, (long long)(c->heavy_factor * (double)c->bk[species].n_hint / (double)std::max(c->g.nx, 1)));
+    hm = std::min<long long>(hm, INT_MAX / 4);
+    sp.heavy_min = c->heavy_on ? (int)hm : INT_MAX;
+    sp.heavy_hint = c->heavy_min <= 0 ? INT_MAX : (int)(c->heavy_on ? hm / 2 : hm);     // (hysteresis)
     return sp;
 }
 
@@ -227,7 +249,7 @@ void free_buckets(Buckets& B) {
     if (B.d_start) cudaFree(B.d_start);
     if (B.d_count) cudaFree(B.d_count);
     for (int k = 0; k < NF_FULL; k++) if (B.d_f[k]) { cudaFree(B.d_f[k]); B.d_f[k] = nullptr; }
-    B.d_start = nullptr; B.d_count = nullptr; B.allocated = false; B.slots = 0;
+    B.d_start = nullptr; B.d_count = nullptr; B.allocated = false; B.slots = 0; B.cap_slots = 0;
 }
 
 // capacity policy: demand * slack + pad, rounded up to a multiple of 32 slots
@@ -240,7 +262,10 @@ long long bucket_cap(opal_ctx* c, long long demand, bool roomy) {
     return (cap + 31) / 32 * 32;
 }
 
-bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand, bool full) {
+// `spare`: a set of arrays a re-layout left behind (regrid).  When it is large enough the new layout moves in without a single
+// cudaMalloc / cudaFree (each a device-wide synchronisation of milliseconds: a moving density pile re-lays its buckets out every
+// few hundred steps); otherwise it is freed and the new arrays get headroom for the next time.
+bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand, bool full, Buckets* spare = nullptr) {
     const int ncell = c->g.nx;
     B.h_start.assign(ncell + 1, 0);
     long long total = 0;
@@ -249,16 +274,29 @@ bool alloc_buckets(opal_ctx* c, Buckets& B, const std::vector<long long>& demand
     for (int i = 0; i < ncell; i++) B.h_start[i + 1] = B.h_start[i] + bucket_cap(c, demand[i], roomy);
     B.slots = B.h_start[ncell];
     B.full = full;
-    CUB(cudaMalloc(&B.d_start, (size_t)(ncell + 1) * sizeof(long long)));
-    CUB(cudaMalloc(&B.d_count, (size_t)ncell * sizeof(int)));
+    const int nf = full ? NF_FULL : NF_LEAN;
+    if (spare && !c->pool_buckets) { free_buckets(*spare); spare = nullptr; }
+    if (spare && spare->d_start && spare->full == full && spare->cap_slots >= B.slots) {
+        // (what the arrays hold is finite -- particles of an earlier layout, or the zeroes they were allocated with -- which is all
+        //  the lean push asks of a slot beyond count[])
+        B.d_start = spare->d_start; B.d_count = spare->d_count; B.cap_slots = spare->cap_slots;
+        for (int k = 0; k < NF_FULL; k++) B.d_f[k] = spare->d_f[k];
+        *spare = Buckets();
+    } else {
+        const long long spare_cap = spare ? spare->cap_slots : 0;
+        if (spare) free_buckets(*spare);
+        // (small populations: room to spare, so that the layouts to come find the arrays they move into large enough)
+        B.cap_slots = std::max<long long>(spare && roomy ? std::max(2 * B.slots, 2 * spare_cap) : B.slots, 1);
+        CUB(cudaMalloc(&B.d_start, (size_t)(ncell + 1) * sizeof(long long)));
+        CUB(cudaMalloc(&B.d_count, (size_t)ncell * sizeof(int)));
+        for (int k = 0; k < nf; k++) {
+            CUB(cudaMalloc(&B.d_f[k], (size_t)B.cap_slots * sizeof(double)));
+            // zero-filled: the lean push runs its arithmetic on every lane of a chunk, also on slots no particle has ever occupied
+            CUB(cudaMemsetAsync(B.d_f[k], 0, (size_t)B.cap_slots * sizeof(double), c->stream));
+        }
+    }
     CUB(cudaMemcpyAsync(B.d_start, B.h_start.data(), (size_t)(ncell + 1) * sizeof(long long), cudaMemcpyHostToDevice, c->stream));
     CUB(cudaMemsetAsync(B.d_count, 0, (size_t)ncell * sizeof(int), c->stream));
-    const int nf = full ? NF_FULL : NF_LEAN;
-    for (int k = 0; k < nf; k++) {
-        CUB(cudaMalloc(&B.d_f[k], (size_t)std::max<long long>(B.slots, 1) * sizeof(double)));
-        // zero-filled: the lean push runs its arithmetic on every lane of a chunk, also on slots no particle has ever occupied
-        CUB(cudaMemsetAsync(B.d_f[k], 0, (size_t)std::max<long long>(B.slots, 1) * sizeof(double), c->stream));
-    }
     CUB(cudaStreamSynchronize(c->stream));
     B.allocated = true;
     return true;
@@ -341,6 +379,7 @@ bool ensure_cell_movers(opal_ctx* c, int sp, long long n_particles) {
     long long mc = (long long)std::ceil((env_double("OPAL_CELL_MOVER_FRACTION", 0.02) * ppc + 12.0) / 16.0) * 16;   // per direction
     if (mc < 16) mc = 16;
     if (mc > 256) mc = 256;
+    mc = std::max<long long>(mc, L.mc_floor);
     if (!L.d_hcount || mc > L.mc) {
         for (int k = 0; k < 2; k++) {
             if (L.d_strips[k]) cudaFree(L.d_strips[k]);
@@ -357,6 +396,32 @@ bool ensure_cell_movers(opal_ctx* c, int sp, long long n_particles) {
         L.mc = (int)mc;
     }
     reset_lean(c, sp);
+    return true;
+}
+
+// Strips too narrow for this plasma?  (A relativistically hot cell sends half its particles next door every step; what does not
+// fit its strip goes through the segmented buffer and k_scatter: global atomics per record.)  Small grids can afford wide strips.
+int strip_width_cap(const opal_ctx* c) {
+    const long long by_memory = (long long)(1.0e9 / (2.0 * sizeof(StripRec) * (double)c->g.nx)) / 16 * 16;    // ~1 GB per strip buffer
+    return (int)std::min<long long>(by_memory, 2048);      // (a large grid stays with what ensure_cell_movers gave it)
+}
+bool strips_too_narrow(const opal_ctx* c, int sp) {
+    const opal_ctx::Lean& L = c->lean[sp];
+    if (!L.d_hcount || L.spill_adv < 8 || L.mc >= strip_width_cap(c) || !c->widen_strips) return false;
+    const double per_advance = (double)L.spill / (double)L.spill_adv;
+    return per_advance > std::max(64.0, 0.002 * (double)c->bk[sp].n_hint);
+}
+bool settle(opal_ctx* c, int sp);
+bool maybe_widen_strips(opal_ctx* c) {
+    for (int sp = 0; sp < 2; sp++) {
+        opal_ctx::Lean& L = c->lean[sp];
+        if (!strips_too_narrow(c, sp)) { if (L.spill_adv >= 64) { L.spill = 0; L.spill_adv = 0; } continue; }
+        if (!settle(c, sp)) return false;                   // the last push's movers into the buckets, free slots closed
+        L.mc_floor = std::max(L.mc, std::min(strip_width_cap(c), std::max(4 * L.mc, 64)));
+        L.spill = 0; L.spill_adv = 0;
+        c->n_widened++;
+        if (!ensure_cell_movers(c, sp, c->bk[sp].n_hint)) return false;
+    }
     return true;
 }
 
@@ -408,10 +473,20 @@ bool reset_status(opal_ctx* c, bool keep_err) {
 }
 
 // copy the status block to the host, translate sticky device-side assertion bits
+// what the status block just read says about heavy cells; returns true when the block-per-cell launch was just switched on
+bool note_heavy(opal_ctx* c) {
+    if (c->h_status->heavy_seen) {
+        c->heavy_quiet = 0;
+        if (!c->heavy_on && c->heavy_min > 0) { c->heavy_on = true; return true; }
+    } else if (c->heavy_on && !c->heavy_forced && ++c->heavy_quiet >= 64) c->heavy_on = false;
+    return false;
+}
+
 bool fetch_status(opal_ctx* c) {
     // the per-segment mover counts travel with it (4 KB): advance_charged sizes the mover buffer from them
     CUB(cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUB(cudaStreamSynchronize(c->stream));
+    note_heavy(c);
     const unsigned e = c->h_status->err;
     if (e & ERR_CFL) return fail(c, OPAL_EASSERT_CFL, "push: assert!(dxi < 1.0) failed (electron.rs:313 / ion.rs:199 / photon.rs:164)");
     if (e & ERR_INDEX) return fail(c, OPAL_EASSERT_INDEX, "cell index out of range (yee.rs:501-502)");
@@ -462,11 +537,15 @@ bool settle(opal_ctx* c, int sp) {
 // movers parked in d_overflow), then scatter the parked movers.
 bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
     c->n_regrids++;
+    WallTimer wt(c->t_regrid);
+    double tq = wall_now();
+    auto lap = [&](int k) { const double t = wall_now(); c->t_rg[k] += t - tq; tq = t; };
     Buckets& B = c->bk[sp];
     const int ncell = c->g.nx;
     std::vector<int> cnt(ncell);
     CUB(cudaMemcpyAsync(cnt.data(), B.d_count, (size_t)ncell * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CUB(cudaStreamSynchronize(c->stream));
+    lap(0);
     std::vector<long long> demand(ncell);
     long long total = 0;
     for (int i = 0; i < ncell; i++) { demand[i] = cnt[i]; total += cnt[i]; }
@@ -492,15 +571,17 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
         // the old and the new buckets coexist during the copy: widen only when that fits comfortably
         long long wide_slots = 0;
         for (int i = 0; i < ncell; i++) wide_slots += bucket_cap(c, wide[i], false);
-        size_t free_b = 0, total_b = 0;
-        cudaMemGetInfo(&free_b, &total_b);
         const double need = (double)wide_slots * (B.full ? NF_FULL : NF_LEAN) * sizeof(double);
-        if (need < 0.8 * (double)free_b) demand.swap(wide);
+        size_t free_b = 0, total_b = 0;
+        if (need > 1.0e9) cudaMemGetInfo(&free_b, &total_b);           // (a millisecond: only asked when it can matter)
+        if (need <= 1.0e9 || need < 0.8 * (double)free_b) demand.swap(wide);
         else { c->regrid_radius[sp] = 0; c->regrid_boost[sp] = 1.0; }
     }
+    lap(1);
     Buckets old = B;
     B = Buckets();
-    if (!alloc_buckets(c, B, demand, old.full)) return false;
+    if (!alloc_buckets(c, B, demand, old.full, &c->spare[sp])) return false;
+    lap(2);
     B.n_hint = total;
     B.movers_sized = old.movers_sized;
     BucketDev src; src.ncell = ncell; src.start = old.d_start; src.count = old.d_count;
@@ -522,7 +603,13 @@ bool regrid(opal_ctx* c, int sp, bool deposit_parked) {
                  nullptr, nullptr, reinterpret_cast<int*>(c->d_overflow), c->d_status); c->launches++;
     (void)n_parked;
     CUB(cudaStreamSynchronize(c->stream));
-    free_buckets(old);
+    lap(3);
+    // small populations keep the old arrays for the next re-layout to move into; large ones give the memory back
+    if ((double)old.cap_slots * (old.full ? NF_FULL : NF_LEAN) * sizeof(double) <= 2.0e9) {
+        c->spare[sp] = old;                   // (its arrays only: alloc_buckets looks at nothing else)
+        c->spare[sp].allocated = false;
+    } else free_buckets(old);
+    lap(4);
     return fetch_status(c);
 }
 
@@ -724,6 +811,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     LeanStrips ls = {L.d_strips[L.parity], L.d_scount[L.parity], L.d_strips[1 - L.parity], L.d_scount[1 - L.parity], L.d_hcount};
     { Timed tm(c, 0); strips = c->k.push(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, L.d_hcount ? &ls : nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                                          c->d_overflow, c->d_status, ke_out); c->launches++; }
+    if (strips && p.heavy_min < INT_MAX) { c->launches++; c->n_heavy_launches++; }
     if (ke_out && strips) c->ke_fused = true;
     if (strips) { L.parity ^= 1; L.pending = true; L.holes = true; }      // this push's movers wait for the next one
     { Timed tm(c, 1); c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, dep, c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
@@ -732,6 +820,7 @@ bool advance_charged(opal_ctx* c, int sp, bool dep, bool check, bool want_ke = f
     if (check) {
         if (!fetch_status(c)) return false;
         c->last_gone[sp][0] = c->h_status->gone[0]; c->last_gone[sp][1] = c->h_status->gone[1];
+        if (strips) { L.spill += c->h_status->strip_spill[sp]; L.spill_adv++; }
         if (!handle_overflow(c, sp, dep)) return false;
         if (!grow_movers_after(c)) return false;
     }
@@ -941,6 +1030,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
         c->k.scatter(c->stream, c->g, bdev(c, sp), p, B.full, cfg.fused(), c->d_movers, nullptr, 0, 0, nullptr, c->d_out[0] + 1, c->d_out[1] + 1,
                      reinterpret_cast<int*>(c->d_overflow), c->d_status);
         n += 2;
+        if (strips && p.heavy_min < INT_MAX) { n++; c->n_heavy_launches++; }      // the block-per-cell launch behind the push
         pend = sp;
     }
     if (photons_move) {
@@ -1001,6 +1091,7 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     const int parity0[2] = {c->lean[0].parity, c->lean[1].parity};     // two captured steps leave the strip parity where it was
     const int ph_cur0 = c->ph_cur;                                     // ... and the photon ping-pong
     const uint64_t emit_call0 = c->emit_calls;
+    const double tg0 = wall_now();
     cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
     if (e == cudaSuccess) {
         per_step = enqueue_step(c, cfg, emit_call0);
@@ -1009,8 +1100,11 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     }
     if (e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
     if (e != cudaSuccess) { if (graph) cudaGraphDestroy(graph); leave(); return fail(c, OPAL_ECUDA, std::string("burst graph: ") + cudaGetErrorString(e)); }
+    c->t_graph += wall_now() - tg0;
+    const double tr0 = wall_now();
     bool ok = true;
     int64_t s = 0;
+    int spill_seen[2] = {0, 0};
     while (s < n && ok) {
         const int64_t batch = std::min<int64_t>(n - s, 128);
         for (int64_t i = 0; i < batch; i += 2) {
@@ -1020,12 +1114,18 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
         c->launches += batch * per_step;
         if (cudaMemcpyAsync(c->h_status, c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess ||
             cudaStreamSynchronize(c->stream) != cudaSuccess) { ok = fail(c, OPAL_ECUDA, "burst status read-back failed"); break; }
+        for (int sp = 0; sp < 2; sp++) {            // (the block was zeroed when the burst began)
+            c->lean[sp].spill += c->h_status->strip_spill[sp] - spill_seen[sp]; spill_seen[sp] = c->h_status->strip_spill[sp];
+            c->lean[sp].spill_adv += c->h_status->step - *done;
+        }
         *done = c->h_status->step;
-        if (c->h_status->halt) { *halted = true; c->n_halts++; break; }
+        if (c->h_status->halt) { *halted = true; c->n_halts++; c->n_wasted += (s + batch) - *done; note_heavy(c); break; }
         s += batch;
+        if (note_heavy(c)) break;                    // heavy cells have appeared: the caller starts a new burst with the block-per-cell launch in it
+        if (strips_too_narrow(c, 0) || strips_too_narrow(c, 1)) break;      // ... or one with wider mover strips
     }
-    cudaGraphExecDestroy(exec);
-    cudaGraphDestroy(graph);
+    c->t_replay += wall_now() - tr0;
+    { const double td0 = wall_now(); cudaGraphExecDestroy(exec); cudaGraphDestroy(graph); c->t_graph += wall_now() - td0; }
     leave();
     c->burst_steps += *done;
     if (ok && (*done & 1)) swap_fields(c);       // an odd number of steps ran: the fields sit in the other buffer set
@@ -1059,6 +1159,13 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     c->slack = env_double("OPAL_BUCKET_SLACK", 1.25);
     c->slack_from_env = getenv("OPAL_BUCKET_SLACK") != nullptr || getenv("OPAL_BUCKET_PAD") != nullptr;
     c->pad = (int)env_ll("OPAL_BUCKET_PAD", 64);
+    // OPAL_HEAVY_MIN: cell population above which the lean push may hand a cell to a whole block (0: never); OPAL_HEAVY_FORCE=1
+    // keeps that second launch on from the first step (tests)
+    c->heavy_min = (int)std::max<long long>(0, std::min<long long>(env_ll("OPAL_HEAVY_MIN", 4096), INT_MAX / 4));
+    c->heavy_factor = std::max(0.0, env_double("OPAL_HEAVY_FACTOR", 8.0));       // ... and above this many times the average population
+    c->heavy_forced = c->heavy_on = env_ll("OPAL_HEAVY_FORCE", 0) != 0 && c->heavy_min > 0;
+    c->widen_strips = env_ll("OPAL_STRIP_WIDEN", 1) != 0;
+    c->pool_buckets = env_ll("OPAL_BUCKET_POOL", 1) != 0;
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     GridDev& g = c->g;
@@ -1107,11 +1214,11 @@ opal_status opal_destroy(opal_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (const char* e = getenv("OPAL_STATS")) if (e[0] == '1')
-        fprintf(stderr, "opal_b200 stats: launches %lld, burst steps %lld in %lld bursts, %lld halts, %lld re-layouts\n", (long long)c->launches,
-                (long long)c->burst_steps, (long long)c->n_bursts, (long long)c->n_halts, (long long)c->n_regrids);
+        fprintf(stderr, "opal_b200 stats: launches %lld, burst steps %lld in %lld bursts, %lld halts (%lld replayed steps skipped behind them), %lld re-layouts; %lld block-per-cell launches enqueued, strips widened %lld times (now %d / %d records); host seconds: re-layouts %.3f (counts %.3f, sizing %.3f, alloc %.3f, copy %.3f, free %.3f), graph build %.3f, replays %.3f\n",
+                (long long)c->launches, (long long)c->burst_steps, (long long)c->n_bursts, (long long)c->n_halts, (long long)c->n_wasted, (long long)c->n_regrids, (long long)c->n_heavy_launches, (long long)c->n_widened, c->lean[0].mc, c->lean[1].mc, c->t_regrid, c->t_rg[0], c->t_rg[1], c->t_rg[2], c->t_rg[3], c->t_rg[4], c->t_graph, c->t_replay);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (int k = 0; k < 3; k++) for (auto& p : c->ev[k]) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
-    for (int s = 0; s < 2; s++) free_buckets(c->bk[s]);
+    for (int s = 0; s < 2; s++) { free_buckets(c->bk[s]); free_buckets(c->spare[s]); }
     if (c->d_absorb_kind) cudaFree(c->d_absorb_kind);
     if (c->d_absorb_slot) cudaFree(c->d_absorb_slot);
     if (c->d_absorb_last) cudaFree(c->d_absorb_last);
@@ -1616,13 +1723,14 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
             if (!photon_count(c, &nph)) break;
             if (!ensure_photons(c, (long long)nph + 2 * c->bk[OPAL_ELECTRON].n_hint)) break;
         }
+        if (!maybe_widen_strips(c)) break;
         const int64_t n = ((nsteps - s0 - 1) / 2) * 2;
         int64_t done = 0;
         bool halted = false;
         if (!run_burst(c, cfg, n, t, laser_y ? laser_y + s0 : nullptr, laser_z ? laser_z + s0 : nullptr, &done, &halted)) break;
         s0 += done;
         for (int64_t k = 0; k < done; k++) t += c->g.dt;             // main.rs:266
-        if (!halted) break;
+        if (!halted) { if (done >= n) break; continue; }     // (a burst that ended early at a step boundary: start the next one)
         // step s0 stopped half-way: finish it the ordinary way, then resume
         const unsigned err = c->h_status->err;
         const int hphase = c->h_status->halt_species;
@@ -1640,6 +1748,7 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
         t += c->g.dt;
     }
     for (int64_t s = s0; s < nsteps && c->status == OPAL_OK; s++) {   // main.rs:238-267
+        if (!maybe_widen_strips(c)) break;
         // the last step of the call also sums the electrons' kinetic energy (lean strip kernel): opal_energy then needs no particle pass
         if (!run_phases(c, cfg, PH_ELECTRONS, t, laser_y ? laser_y[s] : 0.0, laser_z ? laser_z[s] : 0.0, s == nsteps - 1 && !cfg.emit && !c->absorb_on)) break;
         t += c->g.dt;

@@ -1315,15 +1315,25 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
         const int gr = (int)(blocks < 1 ? 1 : blocks);
         const int smem = OPAL_PUSH_WPB * (int)sizeof(PushScratch);
         // (the attribute is per device and contexts may live on several devices: set on every launch, a cheap host-side call)
-#define LAUNCHF(B0, K) do { cudaFuncSetAttribute(k_push_lean_fast<B0, K, OPAL_ELECTRON>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
-        k_push_lean_fast<B0, K, OPAL_ELECTRON><<<gr, OPAL_PUSH_WPB * 32, smem, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, ke_out); } while (0)
-#define LAUNCHI(B0) do { cudaFuncSetAttribute(k_push_lean_fast<B0, false, OPAL_ION>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
-        k_push_lean_fast<B0, false, OPAL_ION><<<gr, OPAL_PUSH_WPB * 32, smem, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, nullptr); } while (0)
+        // cells above sp.heavy_min: skipped by the first launch, worked on block by block by the second (two blocks per SM)
+        const bool heavy = sp.heavy_min < INT_MAX;
+        const int smem_h = OPAL_HEAVY_WARPS * (int)sizeof(PushScratch) + (int)sizeof(HeavyShared);
+        const int gr_h = (int)std::min<long long>(2 * 148, ((long long)b.ncell + 7) / 8);
+#define LAUNCH2(B0, K, SPC, KE_OUT) do { \
+        cudaFuncSetAttribute(k_push_lean_fast<B0, K, SPC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); \
+        k_push_lean_fast<B0, K, SPC, false><<<gr, OPAL_PUSH_WPB * 32, smem, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, KE_OUT); \
+        if (heavy) { \
+            cudaFuncSetAttribute(k_push_lean_fast<B0, K, SPC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_h); \
+            k_push_lean_fast<B0, K, SPC, true><<<gr_h, OPAL_HEAVY_WARPS * 32, smem_h, s>>>(g, b, sp, movers, seg, ls->in, ls->scount_in, ls->out, ls->scount_out, ls->hcount, out_l, out_r, overflow, st, KE_OUT); \
+        } } while (0)
+#define LAUNCHF(B0, K) LAUNCH2(B0, K, OPAL_ELECTRON, ke_out)
+#define LAUNCHI(B0) LAUNCH2(B0, false, OPAL_ION, nullptr)
         if (sp.species == OPAL_ION) { if (sp.flags & OPAL_STEP_BX_ZERO) LAUNCHI(true); else LAUNCHI(false); }
         else if (sp.flags & OPAL_STEP_BX_ZERO) { if (ke_out) LAUNCHF(true, true); else LAUNCHF(true, false); }
         else { if (ke_out) LAUNCHF(false, true); else LAUNCHF(false, false); }
 #undef LAUNCHF
 #undef LAUNCHI
+#undef LAUNCH2
         return true;
     }
     if (sp.species == OPAL_ELECTRON && full) {

@@ -163,6 +163,28 @@ struct __align__(128) PushScratch {
     unsigned long long bar[OPAL_PUSH_STAGES + 1];   // mbarriers: one per ring stage + the arrivals
 };
 
+// Heavy cells (k_push_lean_fast<.., HEAVY = true>): a cell holding more than StepParams::heavy_min particles is left out by the
+// one-warp-per-cell launch (which marks it: HEAVY_MARK) and worked on by a whole block of the launch that follows: its
+// OPAL_HEAVY_WARPS warps take the ring stages of the cell's residents in turn, hand out strip slots and free slots through
+// counters in shared memory, share the arrivals, and each reduce and deposit their own partial sums.  One warp alone needs
+// ~11 us per 1000 particles of a cell (all latency).  Measured (tools/bench_heavy_cell.py: ONE cold pile among 2048 cells of
+// 100, whole step): 2000 particles 49 -> 41 us, 4000: 71 -> 43, 8000: 115 -> 53, 16 000: 204 -> 69, 32 000: 550 -> 106; at
+// 1000 the second launch costs more (2-3 us) than it saves, and a few dozen cells of 1000-3000 each (the reference's
+// hole_boring and two_stream decks) run as fast without it -- different warps have them anyway.  Hence the host's default:
+// above 4096 particles AND above 8x the species' average per cell (opal_host.cu: sparams, note_heavy).
+#ifndef OPAL_HEAVY_WARPS
+#define OPAL_HEAVY_WARPS 8
+#endif
+constexpr int HEAVY_LIST_CAP = OPAL_HEAVY_WARPS * 32;   // candidate cells looked at per round: one per thread
+constexpr int HEAVY_FREE_CAP = 1024;                    // free-slot indices remembered per heavy cell and step
+constexpr int HEAVY_MARK = -1;                          // in scount_out[2c] between the two launches: cell c is the second one's
+struct HeavyShared {
+    int list[HEAVY_LIST_CAP];        // the heavy cells among this round's candidates
+    int n_list;
+    int mloc_l, mloc_r, n_free, a_stay;   // the cell's running counters (registers in the one-warp kernel)
+    int free_list[HEAVY_FREE_CAP];
+};
+
 // shift the live particles of one lean bucket down over its free slots (one warp); returns the live count
 __device__ __forceinline__ int compact_cell(const BucketDev& b, long long base, int n, int lane, unsigned lt_mask) {
     __syncwarp();
@@ -198,7 +220,11 @@ __global__ void __launch_bounds__(256) k_compact_cells(BucketDev b, int* __restr
         const int cap = (int)(b.start[c + 1] - b.start[c]);
         const int n = min(b.count[c], cap);
         const int live = compact_cell(b, b.start[c], n, lane, lt_mask);
-        if (lane == 0) { b.count[c] = live + (b.count[c] - n); hcount[c] = 0; }
+        const int parked = b.count[c] - n;                        // demand beyond the bucket's room (see k_push_lean_fast)
+        const int fill_end = min(live + parked, cap);
+        for (int i = live + lane; i < fill_end; i += 32) b.f[F_X][b.start[c] + i] = OPAL_HOLE_MARK;
+        __syncwarp();
+        if (lane == 0) { b.count[c] = live + parked; hcount[c] = fill_end - live; }
     }
 }
 
@@ -248,8 +274,9 @@ __global__ void __launch_bounds__(256) k_strip_flush(BucketDev b, StepParams sp,
 //      pushed particles into *ke_out, so the energy diagnostic that follows a step costs no second pass over HBM.
 // SP:  OPAL_ELECTRON -> Vay push; OPAL_ION -> Boris push in the same reciprocal arithmetic, alpha and the deposited
 //      charge from Z* and A (ion.rs:170-172).
-template <bool BX0, bool KE, int SP>
-__global__ void __launch_bounds__(OPAL_PUSH_WPB * 32, OPAL_PUSH_MINBLK)
+// HEAVY: the block-per-cell variant for the cells the one-warp launch skipped (see HeavyShared above).
+template <bool BX0, bool KE, int SP, bool HEAVY>
+__global__ void __launch_bounds__(HEAVY ? OPAL_HEAVY_WARPS * 32 : OPAL_PUSH_WPB * 32, HEAVY ? 2 : OPAL_PUSH_MINBLK)
 k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict__ movers, int* __restrict__ seg_count,
                  const StripRec* __restrict__ strips_in, const int* __restrict__ scount_in, StripRec* __restrict__ strips_out,
                  int* __restrict__ scount_out, int* __restrict__ hcount, opal_migrant* __restrict__ out_l, opal_migrant* __restrict__ out_r,
@@ -258,6 +285,11 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
     constexpr int NST = OPAL_PUSH_STAGES, SUP = OPAL_PUSH_SUP, SUPN = 32 * SUP;
     extern __shared__ __align__(128) unsigned char s_dyn[];
     PushScratch& S = reinterpret_cast<PushScratch*>(s_dyn)[threadIdx.x >> 5];
+    constexpr int WPC = HEAVY ? OPAL_HEAVY_WARPS : 1;                 // warps that share a cell
+    constexpr int FREE_CAP = HEAVY ? HEAVY_FREE_CAP : PUSH_FREE_CAP;
+    const int wib = HEAVY ? (int)(threadIdx.x >> 5) : 0;              // this warp's place among them
+    HeavyShared& H = *reinterpret_cast<HeavyShared*>(s_dyn + WPC * sizeof(PushScratch));     // (HEAVY only)
+    int* const free_list = HEAVY ? H.free_list : S.free_list;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = lanemask_lt();
     const int warps_total = gridDim.x * OPAL_PUSH_WPB;
@@ -280,10 +312,40 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
     __syncwarp();
     unsigned phase = 0;                          // bit k: the parity the next wait on bar[k] expects
 
-    for (int c = blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5); c < nc; c += warps_total) {
+    // HEAVY: the next cell of this block (every thread calling together); nc when there is none
+    int h_round = 0, h_pos = 0, h_n = 0;
+    auto next_heavy = [&]() -> int {
+        if constexpr (!HEAVY) return nc;
+        else {
+            // rounds of blockDim.x candidates, cell = blockIdx.x + k gridDim.x (neighbouring heavy cells go to different blocks):
+            // every thread looks at one, the heavy ones are listed in shared memory and worked through by the whole block
+            for (;;) {
+                if (h_pos < h_n) return H.list[h_pos++];
+                const long long k0 = (long long)h_round * blockDim.x;
+                if (blockIdx.x + k0 * gridDim.x >= nc) return nc;
+                __syncthreads();                                   // everyone is done with the old list
+                if (threadIdx.x == 0) H.n_list = 0;
+                __syncthreads();
+                // (the mark the one-warp launch left, not the population: that launch has changed the counts of the cells it did)
+                const long long cand = blockIdx.x + (k0 + threadIdx.x) * gridDim.x;
+                if (cand < nc && scount_out[2 * cand] == HEAVY_MARK) H.list[atomicAdd(&H.n_list, 1)] = (int)cand;
+                __syncthreads();
+                h_n = H.n_list; h_pos = 0; h_round++;
+            }
+        }
+    };
+    for (int c = HEAVY ? next_heavy() : (int)(blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5)); c < nc; c = HEAVY ? next_heavy() : c + warps_total) {
         const long long base = b.start[c];
         const int cap = (int)(b.start[c + 1] - base);
         const int n = min(b.count[c], cap);
+        if constexpr (HEAVY) {
+            __syncthreads();                                       // every warp is done with the last cell's counters
+            if (threadIdx.x == 0) { H.mloc_l = 0; H.mloc_r = 0; H.n_free = 0; H.a_stay = 0; }
+            __syncthreads();
+        } else if (n > sp.heavy_min) {                             // left to the block-per-cell launch that follows
+            if (lane == 0) scount_out[2 * c] = HEAVY_MARK;
+            continue;
+        }
         // arrivals: last step's right-movers of the left neighbour cell and left-movers of the right neighbour cell
         int src_l = c - 1, src_r = c + 1;
         if (src_l < 0) src_l = sp.route_left == 1 ? nc - 1 : -1;         // periodic self-neighbour: the opposite edge
@@ -300,15 +362,17 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
         const int j = c + g.left;
         const StripRec* const arr_l = strips_in + ((long long)(src_l < 0 ? 0 : src_l) * 2 + 1) * MC;
         const StripRec* const arr_r = strips_in + ((long long)(src_r < 0 ? 0 : src_r) * 2) * MC;
-        const int st_l = min(n_from_l, PUSH_ARR), st_r = min(n_from_r, PUSH_ARR);      // staged through shared memory
+        // staged through shared memory (HEAVY: the arrivals are shared out among the warps and read from global memory)
+        const int st_l = HEAVY ? 0 : min(n_from_l, PUSH_ARR), st_r = HEAVY ? 0 : min(n_from_r, PUSH_ARR);
         __syncwarp();
         if (elect_one()) {
 #pragma unroll
             for (int s_ = 0; s_ < NST - 1; s_++) {
-                if (s_ < n_sup) {
-                    const unsigned bytes = 256u * (unsigned)min(SUP, n_chunks - s_ * SUP);
+                const int q = wib + s_ * WPC;                      // this warp's ring stages: wib, wib + WPC, ...
+                if (q < n_sup) {
+                    const unsigned bytes = 256u * (unsigned)min(SUP, n_chunks - q * SUP);
                     mbar_expect_tx(&S.bar[s_], 5 * bytes);
-                    const long long o = base + s_ * SUPN;
+                    const long long o = base + (long long)q * SUPN;
                     bulk_g2s(S.ring[s_][0], fx + o, bytes, &S.bar[s_]); bulk_g2s(S.ring[s_][1], fux + o, bytes, &S.bar[s_]);
                     bulk_g2s(S.ring[s_][2], fuy + o, bytes, &S.bar[s_]); bulk_g2s(S.ring[s_][3], fuz + o, bytes, &S.bar[s_]);
                     bulk_g2s(S.ring[s_][4], fw + o, bytes, &S.bar[s_]);
@@ -411,17 +475,36 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
             sjz0 = fma(tz, w0, sjz0); sjz1 = fma(tz, w1, sjz1); sjz2 = fma(tz, w2, sjz2);
         };
         // a mover: into this step's strip of the cell (the neighbour cell's next push picks it up), or out of the slab
-        auto hand_over = [&](bool left, int r, double x_old, double xn, double fl, const V3& u, double W, double igam, double gam2, int it) {
+        // Movers that find their cell's strip full go to the shared segmented buffer (k_scatter, right after this kernel, puts
+        // them into their buckets and deposits them).  ONE reservation there for all of a chunk's -- same cell, same chunk: same
+        // segment; a relativistically hot cell sends half a chunk this way, and that many same-address atomics with a return
+        // value cost microseconds.  Called in warp-uniform code; returns the lane's slot in the segment.  (HEAVY only: in the
+        // one-warp kernel the test for "will this chunk spill" sits in the path of every chunk with a mover and costs the headline
+        // case 2.6 %; there each spilling lane reserves its own slot inside hand_over, as it always did.)
+        auto reserve_spill = [&](bool spills, int it) -> int {
+            const unsigned m_ov = __ballot_sync(FULLMASK, spills);
+            if (!m_ov) return 0;
+            const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)it * 0x85EBCA77u) >> 22);   // top 10 bits: OPAL_MOVER_SEGMENTS == 1024
+            int rg = 0;
+            if (lane == 0) {
+                rg = atomicAdd(seg_count + seg, __popc(m_ov));
+                atomicAdd(&st->strip_spill[SP == OPAL_ELECTRON ? 0 : 1], __popc(m_ov));           // the host widens the strips when this is the rule
+            }
+            return __shfl_sync(FULLMASK, rg, 0) + __popc(m_ov & lt_mask);
+        };
+        auto hand_over = [&](bool left, int r, int rg /* HEAVY: from reserve_spill */, double x_old, double xn, double fl, const V3& u, double W, double igam, double gam2, int it) {
             const int route = left ? route_l : route_r;
             if (route == 1) {
                 if (r < MC) {
                     double2* const rec = reinterpret_cast<double2*>(strips_out + ((long long)c * 2 + (left ? 0 : 1)) * MC + r);   // 3 x 16-byte stores
                     rec[0] = make_double2(xn, x_old); rec[1] = make_double2(u.x, u.y); rec[2] = make_double2(u.z, W);
                 } else {
-                    // strip full (a cell far hotter or denser than the strips were sized for): the shared segmented buffer;
-                    // k_scatter, right after this kernel, puts it into its bucket and deposits it
-                    const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)it * 0x85EBCA77u) >> 22);   // top 10 bits: OPAL_MOVER_SEGMENTS == 1024
-                    const int rg = atomicAdd(seg_count + seg, 1);
+                    // strip full (a cell far hotter or denser than the strips were sized for): slot rg of its segment (reserve_spill)
+                    const int seg = (int)(((unsigned)c * 0x9E3779B1u + (unsigned)it * 0x85EBCA77u) >> 22);   // (as in reserve_spill)
+                    if constexpr (!HEAVY) {
+                        rg = atomicAdd(seg_count + seg, 1);
+                        atomicAdd(&st->strip_spill[SP == OPAL_ELECTRON ? 0 : 1], 1);
+                    }
                     if (rg < sp.mover_cap) {
                         opal_migrant m;
                         long long dst = (long long)c + (left ? -1 : 1);
@@ -470,26 +553,43 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                 deposit_stayer(W, u, igam, ro, xn);
             }
             if (m_free) {                                      // warp-uniform
+                int bf = n_free, bl = mloc_l, br = mloc_r;     // where this chunk's free slots / movers go
+                if constexpr (HEAVY) {
+                    if (lane == 0) {
+                        bf = atomicAdd(&H.n_free, __popc(m_free));
+                        bl = m_l ? atomicAdd(&H.mloc_l, __popc(m_l)) : 0;
+                        br = m_r ? atomicAdd(&H.mloc_r, __popc(m_r)) : 0;
+                    }
+                    bf = __shfl_sync(FULLMASK, bf, 0); bl = __shfl_sync(FULLMASK, bl, 0); br = __shfl_sync(FULLMASK, br, 0);
+                }
+                const bool left = fl < 0.0;
+                const int r = left ? bl + __popc(m_l & lt_mask) : br + __popc(m_r & lt_mask);      // (a mover's) slot in its strip
+                int rg = 0;
+                if constexpr (HEAVY) {
+                    if (bl + __popc(m_l) > MC || br + __popc(m_r) > MC)                            // warp-uniform
+                        rg = reserve_spill(live && !stay && (left ? route_l : route_r) == 1 && r >= MC, k0 >> 5);
+                }
                 if ((m_free >> lane) & 1u) {
-                    const int k = n_free + __popc(m_free & lt_mask);
-                    if (k < PUSH_FREE_CAP) S.free_list[k] = i;
+                    const int k = bf + __popc(m_free & lt_mask);
+                    if (k < FREE_CAP) free_list[k] = i;
                     if (live) {                                // a mover
                         fx[s] = OPAL_HOLE_MARK;                // the vacated slot
-                        const bool left = fl < 0.0;
-                        hand_over(left, left ? mloc_l + __popc(m_l & lt_mask) : mloc_r + __popc(m_r & lt_mask), x, xn, fl, u, W, igam, gam2, k0 >> 5);
+                        hand_over(left, r, rg, x, xn, fl, u, W, igam, gam2, k0 >> 5);
                     }
                 }
-                n_free += __popc(m_free);
-                mloc_l += __popc(m_l); mloc_r += __popc(m_r);
+                if constexpr (!HEAVY) {
+                    n_free += __popc(m_free);
+                    mloc_l += __popc(m_l); mloc_r += __popc(m_r);
+                }
             }
         };
         int stage = 0;
-        for (int ks = 0; ks < n_sup; ks++) {                      // one ring stage = SUP chunks of 32
+        for (int ks = wib; ks < n_sup; ks += WPC) {               // one ring stage = SUP chunks of 32
             mbar_wait(&S.bar[stage], (phase >> stage) & 1u);
             phase ^= 1u << stage;
             __syncwarp();                                          // every lane is done with the stage the next copy refills
             if (elect_one()) {
-                const int nxt = ks + NST - 1;
+                const int nxt = ks + (NST - 1) * WPC;
                 if (nxt < n_sup) {
                     const int ps = stage == 0 ? NST - 1 : stage - 1;      // consumed before this one
                     const unsigned bytes = 256u * (unsigned)min(SUP, n_chunks - nxt * SUP);
@@ -509,19 +609,20 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
 
         // ================= the arrivals: into the free slots, the rest behind the bucket =================
         int a_stay = 0;               // arrivals that stay, so far
-        if (n_arr) {
+        if (n_arr) {                                           // (block-uniform)
             if (st_l + st_r) { mbar_wait(&S.bar[NST], (phase >> NST) & 1u); phase ^= 1u << NST; }
-            const int n_listed = min(n_free, PUSH_FREE_CAP);
+            if constexpr (HEAVY) { __syncthreads(); n_free = H.n_free; }      // every warp has listed its free slots
+            const int n_listed = min(n_free, FREE_CAP);
             __syncwarp();                                      // the free list is complete
-            for (int k0 = 0; k0 < n_arr; k0 += 32) {
+            for (int k0 = wib * 32; k0 < n_arr; k0 += WPC * 32) {
                 const int i = k0 + lane;
                 const bool live = i < n_arr;
                 double x = 0.5, W = 0.0;
                 V3 u = {0.0, 0.0, 0.0};
                 if (live) {
                     StripRec r;
-                    if (i < n_from_l) r = i < PUSH_ARR ? S.arr[0][i] : arr_l[i];
-                    else { const int k = i - n_from_l; r = k < PUSH_ARR ? S.arr[1][k] : arr_r[k]; }
+                    if (i < n_from_l) r = i < st_l ? S.arr[0][i] : arr_l[i];
+                    else { const int k = i - n_from_l; r = k < st_r ? S.arr[1][k] : arr_r[k]; }
                     x = r.x; u = {r.ux, r.uy, r.uz}; W = r.w;
                 }
                 double xn, fl, igam, gam2;
@@ -531,9 +632,25 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                 const unsigned m_stay = __ballot_sync(FULLMASK, stay);
                 const unsigned m_l = __ballot_sync(FULLMASK, live && fl < 0.0);
                 const unsigned m_r = __ballot_sync(FULLMASK, live && fl > 0.0);
+                int ba = a_stay, bl = mloc_l, br = mloc_r;
+                if constexpr (HEAVY) {
+                    if (lane == 0) {
+                        ba = m_stay ? atomicAdd(&H.a_stay, __popc(m_stay)) : 0;
+                        bl = m_l ? atomicAdd(&H.mloc_l, __popc(m_l)) : 0;
+                        br = m_r ? atomicAdd(&H.mloc_r, __popc(m_r)) : 0;
+                    }
+                    ba = __shfl_sync(FULLMASK, ba, 0); bl = __shfl_sync(FULLMASK, bl, 0); br = __shfl_sync(FULLMASK, br, 0);
+                }
+                const bool left = fl < 0.0;
+                const int r = left ? bl + __popc(m_l & lt_mask) : br + __popc(m_r & lt_mask);
+                int rg = 0;
+                if constexpr (HEAVY) {
+                    if (bl + __popc(m_l) > MC || br + __popc(m_r) > MC)
+                        rg = reserve_spill(live && !stay && (left ? route_l : route_r) == 1 && r >= MC, n_chunks + (k0 >> 5));
+                }
                 if (stay) {
-                    const int k = a_stay + __popc(m_stay & lt_mask);
-                    const int slot = k < n_listed ? S.free_list[k] : n + (k - n_listed);     // a free slot, else appended
+                    const int k = ba + __popc(m_stay & lt_mask);
+                    const int slot = k < n_listed ? free_list[k] : n + (k - n_listed);     // a free slot, else appended
                     if (slot < cap) {
                         const long long s = base + slot;
                         fx[s] = xn; fux[s] = u.x; fuy[s] = u.y; fuz[s] = u.z; fw[s] = W;
@@ -548,28 +665,40 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                         } else atomicOr(&st->err, ERR_CAPACITY | ERR_CAP_PARKED);
                     }
                     deposit_stayer(W, u, igam, ro, xn);
-                } else if (live) {
-                    const bool left = fl < 0.0;
-                    hand_over(left, left ? mloc_l + __popc(m_l & lt_mask) : mloc_r + __popc(m_r & lt_mask), x, xn, fl, u, W, igam, gam2, n_chunks + (k0 >> 5));
+                } else if (live) hand_over(left, r, rg, x, xn, fl, u, W, igam, gam2, n_chunks + (k0 >> 5));
+                if constexpr (!HEAVY) {
+                    a_stay += __popc(m_stay);
+                    mloc_l += __popc(m_l); mloc_r += __popc(m_r);
                 }
-                a_stay += __popc(m_stay);
-                mloc_l += __popc(m_l); mloc_r += __popc(m_r);
             }
         }
 
         // ================= the cell's bookkeeping =================
-        const int n_listed = min(n_free, PUSH_FREE_CAP);
+        if constexpr (HEAVY) {
+            __syncthreads();                                       // the cell's counters are final, its strip records visible to the block
+            n_free = H.n_free; a_stay = H.a_stay; mloc_l = H.mloc_l; mloc_r = H.mloc_r;
+        }
+        const int n_listed = min(n_free, FREE_CAP);
         const int used = min(a_stay, n_listed);                   // free slots the arrivals took
         const int n_new = n + (a_stay - used);                    // slots in use now (parked demand included)
         const int holes = n_free - used;
-        if (holes > OPAL_HOLE_MAX) {
-            const int live_n = compact_cell(b, base, min(n_new, cap), lane, lt_mask);
-            if (lane == 0) { b.count[c] = live_n + (n_new - min(n_new, cap)); hcount[c] = 0; }
-        } else if (lane == 0) {
+        // (a heavy cell may carry an eighth of its slots free before its first warp closes them, one chunk at a time)
+        if (holes > (HEAVY ? max(OPAL_HOLE_MAX, n_new >> 3) : OPAL_HOLE_MAX)) {
+            if (wib == 0) {
+                const int live_n = compact_cell(b, base, min(n_new, cap), lane, lt_mask);
+                // arrivals parked because the bucket was full stay counted (count[c] is the demand the host re-lays the buckets out
+                // for); the slots that count now covers behind the live particles hold what the shift left there: mark them free
+                const int parked = n_new - min(n_new, cap);
+                const int fill_end = min(live_n + parked, cap);
+                for (int i = live_n + lane; i < fill_end; i += 32) fx[base + i] = OPAL_HOLE_MARK;
+                if (lane == 0) { b.count[c] = live_n + parked; hcount[c] = fill_end - live_n; }
+            }
+        } else if (lane == 0 && wib == 0) {
             b.count[c] = n_new; hcount[c] = holes;
         }
+        if (lane == 0 && wib == 0 && n_new > sp.heavy_hint) st->heavy_seen = 1;      // the host switches the block-per-cell launch on / off
         const int dep_l = route_l == 1 ? min(mloc_l, MC) : 0, dep_r = route_r == 1 ? min(mloc_r, MC) : 0;   // movers in this step's strips
-        if (lane == 0) {
+        if (lane == 0 && wib == 0) {
             // leavers of the slab (mod.rs:284), whatever happens to them
             if (c == 0 && mloc_l) atomicAdd(&st->gone[0], mloc_l);
             if (c == nc - 1 && mloc_r) atomicAdd(&st->gone[1], mloc_r);
@@ -584,7 +713,7 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
         if (dep_l + dep_r) {
             __syncwarp();                                          // the records written above are visible to every lane
             const StripRec* const mine_l = strips_out + ((long long)c * 2) * MC;
-            for (int k = lane; k < dep_l; k += 32) {
+            for (int k = wib * 32 + lane; k < dep_l; k += WPC * 32) {
                 const StripRec r = mine_l[k];
                 const RFaces ro = r_faces(r.prev_x), rn = r_faces(r.x);
                 const double W = r.w, tw = W * fast_rsqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0)))), ty = tw * r.uy, tz = tw * r.uz;
@@ -595,7 +724,7 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
                 er_m = fma(W, w3, er_m); sr0 = fma(W, w0, sr0); sr1 = fma(W, w1, sr1); sr2 = fma(W, w2, sr2);
             }
             const StripRec* const mine_r = mine_l + MC;
-            for (int k = lane; k < dep_r; k += 32) {
+            for (int k = wib * 32 + lane; k < dep_r; k += WPC * 32) {
                 const StripRec r = mine_r[k];
                 const RFaces ro = r_faces(r.prev_x), rn = r_faces(r.x);
                 const double W = r.w, tw = W * fast_rsqrt(fma(r.ux, r.ux, fma(r.uy, r.uy, fma(r.uz, r.uz, 1.0)))), ty = tw * r.uy, tz = tw * r.uz;

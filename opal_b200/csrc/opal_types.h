@@ -85,7 +85,8 @@ struct StatusDev {
     int halt;            // set by k_burst_check: the host has to intervene before the next kernel may run
     int step;            // steps of the burst completed so far
     int halt_species;    // the species (phase) whose advance raised the halt
-    int pad2;
+    int heavy_seen;      // lean strip kernel: some cell holds more than StepParams::heavy_hint particles
+    int strip_spill[2];  // lean strip kernel, per charged species: movers that found their cell's strip full since the block was last zeroed
     int edge[2];         // multi-slab: particles of the species just advanced that sit in the slab's first / last cell -- all that can
                          // leave through that edge in the NEXT step (|dxi| < 1): the sender sizes its outbox from it
 };
@@ -117,6 +118,10 @@ struct StepParams {
     int mover_cap, out_cap;
     int overflow_cap;        // records in the parked-mover list (destination bucket full)
     int cell_mover_cap;      // records per cell and direction in the mover strips (0: strips not in use)
+    // lean strip kernel: cells holding more than heavy_min particles are left to the block-per-cell launch that follows the
+    // one-warp-per-cell launch (INT_MAX: there is none); a cell ending the step with more than heavy_hint raises
+    // StatusDev::heavy_seen, from which the host decides whether the next steps need that second launch
+    int heavy_min, heavy_hint;
 };
 
 // one set of kernel launchers; two instances exist (fast: FMA contraction on, strict: off)

@@ -329,7 +329,19 @@ int run(const Options& opt, Ranks& ranks) {
         } else
         ck(OPAL_FN(run_steps)(ctx, (int64_t)steps_bt_output, t0, ly.data(), lz.data(), current_deposition ? 1 : 0, photon_emission ? 1 : 0, filters),
            ctx, "run_steps");                                                        // main.rs:238-267, steps_bt_output times
-        loop_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();
+        const double interval_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();
+        loop_seconds += interval_s;
+        if (id == 0 && getenv("OPAL_STATS")) {                                        // instrumentation: where a run spends its time
+            std::fprintf(stderr, "interval %zu: %zu steps in %.1f ms = %.1f us/step", i, steps_bt_output, 1e3 * interval_s, 1e6 * interval_s / (double)steps_bt_output);
+            if (atoi(getenv("OPAL_STATS")) >= 2) {                                    // per-kernel device time (the library then runs step by step)
+                double ms[3]; int64_t nl[3];
+                if (OPAL_FN(kernel_times)(ctx, ms, nl) == OPAL_OK && nl[0] > 0)
+                    std::fprintf(stderr, "; kernels per step: push %.1f us, scatter %.1f us, grid %.1f us", 1e3 * ms[0] / (double)steps_bt_output,
+                                 1e3 * ms[1] / (double)steps_bt_output, 1e3 * ms[2] / (double)steps_bt_output);
+                OPAL_FN(timing)(ctx, 1);                                              // (restarts the sums: the next interval's)
+            }
+            std::fprintf(stderr, "\n");
+        }
         particle_steps += (n_e + n_i) * (int64_t)steps_bt_output;
     }
     if (i == output_frequency) {
