@@ -234,7 +234,8 @@ opal_status OPAL_FN(hgram_bin)(opal_ctx*, int species, int ndim, const int* quan
    serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
    Same arguments and results as opal_hgram_bin, but the device-side bin counters live
    in a static device array of OPAL_HGRAM_STATIC_MAX_BINS + 1 doubles (512 KiB, held by every GPU that loads
-   the library until exit) instead of a cudaMalloc per call; the call makes no cudaMalloc / cudaFree.
+   the library until exit) instead of the scratch memory opal_hgram_bin allocates (and grows) on demand; the
+   call makes no cudaMalloc / cudaFree.
    nbins[0]*nbins[1] > OPAL_HGRAM_STATIC_MAX_BINS returns OPAL_ECAPACITY (message in opal_last_error; the
    context stays usable).  A lean-layout species whose cell hand-over is still pending (the step just run
    left movers in the strips; settling them may re-lay the buckets out, which allocates) returns

@@ -144,6 +144,7 @@ struct opal_ctx {
                                      // d_energy[4] is the electrons' current total_kinetic_energy
     double* h_energy = nullptr;      // pinned
     int* d_tmp_int = nullptr;
+    void* d_hgram = nullptr; size_t hgram_cap = 0;   // scratch of the histogram passes (grow-only: an output writes dozens of histograms)
     unsigned* d_gridbar = nullptr;   // k_grid_step's grid-wide barrier: arrival count, generation
     double* d_qed_tables = nullptr;
     int64_t last_gone[3][2] = {{0, 0}, {0, 0}, {0, 0}};
@@ -1228,7 +1229,7 @@ opal_status opal_destroy(opal_ctx* c) {
         for (int k = 0; k < NF_PHOTON; k++) if (c->ph[w].d_f[k]) cudaFree(c->ph[w].d_f[k]);
     }
     void* frees[] = {c->grid_block, c->d_movers, c->d_overflow, c->d_out[0], c->d_out[1], c->d_in[0], c->d_in[1], c->d_halo_send,
-                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_eq_slot, c->d_eq_cell, c->d_eq_n, c->d_pair[0], c->d_pair[1], c->d_pair_n, c->d_gridbar};
+                     c->d_halo_recv, c->d_status, c->d_energy, c->d_tmp_int, c->d_qed_tables, c->d_laser, c->d_hgram, c->d_eq_slot, c->d_eq_cell, c->d_eq_n, c->d_pair[0], c->d_pair[1], c->d_pair_n, c->d_gridbar};
     for (void* p : frees) if (p) cudaFree(p);
     for (int sp = 0; sp < 2; sp++) {
         for (int k = 0; k < 2; k++) { if (c->lean[sp].d_strips[k]) cudaFree(c->lean[sp].d_strips[k]); if (c->lean[sp].d_scount[k]) cudaFree(c->lean[sp].d_scount[k]); }
@@ -1762,6 +1763,17 @@ opal_status opal_run_steps(opal_ctx* c, int64_t nsteps, double t0, const double*
     return (opal_status)c->status;
 }
 
+static void* hgram_scratch(opal_ctx* c, size_t bytes) {
+    if (bytes > c->hgram_cap) {
+        if (c->d_hgram) cudaFree(c->d_hgram);
+        c->d_hgram = nullptr; c->hgram_cap = 0;
+        const size_t want = std::max<size_t>(bytes, 1 << 20);
+        if (cudaMalloc(&c->d_hgram, want) != cudaSuccess) { fail(c, OPAL_ENOMEM, "histogram scratch"); return nullptr; }
+        c->hgram_cap = want;
+    }
+    return c->d_hgram;
+}
+
 static bool hgram_args_ok(int species, int ndim, const int* q) {
     if (species < 0 || species > 2 || (ndim != 1 && ndim != 2) || !q) return false;
     for (int d = 0; d < ndim; d++) if (q[d] < 0 || q[d] >= OPAL_Q_COUNT_) return false;
@@ -1775,8 +1787,8 @@ opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, 
     for (int d = 0; d < ndim; d++) { mn[d] = std::numeric_limits<double>::max(); mx[d] = -std::numeric_limits<double>::max(); }   // hgram.rs:189
     opal_status st = opal_particles_count(c, species, n);
     if (st != OPAL_OK || *n == 0) return st;
-    unsigned long long* d_mm = nullptr;
-    CU(cudaMalloc(&d_mm, 4 * sizeof(unsigned long long) + 4 * sizeof(double)));
+    unsigned long long* d_mm = static_cast<unsigned long long*>(hgram_scratch(c, 4 * sizeof(unsigned long long) + 4 * sizeof(double)));
+    if (!d_mm) return (opal_status)c->status;
     double* d_out = reinterpret_cast<double*>(d_mm + 4);
     if (species == OPAL_PHOTON) hgram_minmax_photon(c->stream, c->g, pdev(c, c->ph_cur), ndim, q, lg, d_mm, d_out);
     else hgram_minmax_charged(c->stream, c->g, bdev(c, species), species, c->bk[species].full, ndim, q, lg, d_mm, d_out);
@@ -1784,7 +1796,6 @@ opal_status opal_hgram_minmax(opal_ctx* c, int species, int ndim, const int* q, 
     double h[4];
     CU(cudaMemcpyAsync(h, d_out, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    cudaFree(d_mm);
     for (int d = 0; d < ndim; d++) { mn[d] = h[2 * d]; mx[d] = h[2 * d + 1]; }
     return OPAL_OK;
 }
@@ -1808,8 +1819,8 @@ opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, con
     int64_t n = 0;
     opal_status st = opal_particles_count(c, species, &n);
     if (st != OPAL_OK || n == 0) return st;
-    double* d_counts = nullptr;
-    CU(cudaMalloc(&d_counts, (len + 1) * sizeof(double)));
+    double* d_counts = static_cast<double*>(hgram_scratch(c, (len + 1) * sizeof(double)));
+    if (!d_counts) return (opal_status)c->status;
     CU(cudaMemsetAsync(d_counts, 0, (len + 1) * sizeof(double), c->stream));
     if (species == OPAL_PHOTON) hgram_bin_photon(c->stream, c->g, pdev(c, c->ph_cur), ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust, d_counts, d_counts + len);
     else hgram_bin_charged(c->stream, c->g, bdev(c, species), species, c->bk[species].full, ndim, q, lg, gmin, bin_sz, nb, weight_kind, log_density_adjust,
@@ -1818,12 +1829,11 @@ opal_status opal_hgram_bin(opal_ctx* c, int species, int ndim, const int* q, con
     CU(cudaMemcpyAsync(counts, d_counts, len * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaMemcpyAsync(total, d_counts + len, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
-    cudaFree(d_counts);
     return OPAL_OK;
 }
 
 // ---- opal_hgram_bin_static: opal_hgram_bin for callers that may not allocate (no counterpart in the reference).
-// The bin counters -- what opal_hgram_bin cudaMallocs per call -- live in a file-scope device
+// request of the run's operators).  The bin counters -- which opal_hgram_bin keeps in scratch memory it cudaMallocs (and grows) on demand -- live in a file-scope device
 // array that every GPU loading the library holds until exit.  Its NAME is a host-side stand-in in this host code, not a device
 // address: the device address is looked up once per device with cudaGetSymbolAddress (that device current) and passed to the
 // kernels like any other pointer.  All calls share the array (it keeps the last call's counts: cleared on the stream before

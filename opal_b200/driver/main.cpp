@@ -220,8 +220,11 @@ int run(const Options& opt, Ranks& ranks) {
         std::printf("Running %d task%s on %d GPU%s (libopal_b200: one x-slab per GPU)...\n", np, np > 1 ? "s" : "", np, np > 1 ? "s" : "");
 #endif
 
+    double output_seconds = 0.0, grid_seconds = 0.0;
     auto write_all = [&](size_t index) {                                             // main.rs:218-222
+        const auto w0 = std::chrono::steady_clock::now();
         write_grid(ctx, output_dir, index, ranks);
+        grid_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
         write_population(ctx, OPAL_ELECTRON, "electron", eospec, output_dir, index, ranks);
         if (ipc > 0) write_population(ctx, OPAL_ION, ion_name, iospec, output_dir, index, ranks);
         if (pair_creation) write_population(ctx, OPAL_ION, "positron", eospec, output_dir, index, ranks);
@@ -233,6 +236,7 @@ int run(const Options& opt, Ranks& ranks) {
             if (pair_creation) dump_species(ctx, OPAL_ION, "positron", output_dir, index, id);
             if (photons_on) dump_species(ctx, OPAL_PHOTON, "photon", output_dir, index, id);
         }
+        output_seconds += std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
     };
 
     double filters[3];
@@ -355,6 +359,8 @@ int run(const Options& opt, Ranks& ranks) {
     ranks.sum(ps, 1);
     if (id == 0 && !opt.quiet && loop_seconds > 0.0)
         std::printf("time loop: %.3f s, %.4e charged-particle-steps/s\n", loop_seconds, ps[0] / loop_seconds);
+    if (id == 0 && getenv("OPAL_STATS"))
+        std::fprintf(stderr, "outputs: %.3f s (grid files %.3f s), whole run since the first output: %.3f s\n", output_seconds, grid_seconds, std::chrono::duration<double>(std::chrono::steady_clock::now() - wall0).count());
     OPAL_FN(destroy)(ctx);
     return 0;
 }

@@ -36,17 +36,28 @@ std::string special(double v) {
 
 }  // namespace
 
+// {:e} appended to `out` without a temporary per number (a grid file is 11 numbers on each of nx lines, every output):
+// std::to_chars' shortest scientific form is Rust's but for the exponent, which Rust prints without '+' and without padding
+void append_lower_exp(std::string& out, double v) {
+    if (!std::isfinite(v)) { out += special(v); return; }
+    if (v == 0.0) { out += std::signbit(v) ? "-0e0" : "0e0"; return; }
+    char buf[48];
+    const auto r = std::to_chars(buf, buf + sizeof buf, v, std::chars_format::scientific);
+    const char* e = r.ptr - 1;
+    while (e > buf && *e != 'e') e--;
+    out.append(buf, (size_t)(e - buf));
+    out += 'e';
+    const char* p = e + 1;
+    if (*p == '-') out += '-';
+    if (*p == '-' || *p == '+') p++;
+    while (*p == '0' && p + 1 < r.ptr) p++;
+    out.append(p, (size_t)(r.ptr - p));
+}
+
 std::string fmt_lower_exp(double v) {
-    if (!std::isfinite(v)) return special(v);
-    std::string sign = std::signbit(v) ? "-" : "";
-    v = std::fabs(v);
-    if (v == 0.0) return sign + "0e0";
-    std::string d;
-    int e;
-    shortest_digits(v, &d, &e);
-    std::string out = sign + d.substr(0, 1);
-    if (d.size() > 1) out += "." + d.substr(1);
-    return out + "e" + std::to_string(e);
+    std::string out;
+    append_lower_exp(out, v);
+    return out;
 }
 
 std::string fmt_lower_exp6(double v) {

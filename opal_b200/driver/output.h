@@ -16,6 +16,7 @@ namespace opal_driver {
 
 // Rust's float formatting, used by every text output of the reference
 std::string fmt_lower_exp(double v);              // {:e}   shortest round-trip digits, e.g. 1.5e-7, 0e0
+void append_lower_exp(std::string& out, double v);  // the same, appended
 std::string fmt_lower_exp6(double v);             // {:.6e} e.g. 1.200135e-6
 std::string fmt_display(double v);                // {}     shortest round-trip digits, positional, e.g. 0.00015
 std::string fmt_simulation_time(double seconds);  // SimulationTime (setup.rs:417-437): "{: >8.2} unit", nearest SI prefix from as to s

@@ -131,14 +131,14 @@ void write_grid(opal_ctx* ctx, const std::string& dir, size_t index, Reducer& re
     if (red.rank() != 0) return;
     std::ofstream f(dir + "/" + std::to_string(index) + "_grid.dat", std::ios::trunc);
     if (!f) throw std::runtime_error("cannot create grid output in " + dir);
-    std::string line;
+    std::string text;                                                               // the whole file, written once
+    text.reserve(global.size() * 12);
     for (size_t i = 0; i + OPAL_CELL_DOUBLES <= global.size(); i += OPAL_CELL_DOUBLES) {   // yee.rs:765-775: ten {:e} and a final {}
-        line.clear();
-        for (int k = 0; k < 10; k++) { line += fmt_lower_exp(global[i + k]); line += ' '; }
-        line += fmt_display(global[i + 10]);
-        line += '\n';
-        f << line;
+        for (int k = 0; k < 10; k++) { append_lower_exp(text, global[i + k]); text += ' '; }
+        text += fmt_display(global[i + 10]);
+        text += '\n';
     }
+    f.write(text.data(), (std::streamsize)text.size());
 }
 
 void write_energies(opal_ctx* ctx, const std::string& dir, size_t index, Reducer& red) {

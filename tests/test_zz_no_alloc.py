@@ -1,7 +1,7 @@
 """opal_hgram_bin_static: the entry point for callers that may not allocate device memory (no counterpart in the reference
 -- include/opal_b200.h).  Its bin counters live in a static device array shared
 by every call on a GPU, so the checks that matter are: same output as opal_hgram_bin (the existing entry point, which
-cudaMallocs its counters) on CALLS IN A ROW that differ in shape -- anything a call leaves in the array must not leak into
+allocates its counters on demand) on CALLS IN A ROW that differ in shape -- anything a call leaves in the array must not leak into
 the next one -- and a clear refusal beyond the stated maximum.
 
 This file sorts last on purpose (pytest -x at the end of a round stops at the first failure)."""
