@@ -20,6 +20,8 @@
 // the last step wait in the strips.  Anything other than this kernel sees the buckets only after k_strip_flush +
 // k_compact_cells (host: settle).  A cell whose free slots exceed OPAL_HOLE_MAX shifts its live particles down
 // itself (rare: arrivals fill the slots departures open; the excess random-walks).
+// A cell of thousands of particles is one warp's serial work (~11 us per 1000): above StepParams::heavy_min a cell is left to a
+// second launch of this kernel (HEAVY) in which a whole block shares it -- see HeavyShared below.
 // At a slab edge: a leaver through an open boundary is dropped (mod.rs:372-373); towards a neighbour slab it goes
 // straight into the outbox (the receiver deposits it in its own frame); on a periodic single slab it is an ordinary mover.
 //
