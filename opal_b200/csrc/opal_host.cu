@@ -102,6 +102,7 @@ struct opal_ctx {
     KernelTable k;
     GridDev g;              // current E/B buffers
     double* eb_alt[6] = {nullptr};   // the other half of the E/B ping-pong
+    double* j_alt[4] = {nullptr};    // a second set of rho, jx, jy, jz: in a burst the grid launch of step k clears the set step k + 1 deposits into
     double* grid_block = nullptr;    // one allocation for all grid arrays
     Buckets bk[2];          // electrons, ions
     Buckets spare[2];       // the arrays the last re-layout of each moved out of: the next one moves into them (alloc_buckets)
@@ -988,6 +989,11 @@ void swap_fields(opal_ctx* c) {
     for (int k = 0; k < 6; k++) std::swap(*cur[k], c->eb_alt[k]);
 }
 
+void swap_sources(opal_ctx* c) {
+    double** cur[4] = {&c->g.rho, &c->g.jx, &c->g.jy, &c->g.jz};
+    for (int k = 0; k < 4; k++) std::swap(*cur[k], c->j_alt[k]);
+}
+
 // what one iteration of main.rs:238-267 consists of; the phases run in this order
 struct StepCfg {
     bool dep = true, emit = false;
@@ -999,6 +1005,16 @@ enum { PH_ELECTRONS = 0, PH_IONS = 1, PH_PHOTONS = 2, PH_ABSORB = 3, PH_EMIT_ROO
 // One iteration of main.rs:238-267 without the host in the loop (one slab), as few launches as the phases allow: the check
 // of an advance (parked movers, asserts, mover segments filling up) rides on the next kernel of the step (GridDev::prev_phase)
 // or shares a launch with the next species' begin-mark (burst_mark 3); the begin-mark of the first species rides on k_clear.
+// Bursts whose steps end in the one-launch grid step: that launch also clears the source arrays of the NEXT step (a second set:
+// opal_ctx::j_alt) and zeroes its per-advance counters, so no step of the burst begins with a clear launch of its own
+// (run_burst clears for the first one).
+bool clear_rides_on_grid_step(opal_ctx* c, const StepCfg& cfg) {
+    const int last_sp = c->bk[1].allocated ? 1 : (c->bk[0].allocated ? 0 : -1);
+    const bool photons_move = c->ph[0].cap > 0 && !(c->flags & OPAL_FLAG_IMMOBILE_PHOTONS);
+    const bool emit = cfg.emit && c->bk[OPAL_ELECTRON].allocated;
+    return cfg.fused() && !photons_move && !emit && last_sp >= 0 && env_ll("OPAL_GRID_FUSED", 1) != 0 && env_ll("OPAL_CLEAR_FUSED", 1) != 0;
+}
+
 // Returns the launch count.
 int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
     int n = 0;
@@ -1013,7 +1029,9 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
     int* ph_dst_n = photons_move ? c->ph[1 - c->ph_cur].d_n : nullptr;      // emptied by the first begin-mark of the step
     auto gdev = [&](int prev_phase, int count_step) { GridDev g = c->g; g.prev_phase = prev_phase; g.count_step = count_step; g.seg_cap = c->mover_seg_cap; return g; };
     bool cleared_with_mark = false;
-    if (cfg.dep) { c->k.clear(c->stream, c->g, last_sp >= 0 ? c->d_status : nullptr); n++; cleared_with_mark = last_sp >= 0; }
+    const bool clear_rides = clear_rides_on_grid_step(c, cfg);
+    if (clear_rides) cleared_with_mark = true;       // by the grid launch of the step before (the first step: by run_burst)
+    else if (cfg.dep) { c->k.clear(c->stream, c->g, last_sp >= 0 ? c->d_status : nullptr); n++; cleared_with_mark = last_sp >= 0; }
     for (int sp = 0; sp < 2; sp++) {
         Buckets& B = c->bk[sp];
         if (!B.allocated) continue;
@@ -1057,7 +1075,8 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
     GridDev nxt = c->g;
     nxt.ex = c->eb_alt[0]; nxt.ey = c->eb_alt[1]; nxt.ez = c->eb_alt[2]; nxt.bx = c->eb_alt[3]; nxt.by = c->eb_alt[4]; nxt.bz = c->eb_alt[5];
     if (one_grid_launch) {
-        c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar, c->mover_seg_cap);
+        if (clear_rides) { nxt.rho = c->j_alt[0]; nxt.jx = c->j_alt[1]; nxt.jy = c->j_alt[2]; nxt.jz = c->j_alt[3]; }
+        c->k.grid_step(c->stream, c->g, nxt, c->d_status, last_sp, c->d_gridbar, c->mover_seg_cap, clear_rides);
         n++;
     } else {
         c->k.sync_bc(c->stream, gdev(pend, 0), nullptr, 0.0, 0.0, nullptr);
@@ -1065,6 +1084,7 @@ int enqueue_step(opal_ctx* c, const StepCfg& cfg, uint64_t emit_call0) {
         n += 2;
     }
     c->eb_alt[0] = c->g.ex; c->eb_alt[1] = c->g.ey; c->eb_alt[2] = c->g.ez; c->eb_alt[3] = c->g.bx; c->eb_alt[4] = c->g.by; c->eb_alt[5] = c->g.bz;
+    if (clear_rides) { c->j_alt[0] = c->g.rho; c->j_alt[1] = c->g.jx; c->j_alt[2] = c->g.jy; c->j_alt[3] = c->g.jz; }
     c->g = nxt;
     return n;
 }
@@ -1094,6 +1114,8 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     const int parity0[2] = {c->lean[0].parity, c->lean[1].parity};     // two captured steps leave the strip parity where it was
     const int ph_cur0 = c->ph_cur;                                     // ... and the photon ping-pong
     const uint64_t emit_call0 = c->emit_calls;
+    const bool clear_rides = clear_rides_on_grid_step(c, cfg);
+    if (clear_rides) { c->k.clear(c->stream, c->g, c->d_status); c->launches++; }      // the first step's; every later one's rides on a grid launch
     const double tg0 = wall_now();
     cudaError_t e = cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal);
     if (e == cudaSuccess) {
@@ -1131,7 +1153,7 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     { const double td0 = wall_now(); cudaGraphExecDestroy(exec); cudaGraphDestroy(graph); c->t_graph += wall_now() - td0; }
     leave();
     c->burst_steps += *done;
-    if (ok && (*done & 1)) swap_fields(c);       // an odd number of steps ran: the fields sit in the other buffer set
+    if (ok && (*done & 1)) { swap_fields(c); if (clear_rides) swap_sources(c); }      // an odd number of steps ran: the fields (and sources) sit in the other buffer set
     const int hphase = *halted ? c->h_status->halt_species : -1;   // the phase of the half-finished step that raised the halt
     for (int sp = 0; sp < 2; sp++) {
         // pushes of this species that ran: one per completed step, plus the half-finished step up to the halting phase
@@ -1182,12 +1204,13 @@ opal_status opal_create(opal_ctx** out, int device, int64_t nx, double xmin, dou
     else { g.right_bdy = OPAL_BDY_INTERNAL; g.right = OPAL_GHOST_SIZE; }
     g.len = g.nx + g.left + g.right;
     const size_t n = (size_t)g.len;
-    CU(cudaMalloc(&c->grid_block, 16 * n * sizeof(double)));
-    CU(cudaMemsetAsync(c->grid_block, 0, 16 * n * sizeof(double), c->stream));
+    CU(cudaMalloc(&c->grid_block, 20 * n * sizeof(double)));
+    CU(cudaMemsetAsync(c->grid_block, 0, 20 * n * sizeof(double), c->stream));
     double* p = c->grid_block;
     g.rho = p; g.jx = p + n; g.jy = p + 2 * n; g.jz = p + 3 * n;
     g.ex = p + 4 * n; g.ey = p + 5 * n; g.ez = p + 6 * n; g.bx = p + 7 * n; g.by = p + 8 * n; g.bz = p + 9 * n;
     for (int k = 0; k < 6; k++) c->eb_alt[k] = p + (10 + k) * n;
+    for (int k = 0; k < 4; k++) c->j_alt[k] = p + (16 + k) * n;
     CU(cudaMalloc(&c->d_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int)));
     CU(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
     CU(cudaMallocHost(&c->h_status, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int)));

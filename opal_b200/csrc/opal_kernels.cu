@@ -1077,8 +1077,11 @@ __device__ __forceinline__ bool segments_filling(const StatusDev* st, int mover_
 // a grid-wide barrier, B/2 - E - B/2 (yee.rs:345-349) over the tiles, and the step counter.  At most 148 blocks of FT
 // threads with < 9 KB of shared memory each: all resident at once, so the spin barrier cannot starve (it still gives up
 // after ~1 s and raises ERR_INDEX rather than hang the device).
+// clear_next: o.rho / o.j* are the OTHER set of source arrays (the host alternates two, like E and B): the next step deposits
+// there, so this launch also does that step's Grid::clear (yee.rs:543) and begin-mark -- nobody reads that set now -- and a
+// replayed step of one lean species is three launches (push, scatter, this).
 __global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDev* st, int last_species, unsigned* bar /* count, generation */,
-                                                  int mover_cap) {
+                                                  int mover_cap, int clear_next) {
     if (*(volatile const int*)&st->halt) return;
     const bool filling = segments_filling(st, mover_cap, threadIdx.x, blockDim.x);
     if (st->n_overflow > 0 || st->err || filling) {       // the same for every block: nobody advances the fields
@@ -1100,6 +1103,15 @@ __global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDe
         __syncthreads();
     }
     for (int t0 = blockIdx.x * FT; t0 < g.len; t0 += gridDim.x * FT) field_tile(g, o, t0);
+    if (clear_next) {
+        for (int i = blockIdx.x * FT + threadIdx.x; i < g.len; i += gridDim.x * FT) { o.rho[i] = 0.0; o.jx[i] = 0.0; o.jy[i] = 0.0; o.jz[i] = 0.0; }
+        if (blockIdx.x == 0) {                                  // (what k_clear does with st != null; the check above has looked at them)
+            __syncthreads();                                    // every thread of this block is past segments_filling
+            int* seg = reinterpret_cast<int*>(st + 1);
+            for (int i = threadIdx.x; i < OPAL_MOVER_SEGMENTS; i += blockDim.x) seg[i] = 0;
+            if (threadIdx.x == 0) { st->n_movers = 0; st->n_overflow = 0; st->n_out[0] = st->n_out[1] = 0; st->gone[0] = st->gone[1] = 0; st->n_new_photons = 0; }
+        }
+    }
     if (blockIdx.x == 0 && threadIdx.x == 0) st->step = st->step + 1;     // (read only by the kernels of the next step)
 }
 
@@ -1476,10 +1488,10 @@ static void l_clear(cudaStream_t s, const GridDev& g, StatusDev* st_begin_mark) 
     if (grid > 148 * 8) grid = 148 * 8;
     k_clear<<<grid, 256, 0, s>>>(g, st_begin_mark);
 }
-static void l_grid_step(cudaStream_t s, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* bar, int mover_cap) {
+static void l_grid_step(cudaStream_t s, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* bar, int mover_cap, bool clear_next) {
     int grid = (cur.len + FT - 1) / FT;
     if (grid > 148) grid = 148;
-    k_grid_step<<<grid, FT, 0, s>>>(cur, nxt, st, last_species, bar, mover_cap);
+    k_grid_step<<<grid, FT, 0, s>>>(cur, nxt, st, last_species, bar, mover_cap, clear_next ? 1 : 0);
 }
 static void l_halo_pack(cudaStream_t s, const GridDev& g, double* out) { k_halo_pack<<<1, 192, 0, s>>>(g, out); }
 

@@ -152,7 +152,8 @@ struct KernelTable {
     void (*field)(cudaStream_t, const GridDev& cur, const GridDev& nxt, bool zero_next_j);
     void (*clear)(cudaStream_t, const GridDev&, StatusDev* begin_mark /* bursts: also zero the per-advance counters; else null */);
     // bursts on one slab: check of the last advance + halo/BC + field update + step counter in one launch (k_grid_step)
-    void (*grid_step)(cudaStream_t, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* barrier2, int mover_cap);
+    // clear_next: nxt's rho / j arrays are the other source set; clear them and zero the per-advance counters for the next step
+    void (*grid_step)(cudaStream_t, const GridDev& cur, const GridDev& nxt, StatusDev* st, int last_species, unsigned* barrier2, int mover_cap, bool clear_next);
     void (*halo_pack)(cudaStream_t, const GridDev&, double* out2x8x11);
     void (*energy)(cudaStream_t, const GridDev&, const BucketDev* electrons, const BucketDev* ions, const PhotonDev* photons,
                    bool full, double* out4);
