@@ -124,6 +124,7 @@ struct opal_ctx {
         int parity = 0;           // the buffer the NEXT push reads
         bool pending = false;     // movers of the last push wait in d_strips[parity] (not yet in the buckets)
         bool holes = false;       // the buckets carry free slots (count[] counts slots in use)
+        bool range_on = false; int c_begin = 0, c_end = 0;   // inside a burst: the cells the push launch covers (BucketDev::c_begin)
         int mc_floor = 0;         // strips at least this wide: raised when movers keep finding them full (maybe_widen_strips)
         long long spill = 0, spill_adv = 0;   // movers that did, and the advances they were counted over
     } lean[2];
@@ -202,6 +203,10 @@ BucketDev bdev(opal_ctx* c, int sp) {
     BucketDev b;
     Buckets& B = c->bk[sp];
     b.ncell = c->g.nx; b.start = B.d_start; b.count = B.d_count;
+    b.c_begin = 0; b.c_end = b.ncell;
+    if ((sp == OPAL_ELECTRON || sp == OPAL_ION) && c->lean[sp].range_on && c->g.halt) {       // (set for the launches of a burst only)
+        b.c_begin = c->lean[sp].c_begin; b.c_end = c->lean[sp].c_end;
+    }
     for (int k = 0; k < NF_FULL; k++) b.f[k] = B.d_f[k];
     b.z_star = c->z_star; b.mass_number = c->mass_number;
     if (sp == OPAL_ELECTRON && c->eq_on && c->d_eq_n) { b.eq_slot = c->d_eq_slot; b.eq_cell = c->d_eq_cell; b.eq_n = c->d_eq_n; b.eq_cap = c->eq_cap; }
@@ -643,6 +648,15 @@ __global__ void k_burst_zero_int(const StatusDev* st, int* p) {
     if (threadIdx.x == 0 && !*(volatile const int*)&st->halt) *p = 0;
 }
 // live particles of a species: sum of count[] (out must be zeroed)
+// first and last non-empty cell of a species (out[0] = min index, out[1] = max index; preset to INT_MAX / -1)
+__global__ void __launch_bounds__(256) k_occupied_range(const int* __restrict__ count, int ncell, int* out) {
+    int lo = INT_MAX, hi = -1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ncell; i += gridDim.x * blockDim.x)
+        if (count[i] > 0) { lo = min(lo, i); hi = max(hi, i); }
+    for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+    if ((threadIdx.x & 31) == 0 && hi >= 0) { atomicMin(out, lo); atomicMax(out + 1, hi); }
+}
+
 __global__ void __launch_bounds__(256) k_total_count(const int* __restrict__ count, int ncell, unsigned long long* out) {
     unsigned long long acc = 0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < ncell; i += gridDim.x * blockDim.x) acc += (unsigned long long)count[i];
@@ -1105,9 +1119,34 @@ bool run_burst(opal_ctx* c, const StepCfg& cfg, int64_t n, double t0, const doub
     { double t = t0; for (int64_t k = 0; k < n; k++) { lh[3 * k] = ly ? ly[k] : 0.0; lh[3 * k + 1] = lz ? lz[k] : 0.0; lh[3 * k + 2] = t; t += c->g.dt; } }
     CUB(cudaMemcpyAsync(c->d_laser, lh.data(), lh.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
     CUB(cudaMemsetAsync(c->d_status, 0, sizeof(StatusDev) + OPAL_MOVER_SEGMENTS * sizeof(int), c->stream));
+    // Where are the particles?  The lean push launches one block per cell; a target that fills a quarter of the grid need not
+    // pay for the vacuum around it.  A particle moves less than a cell per step, so nothing leaves [first - n, last + n] within
+    // the n steps of this burst (+ 4: the movers waiting in the strips, and the cells that emptied in the last two steps and
+    // still have to write their empty strip counts).  A range that touches a periodic edge is not restricted.
+    int h_range[4] = {INT_MAX, -1, INT_MAX, -1};
+    const bool restrict_ok = cfg.fused() && env_ll("OPAL_PUSH_RANGE", 1) != 0;
+    if (restrict_ok) {
+        CUB(cudaMemcpyAsync(c->d_tmp_int + 4, h_range, sizeof(h_range), cudaMemcpyHostToDevice, c->stream));
+        for (int sp = 0; sp < 2; sp++) if (c->bk[sp].allocated && c->lean[sp].d_hcount) {
+            int gr = (c->g.nx + 255) / 256; if (gr > 148 * 4) gr = 148 * 4;
+            k_occupied_range<<<gr, 256, 0, c->stream>>>(c->bk[sp].d_count, c->g.nx, c->d_tmp_int + 4 + 2 * sp); c->launches++;
+        }
+        CUB(cudaMemcpyAsync(h_range, c->d_tmp_int + 4, sizeof(h_range), cudaMemcpyDeviceToHost, c->stream));
+    }
     CUB(cudaStreamSynchronize(c->stream));
+    for (int sp = 0; sp < 2; sp++) {
+        opal_ctx::Lean& L = c->lean[sp];
+        L.range_on = false;
+        if (!restrict_ok || !c->bk[sp].allocated || !L.d_hcount || h_range[2 * sp + 1] < 0) continue;
+        const long long lo = (long long)h_range[2 * sp] - n - 4, hi = (long long)h_range[2 * sp + 1] + n + 4;
+        const bool wraps = c->self_nbr() && c->has_left();                       // periodic single slab: the two edges are neighbours
+        if (wraps && (lo <= 0 || hi >= c->g.nx - 1)) continue;
+        L.c_begin = (int)std::max<long long>(lo, 0); L.c_end = (int)std::min<long long>(hi + 1, c->g.nx);
+        L.range_on = L.c_end - L.c_begin < c->g.nx;
+    }
     c->g.halt = &c->d_status->halt; c->g.step = &c->d_status->step; c->g.laser_arr = c->d_laser; c->g.bst = c->d_status;
-    auto leave = [&]() { c->g.halt = nullptr; c->g.step = nullptr; c->g.laser_arr = nullptr; c->g.bst = nullptr; c->g.prev_phase = -1; c->g.count_step = 0; };
+    auto leave = [&]() { c->g.halt = nullptr; c->g.step = nullptr; c->g.laser_arr = nullptr; c->g.bst = nullptr; c->g.prev_phase = -1; c->g.count_step = 0;
+                         c->lean[0].range_on = false; c->lean[1].range_on = false; };
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int per_step = 0;

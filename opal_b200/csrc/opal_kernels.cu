@@ -1323,7 +1323,7 @@ static bool l_push(cudaStream_t s, const GridDev& g, const BucketDev& b, const S
     const int grid = cell_grid(b.ncell);
 #ifdef OPAL_FAST
     if ((sp.species == OPAL_ELECTRON || sp.species == OPAL_ION) && !full && dep && ls && sp.cell_mover_cap > 0) {
-        long long blocks = ((long long)b.ncell + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
+        long long blocks = ((long long)(b.c_end - b.c_begin) + OPAL_PUSH_WPB - 1) / OPAL_PUSH_WPB;
         const int gr = (int)(blocks < 1 ? 1 : blocks);
         const int smem = OPAL_PUSH_WPB * (int)sizeof(PushScratch);
         // (the attribute is per device and contexts may live on several devices: set on every launch, a cheap host-side call)

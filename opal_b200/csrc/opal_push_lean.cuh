@@ -336,7 +336,10 @@ k_push_lean_fast(GridDev g, BucketDev b, StepParams sp, opal_migrant* __restrict
             }
         }
     };
-    for (int c = HEAVY ? next_heavy() : (int)(blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5)); c < nc; c = HEAVY ? next_heavy() : c + warps_total) {
+    // (the one-warp launch covers the cells [c_begin, c_end) the host vouches for -- all of them outside a burst; next_heavy() ends
+    //  with nc >= c_end)
+    const int c_end = HEAVY ? nc : b.c_end;
+    for (int c = HEAVY ? next_heavy() : b.c_begin + (int)(blockIdx.x * OPAL_PUSH_WPB + (threadIdx.x >> 5)); c < c_end; c = HEAVY ? next_heavy() : c + warps_total) {
         const long long base = b.start[c];
         const int cap = (int)(b.start[c + 1] - base);
         const int n = min(b.count[c], cap);

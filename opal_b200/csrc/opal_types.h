@@ -50,6 +50,10 @@ struct BucketDev {
     int* count;
     double* f[NF_FULL];
     double z_star, mass_number;     // ions (ion.rs:236)
+    // lean strip kernel inside a burst: the cells the one-warp-per-cell launch covers, [c_begin, c_end).  Everything outside is
+    // empty, has empty strips in both buffers, and cannot be reached before the burst ends (a particle moves less than a
+    // cell per step): host, run_burst.  Every other kernel, and every launch outside a burst, covers [0, ncell).
+    int c_begin = 0, c_end = 0;
     // Emitter queue (electrons, full state, emission inside opal_run_steps; null otherwise): the push and the scatter that
     // precede emit_radiation in a step know which electrons' optical depth has run out (electron.rs:209) and where they ended
     // up -- they list (slot, cell), and k_emit samples exactly those with every lane busy instead of scanning tau of all.

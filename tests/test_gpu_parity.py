@@ -381,3 +381,26 @@ def test_lean_ions_fast_boris_kernel(gpu, oracle, bx):
         pc.compare_fields(a.fields(), b.fields())
         _same_energies(a, b)
     assert a.count(ION) == nx * 40 and a.count(ELECTRON) == nx * 60
+
+
+@pytest.mark.parametrize("bounds", ["periodic", "open"])
+def test_lean_bursts_launch_only_where_particles_can_be(gpu, oracle, bounds):
+    """Inside a graph-replayed burst the lean push covers the occupied cells plus as many cells as the burst has steps
+    (opal_host.cu: run_burst).  A hot slab in the middle of a mostly empty grid expands at ~0.9 cells per step through several
+    bursts; the last chunk lets it reach (and, periodic, wrap around) the edges, where the restriction must switch itself off."""
+    nx, dx = 640, 500.0
+    lr = (BDY_INTERNAL, BDY_INTERNAL) if bounds == "periodic" else (BDY_LASER, BDY_ABSORBING)
+    a, b = _pair(gpu, oracle, nx, 0.0, dx, lr[0], lr[1], flags=FLAG_LEAN_STATE)
+    p = pc.thermal_particles(nx, 80, dx, 2.5, seed=9, cells=np.arange(300, 330), ne=2.0e-3)      # (thin: it streams, it does not explode)
+    pc.upload(a, ELECTRON, p)
+    pc.upload(b, ELECTRON, p)
+    for chunk in (7, 60, 150, 200):
+        a.run_steps(chunk)
+        b.run_steps(chunk)
+        assert a.count(ELECTRON) == b.count(ELECTRON)
+        pc.compare_particles(a.download(ELECTRON), b.download(ELECTRON), fields=("x", "ux", "uy", "uz"))
+        pc.compare_fields(a.fields(), b.fields())
+        assert a.last_leavers(ELECTRON) == b.last_leavers(ELECTRON)
+        _same_energies(a, b)
+    cells = b.download(ELECTRON)["cell"]
+    assert cells.min() < 20 and cells.max() > nx - 20          # the plasma did get to the edges
