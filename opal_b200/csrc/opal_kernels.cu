@@ -1004,6 +1004,12 @@ __device__ __forceinline__ void field_tile(const GridDev& g, const GridDev& o, c
     __syncthreads();                                      // (a block that walks several tiles re-uses the staging arrays)
     const int len = g.len;
     const double hdt = 0.5 * g.dt;
+    // the sources and E_x of the E step below: asked for now, so that their latency overlaps the staging (a small grid is a few
+    // blocks, and this kernel is then a chain of memory round trips).  Thread 0 also does the one cell beyond the tile.
+    const int ia = t0 + tid, ib = t0 + FT;
+    double jx_a = 0.0, jy_a = 0.0, jz_a = 0.0, ex_a = 0.0, jy_b = 0.0, jz_b = 0.0;
+    if (ia < len) { jx_a = g.jx[ia]; jy_a = g.jy[ia]; jz_a = g.jz[ia]; ex_a = g.ex[ia]; }
+    if (tid == 0 && ib < len) { jy_b = g.jy[ib]; jz_b = g.jz[ib]; }
     // stage E (t0-1 .. t0+FT+1) and B (t0-1 .. t0+FT)
     for (int k = tid; k < FT + 3; k += FT) {
         const int i = t0 - 1 + k;
@@ -1035,9 +1041,10 @@ __device__ __forceinline__ void field_tile(const GridDev& g, const GridDev& o, c
                 const double ez = sigma * s_ez[k] + OPAL_C * kappa * s_by[k];
                 s_ey[k] = ey; s_ez[k] = ez;
             } else {
-                if (k <= FT) ex_new = g.ex[i] + -g.dt * g.jx[i] / OPAL_EPS0;
-                const double ey = s_ey[k] + (g.dt * OPAL_C_SQD * (s_bz[k - 1] - s_bz[k]) / g.dx - g.dt * g.jy[i] / OPAL_EPS0);
-                const double ez = s_ez[k] + (g.dt * OPAL_C_SQD * (s_by[k] - s_by[k - 1]) / g.dx - g.dt * g.jz[i] / OPAL_EPS0);
+                const bool own = k <= FT;                  // i == ia (this thread's cell of the tile); else i == ib (thread 0)
+                if (own) ex_new = ex_a + -g.dt * jx_a / OPAL_EPS0;
+                const double ey = s_ey[k] + (g.dt * OPAL_C_SQD * (s_bz[k - 1] - s_bz[k]) / g.dx - g.dt * (own ? jy_a : jy_b) / OPAL_EPS0);
+                const double ez = s_ez[k] + (g.dt * OPAL_C_SQD * (s_by[k] - s_by[k - 1]) / g.dx - g.dt * (own ? jz_a : jz_b) / OPAL_EPS0);
                 s_ey[k] = ey; s_ez[k] = ez;
             }
         }
@@ -1082,9 +1089,12 @@ __device__ __forceinline__ bool segments_filling(const StatusDev* st, int mover_
 // replayed step of one lean species is three launches (push, scatter, this).
 __global__ void __launch_bounds__(FT) k_grid_step(GridDev g, GridDev o, StatusDev* st, int last_species, unsigned* bar /* count, generation */,
                                                   int mover_cap, int clear_next) {
-    if (*(volatile const int*)&st->halt) return;
+    // (all the status words in one round trip: the branch on `halt` comes after the loads of the others have been issued)
+    const int halt = *(volatile const int*)&st->halt, n_overflow = *(volatile const int*)&st->n_overflow;
+    const unsigned err = *(volatile const unsigned*)&st->err;
     const bool filling = segments_filling(st, mover_cap, threadIdx.x, blockDim.x);
-    if (st->n_overflow > 0 || st->err || filling) {       // the same for every block: nobody advances the fields
+    if (halt) return;
+    if (n_overflow > 0 || err || filling) {               // the same for every block: nobody advances the fields
         if (blockIdx.x == 0 && threadIdx.x == 0) { st->halt_species = last_species; __threadfence(); st->halt = 1; }
         return;
     }
