@@ -409,7 +409,7 @@ bool ensure_cell_movers(opal_ctx* c, int sp, long long n_particles) {
 // Strips too narrow for this plasma?  (A relativistically hot cell sends half its particles next door every step; what does not
 // fit its strip goes through the segmented buffer and k_scatter: global atomics per record.)  Small grids can afford wide strips.
 int strip_width_cap(const opal_ctx* c) {
-    const long long by_memory = (long long)(1.0e9 / (2.0 * sizeof(StripRec) * (double)c->g.nx)) / 16 * 16;    // ~1 GB per strip buffer
+    const long long by_memory = (long long)(env_double("OPAL_STRIP_BYTES", 2.0e9) / (2.0 * sizeof(StripRec) * (double)c->g.nx)) / 16 * 16;    // ~2 GB per strip buffer
     return (int)std::min<long long>(by_memory, 2048);      // (a large grid stays with what ensure_cell_movers gave it)
 }
 bool strips_too_narrow(const opal_ctx* c, int sp) {
